@@ -1,0 +1,164 @@
+/*
+ * mvdecon.h -- C ABI of libmvdecon.so, the B200 (sm_100a) implementation of the multi-view
+ * Richardson-Lucy deconvolution inner loop of PreibischLab/SPIM_Registration.
+ *
+ * Part 1 are the symbols the reference binds through JNA today; a library exporting them is a
+ * drop-in for the reference's "FourierConvolutionCUDALib".  Part 2 is the resident whole-loop API
+ * (SURVEY.md section 8b "Level-1"), which keeps every view, weight, kernel spectrum, psi and the
+ * quotient in HBM for the whole deconvolution.  Citations are relative to the reference tree,
+ * J/ = src/main/java/.
+ *
+ * Conventions: all pixel data float32, x fastest (index = x + X*(y + Y*z)).  Part 1 passes
+ * dimensions reversed (z,y,x) exactly as the reference does (MVDeconFFTThreads.java:136-144);
+ * Part 2 passes dimensions as (x,y,z).  No function retains a caller pointer after it returns.
+ * No function calls exit()/abort(); Part 2 functions return 0 on success, non-zero on failure,
+ * and every failure latches a message readable with mvdGetLastError().
+ */
+#ifndef MVDECON_H
+#define MVDECON_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------
+ * Part 1 -- legacy JNA symbols
+ * ------------------------------------------------------------------------------------------ */
+
+/* J/spim/process/cuda/CUDAStandardFunctions.java:15 */
+int getCUDAcomputeCapabilityMinorVersion(int devCUDA);
+/* CUDAStandardFunctions.java:16 */
+int getCUDAcomputeCapabilityMajorVersion(int devCUDA);
+/* CUDAStandardFunctions.java:17-20 : -1 = driver failure, 0 = no device (CUDATools.java:37-48) */
+int getNumDevicesCUDA(void);
+/* CUDAStandardFunctions.java:21 : caller passes a zeroed 256-byte buffer (CUDATools.java:55,63-69) */
+void getNameDeviceCUDA(int devCUDA, char* name);
+/* CUDAStandardFunctions.java:22 : total device memory in bytes (Java long) */
+long long getMemDeviceCUDA(int devCUDA);
+/* CUDAStandardFunctions.java:23 : free device memory in bytes (optional in the reference,
+ * CUDATools.java:76-84 catches UnsatisfiedLinkError) */
+long long getFreeMemDeviceCUDA(int devCUDA);
+
+/* J/spim/process/cuda/CUDAFourierConvolution.java:10, called from
+ * MVDeconFFTThreads.java:65-68 and :88-91 (and legacy LRFFTThreads.java:49,64).
+ * Convolves the block `im` (imDim = {z,y,x}) in place with `kernel` (kernelDim = {z,y,x}), kernel
+ * centre at floor(K/2) (J/fftMethods/FFTConvolution.java:506-516).  Values outside the block are
+ * taken as zero; the reference only consumes block coordinates [K/2, B-1-K/2]
+ * (Block.java:313-359), for which the extension is irrelevant.  Re-entrant: one host thread per
+ * device may call concurrently (MVDeconFFT.java:426-445).  On failure `im` is left untouched and
+ * the error is latched (mvdGetLastError). */
+void convolution3DfftCUDAInPlace(float* im, int* imDim, float* kernel, int* kernelDim, int devCUDA);
+
+/* CUDAFourierConvolution.java:9 -- declared by the reference, never called.  Returns a
+ * malloc()ed array with the result (caller frees) or NULL on failure. */
+float* convolution3DfftCUDA(float* im, int* imDim, float* kernel, int* kernelDim, int devCUDA);
+
+/* ------------------------------------------------------------------------------------------
+ * Part 2 -- resident deconvolution loop
+ * Mirrors MVDeconvolution (J/spim/process/fusion/deconvolution/MVDeconvolution.java:73-190,
+ * 333-444) with MVDeconFFT.convolve1/convolve2 (MVDeconFFT.java:363-535) fused in.
+ * ------------------------------------------------------------------------------------------ */
+
+typedef struct mvdContext mvdContext;
+
+/* Copies the last error message of the calling thread (or of the last failing legacy call) into
+ * buf (n bytes, always NUL-terminated).  Returns the latched code (0 = no error) and clears it. */
+int mvdGetLastError(char* buf, int n);
+
+/* Library/build description ("mvdecon-b200 <version> sm_100a ...") */
+const char* mvdVersion(void);
+
+#define MVD_MEM_HOST 0
+#define MVD_MEM_DEVICE 1
+
+/* Create a context on CUDA device `device` for one brick of the deconvolved volume.
+ *   globalDim   (x,y,z) size of the whole deconvolved volume psi.
+ *   brickOffset (x,y,z) first voxel of this brick, brickDim its size; NULL, NULL = whole volume.
+ *   ghost       (x,y,z) halo width kept around the brick for psi and the quotient (filled by the
+ *               caller's halo exchange, see mvdArrayInfo); NULL or zeros for a single brick.  Ghost
+ *               layers are clipped at the global volume border, where the reference's
+ *               out-of-bounds rules apply instead (mirror-single for psi, constant 1 for the
+ *               quotient; MVDeconFFTThreads.java:23,42,57,82).
+ *   lambda      Tikhonov parameter, 0 = off (EfficientBayesianBased.java:89,252-253).
+ *   minValue    floor of psi, 1e-4f in the reference (MVDeconvolution.java:49). */
+int mvdCreate(mvdContext** ctx, int device, const int globalDim[3], const int brickOffset[3], const int brickDim[3],
+              const int ghost[3], double lambda, float minValue);
+int mvdDestroy(mvdContext* ctx);
+
+/* Use an existing CUDA stream (cudaStream_t passed as void*) for all work of this context. */
+int mvdSetStream(mvdContext* ctx, void* cudaStream);
+int mvdSynchronize(mvdContext* ctx);
+
+/* Add one view (MVDeconInput.add / new MVDeconFFT, MVDeconFFT.java:57-158).
+ *   img      brickDim floats: the transformed view, 0 = no data (MVDeconvolution.java:496).
+ *   weight   brickDim floats or NULL; with NULL the constant `weightConst` is used (the
+ *            reference's NO_WEIGHTS case after normalisation, ProcessForDeconvolution.java:351-384).
+ *   kernel1, kernel2  already prepared as by MVDeconFFT.init (MVDeconFFT.java:162-303), dims (x,y,z).
+ *   memKind  MVD_MEM_HOST or MVD_MEM_DEVICE: where img and weight live (kernels are always host).
+ * Returns the view index through *viewIndex (may be NULL). */
+int mvdAddView(mvdContext* ctx, const float* img, const float* weight, float weightConst, const float* kernel1,
+               const int kernel1Dim[3], const float* kernel2, const int kernel2Dim[3], int memKind, int* viewIndex);
+int mvdNumViews(mvdContext* ctx);
+
+/* psi initialisation (MVDeconvolution.java:105-127, FirstIteration.java:63-171):
+ * mvdFirstIterationSums returns this brick's sum of per-voxel view averages and the count of
+ * voxels with data; mvdFillPsi sets psi (brick and ghost) to a constant; mvdInitPsiAverage does
+ * both for a single brick (NaN average -> 0.5) and returns the average. */
+int mvdFirstIterationSums(mvdContext* ctx, double* sum, long long* count);
+int mvdFillPsi(mvdContext* ctx, float value);
+int mvdInitPsiAverage(mvdContext* ctx, double* avg);
+/* Start from a given psi instead (MVDeconvolution.initialImage, MVDeconvolution.java:95-104):
+ * brickDim floats; values <= 0 or NaN are not touched here (the reference replaces them while
+ * loading, MVDeconvolution.java:237-320 -- do that before the call). */
+int mvdSetPsi(mvdContext* ctx, const float* psi, int memKind);
+int mvdGetPsi(mvdContext* ctx, float* psi, int memKind);
+
+/* Whole iterations on a single brick (MVDeconvolution.runIteration, :333-444): for every view in
+ * order conv1 -> quotient -> conv2 -> update.  sumChange/maxChange (may be NULL) receive
+ * numIterations*numViews values, index = iteration*numViews + view (the per-view log line of
+ * MVDeconvolution.java:427-436).  Fails if the context has ghost layers (use the step API). */
+int mvdRunIterations(mvdContext* ctx, int numIterations, double* sumChange, double* maxChange);
+
+/* Step API for bricks with ghost layers.  Per view and iteration the caller runs
+ *   mvdStepQuotient(v)   quotient = img_v > 0 ? img_v / conv1_v(psi) : 1        on the brick
+ *   <exchange MVD_ARRAY_QUOTIENT ghost layers with the neighbouring bricks>
+ *   mvdStepUpdate(v)     psi = update(psi, conv2_v(quotient), w_v, lambda)       on the brick
+ *   <exchange MVD_ARRAY_PSI ghost layers>
+ * statSlot indexes a device-side statistics table read back with mvdGetStats. */
+int mvdStepQuotient(mvdContext* ctx, int view);
+int mvdStepUpdate(mvdContext* ctx, int view, int statSlot);
+int mvdGetStats(mvdContext* ctx, int firstSlot, int numSlots, double* sumChange, double* maxChange);
+
+#define MVD_ARRAY_PSI 0
+#define MVD_ARRAY_QUOTIENT 1
+/* Device pointer and geometry of a ghosted array: dim = extent, off = index of brick voxel 0. */
+int mvdArrayInfo(mvdContext* ctx, int which, void** devicePtr, int dim[3], int off[3]);
+
+/* psi = 0 where no view has data (MVDeconvolution.java:180-187). */
+int mvdMaskNeverUpdated(mvdContext* ctx);
+
+/* Stand-alone resident convolution with the engine used by the loop: out = conv(ext(src), kernel)
+ * restricted to the volume, src/out dim (x,y,z) host arrays.  extMode 0 zero, 1 constant
+ * extValue, 2 mirror-single.  Used by the tests and by the kernel preparation. */
+int mvdConvolve(int device, const float* src, const int dim[3], const float* kernel, const int kernelDim[3], int extMode,
+                float extValue, float* out);
+
+/* Tile plan chosen for (dim, kernelDim): writes up to maxTiles records of 12 ints
+ * (window size b[3], window origin o[3], first output voxel e[3], output count n[3]) and returns
+ * the tile count, or -1. */
+int mvdPlanTiles(const int dim[3], const int kernelDim[3], int* out, int maxTiles);
+
+/* Block tiling of the reference, bit-exact (BlockGeneratorFixedSizePrecise.java:25-101).
+ * Writes per block 5*numDimensions values: blockSize, offset, effectiveSize, effectiveOffset,
+ * effectiveLocalOffset.  Returns the number of blocks, 0 if blockSize is smaller than the kernel
+ * (the reference returns null, :38-42), or -1 if maxBlocks is too small. */
+long long mvdDivideIntoBlocks(const long long* imgSize, const long long* kernelSize, const long long* blockSize,
+                              int numDimensions, long long* out, long long maxBlocks);
+
+/* Counters for bench.py: kernels launched by this library in the calling process. */
+long long mvdKernelLaunchCount(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MVDECON_H */

@@ -1,0 +1,336 @@
+"""CPU oracle (numpy/scipy) of the multi-view deconvolution hot path -- TEST INFRASTRUCTURE ONLY.
+
+This file restates, function by function, the algorithm of PreibischLab/SPIM_Registration's
+multi-view Richardson-Lucy loop so that the CUDA library can be checked against it.  Only
+tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may import it; the product
+(spim_registration_b200/) never does.
+
+PARITY UNPINNED: the reference ships no tests, golden vectors or fixtures for this path and
+cannot be executed here (no JVM, dependencies not vendored).  The oracle
+is pinned only against the known-answer values derivable from the reference's own `main`
+methods (Block.java:367-402 tiling, MVDeconvolution.java:707-714 tikhonov table) -- see
+tests/test_oracle.py.
+
+Array convention: numpy arrays are indexed [z, y, x] (C order), i.e. x fastest, matching the
+reference's ArrayImg layout index = x + X*(y + Y*z).  Citations are relative to
+/root/reference/src/main/java/ (abbreviated J/).
+
+Convolutions are evaluated exactly (float64 FFT on the explicitly extended array, then cast to
+float32 wherever the reference stores a FloatType) instead of through a float32 FFT as the
+reference does (J/fftMethods/FFTConvolution.java:470-551); the convention is TRUE convolution
+with the kernel centre at floor(K/2) (FFTConvolution.java:506-516), see SURVEY.md 8c caveat.
+"""
+import math
+
+import numpy as np
+from scipy import signal
+
+F32 = np.float32
+MIN_VALUE = F32(0.0001)  # MVDeconvolution.java:49 / MVDeconInput.java:12
+
+PSFTYPES = ("OPTIMIZATION_II", "OPTIMIZATION_I", "EFFICIENT_BAYESIAN", "INDEPENDENT")  # MVDeconFFT.java:28
+
+
+# --------------------------------------------------------------------------------------------
+# J/spim/process/fusion/FusionHelper.java:236-260
+def divide_into_portions(image_size, num_portions):
+    chunk = image_size // num_portions
+    mod = image_size % num_portions
+    out = []
+    for pid in range(num_portions):
+        start = pid * chunk
+        loop = chunk + mod if pid == num_portions - 1 else chunk
+        out.append((start, loop))
+    return out
+
+
+# J/spim/process/fusion/deconvolution/AdjustInput.java:44-100
+def sum_img(img, num_threads):
+    """sumImg including its quirk: the partial sum of the portion that started first
+    (deterministically restated as portion 0) is added twice (AdjustInput.java:93-97)."""
+    flat = np.asarray(img, dtype=F32).reshape(-1).astype(np.float64)
+    portions = divide_into_portions(flat.size, num_threads * 2)
+    sums = [math.fsum(flat[s:s + n]) for (s, n) in portions]
+    return math.fsum([sums[0]] + sums)
+
+
+# AdjustInput.java:29-36
+def norm_img(img, num_threads):
+    s = sum_img(img, num_threads)
+    return (np.asarray(img, dtype=F32).astype(np.float64) / s).astype(F32)
+
+
+# J/spim/process/fusion/deconvolution/Mirror.java:31-108 (sequential semantics)
+def mirror(img, dimension):
+    """dimension counts x=0, y=1, z=2.  Odd sizes: a true flip.  Even sizes: the middle pair is
+    swapped twice and therefore stays (Mirror.java:72, sizeMirrorH = dim/2)."""
+    a = np.array(img, dtype=F32, copy=True)
+    axis = a.ndim - 1 - dimension
+    n = a.shape[axis]
+    a = np.moveaxis(a, axis, 0)
+    out = a.copy()
+    half = n // 2
+    for p in range(half + 1):
+        q = n - 1 - p
+        tmp = out[p].copy()
+        out[p] = out[q]
+        out[q] = tmp
+    return np.ascontiguousarray(np.moveaxis(out, 0, axis))
+
+
+# MVDeconFFT.java:315-323
+def compute_inverted_kernel(kernel):
+    k = np.asarray(kernel, dtype=F32)
+    for d in range(k.ndim):
+        k = mirror(k, d)
+    return k
+
+
+# MVDeconFFT.java:305-313, 325-333 (float multiplication repeated numViews-1 times)
+def compute_exponential_kernel(kernel, num_views):
+    k = np.asarray(kernel, dtype=F32)
+    r = k.copy()
+    for _ in range(1, num_views):
+        r = (r * k).astype(F32)
+    return r
+
+
+# --------------------------------------------------------------------------------------------
+# out-of-bounds rules
+def extend(a, halo_lo, halo_hi, mode, value=0.0):
+    """Extend array a by halo_lo/halo_hi (per numpy axis) voxels.
+    mode 'mirror' = Views.extendMirrorSingle (edge voxel not repeated), 'const' = extendValue,
+    'zero' = extendZero."""
+    a = np.asarray(a)
+    pad = list(zip(halo_lo, halo_hi))
+    if mode == "mirror":
+        # np.pad 'reflect' needs halo < n; fall back to explicit index maps otherwise
+        if all(max(lo, hi) < n for (lo, hi), n in zip(pad, a.shape)):
+            return np.pad(a, pad, mode="reflect")
+        out = a
+        for ax, ((lo, hi), n) in enumerate(zip(pad, a.shape)):
+            idx = np.arange(-lo, n + hi)
+            if n == 1:
+                idx = np.zeros_like(idx)
+            else:
+                p = 2 * n - 2
+                idx = np.mod(idx, p)
+                idx = np.where(idx >= n, p - idx, idx)
+            out = np.take(out, idx, axis=ax)
+        return out
+    if mode == "const":
+        return np.pad(a, pad, mode="constant", constant_values=value)
+    if mode == "zero":
+        return np.pad(a, pad, mode="constant", constant_values=0.0)
+    raise ValueError(mode)
+
+
+def convolve_extended(f, kernel, mode, value=0.0):
+    """conv(ext(f), k)(x) = sum_j ext(f)(x + K//2 - j) k(j) for x in the domain of f.
+    (MVDeconFFT.java:363-535 semantics, FFTConvolution.java:506-516 kernel centre.)  float32 out."""
+    k = np.asarray(kernel, dtype=np.float64)
+    K = k.shape
+    hr = [s // 2 for s in K]           # reads up to x + K//2
+    hl = [s - 1 - s // 2 for s in K]   # and down to x - (K-1-K//2)
+    fe = extend(np.asarray(f, dtype=np.float64), hl, hr, mode, value)
+    out = signal.fftconvolve(fe, k, mode="valid")
+    assert out.shape == np.asarray(f).shape
+    return out.astype(F32)
+
+
+def convolve_direct(f, kernel, mode, value=0.0):
+    """FFT-free O(N K^3) cross-check of convolve_extended for tiny arrays."""
+    k = np.asarray(kernel, dtype=np.float64)
+    K = k.shape
+    hr = [s // 2 for s in K]
+    hl = [s - 1 - s // 2 for s in K]
+    fe = extend(np.asarray(f, dtype=np.float64), hl, hr, mode, value)
+    out = np.zeros(np.asarray(f).shape, dtype=np.float64)
+    Z, Y, X = out.shape
+    for jz in range(K[0]):
+        for jy in range(K[1]):
+            for jx in range(K[2]):
+                # ext index = x + hl + (K//2 - j) ... with ext origin at -hl: x + K//2 - j + hl
+                oz, oy, ox = hl[0] + hr[0] - jz, hl[1] + hr[1] - jy, hl[2] + hr[2] - jx
+                out += k[jz, jy, jx] * fe[oz:oz + Z, oy:oy + Y, ox:ox + X]
+    return out.astype(F32)
+
+
+# --------------------------------------------------------------------------------------------
+# kernel preparation, MVDeconFFT.init (MVDeconFFT.java:162-303) driven by MVDeconInput.init
+# (MVDeconInput.java:43-49): views are initialised IN ORDER, so while view v is prepared the
+# kernel1 of views w < v is already normalised and that of views w > v is not yet.
+def _conv_zero_same(inp, kernel):
+    # new FFTConvolution(Views.extendZero(input), input, Views.extendZero(kernel), kernel, output)
+    return convolve_extended(inp, kernel, "zero")
+
+
+def init_kernels(psfs, psftype, num_threads=8):
+    """Returns (kernel1[], kernel2[]) as float32 arrays [z,y,x]."""
+    assert psftype in PSFTYPES
+    k1 = [np.array(p, dtype=F32, copy=True) for p in psfs]
+    k2 = [None] * len(k1)
+    V = len(k1)
+    for v in range(V):
+        k1[v] = norm_img(k1[v], num_threads)  # :165
+        if V == 1 or psftype == "INDEPENDENT":  # :174-180
+            k2[v] = compute_inverted_kernel(k1[v])
+        elif psftype == "EFFICIENT_BAYESIAN":  # :181-244
+            tmp = compute_inverted_kernel(k1[v])
+            for w in range(V):
+                if w == v:
+                    continue
+                out = _conv_zero_same(compute_inverted_kernel(k1[v]), k1[w])
+                out = _conv_zero_same(out, compute_inverted_kernel(k1[w]))
+                tmp = (out * tmp).astype(F32)
+            k2[v] = norm_img(tmp, num_threads)
+        elif psftype == "OPTIMIZATION_I":  # :245-291
+            tmp = k1[v].copy()
+            for w in range(V):
+                if w == v:
+                    continue
+                out = _conv_zero_same(k1[v], compute_inverted_kernel(k1[w]))
+                tmp = (out * tmp).astype(F32)
+            tmp = norm_img(tmp, num_threads)
+            k2[v] = compute_inverted_kernel(tmp)
+        else:  # OPTIMIZATION_II :292-302
+            e = compute_exponential_kernel(k1[v], V)
+            e = norm_img(e, num_threads)
+            k2[v] = compute_inverted_kernel(e)
+    return k1, k2
+
+
+# --------------------------------------------------------------------------------------------
+# MVDeconvolution.java:192-235 + FirstIteration.java:63-171
+def fuse_first_iteration(imgs):
+    """Returns (avg, count_image).  avg = mean over voxels with >= 1 view of the mean of the views
+    having data there (double accumulation)."""
+    stack = np.stack([np.asarray(i, dtype=F32).astype(np.float64) for i in imgs])
+    pos = stack > 0
+    cnt = pos.sum(axis=0)
+    s = np.where(pos, stack, 0.0).sum(axis=0)
+    has = cnt > 0
+    total = math.fsum((s[has] / cnt[has]).ravel())
+    n = int(has.sum())
+    avg = total / n if n > 0 else float("nan")
+    return avg, cnt.astype(F32)
+
+
+# MVDeconvolution.java:473-525
+def compute_quotient(psi_blurred, img):
+    pb = np.asarray(psi_blurred, dtype=F32)
+    im = np.asarray(img, dtype=F32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        q = (im / pb).astype(F32)
+    return np.where(im > 0, q, F32(1.0)).astype(F32)
+
+
+# MVDeconvolution.java:705
+def tikhonov(value, lam):
+    return (np.sqrt(1.0 + 2.0 * lam * value) - 1.0) / lam
+
+
+# MVDeconvolution.java:582-703 (computeFinalValues + computeNextValue + change)
+def compute_final_values(psi, integral, weight, lam, min_value=MIN_VALUE):
+    psi = np.asarray(psi, dtype=F32)
+    integral = np.asarray(integral, dtype=F32)
+    weight = np.broadcast_to(np.asarray(weight, dtype=F32), psi.shape)
+    with np.errstate(all="ignore"):
+        value = (psi * integral).astype(F32)
+        if lam > 0:
+            adj_pos = tikhonov(value.astype(np.float64), float(lam)).astype(F32)
+        else:
+            adj_pos = value
+        adjusted = np.where(value > 0, adj_pos, F32(min_value)).astype(F32)
+        nxt = np.where(np.isnan(adjusted), F32(min_value), np.maximum(F32(min_value), adjusted)).astype(F32)
+        new = (psi + ((nxt - psi).astype(F32) * weight).astype(F32)).astype(F32)
+        change = np.abs((new - psi).astype(F32)).astype(F32)
+    sum_change = float(np.sum(change.astype(np.float64)))
+    max_change = float(np.max(change)) if change.size else -1.0
+    return new, sum_change, max_change
+
+
+def run_deconvolution(imgs, weights, kernel1, kernel2, num_iterations, lam, psi0=None, min_value=MIN_VALUE, conv=None):
+    """MVDeconvolution constructor (MVDeconvolution.java:73-190) given prepared kernels.
+    weights[v]: array or scalar.  Returns (psi, stats[iter][view] = (sum, max), avg)."""
+    conv = conv or convolve_extended
+    V = len(imgs)
+    avg, cnt = fuse_first_iteration(imgs)
+    if psi0 is None:
+        if math.isnan(avg):
+            avg = 0.5  # :117-121
+        psi = np.full(np.asarray(imgs[0]).shape, F32(avg), dtype=F32)
+    else:
+        psi = np.array(psi0, dtype=F32, copy=True)
+    stats = []
+    for _ in range(num_iterations):  # runIteration :333-444
+        row = []
+        for v in range(V):
+            t1 = conv(psi, kernel1[v], "mirror")            # convolve1 :362
+            t1 = compute_quotient(t1, imgs[v])              # :371-385
+            t2 = conv(t1, kernel2[v], "const", 1.0)         # convolve2 :397
+            psi, s, m = compute_final_values(psi, t2, weights[v], lam, min_value)  # :405-436
+            row.append((s, m))
+        stats.append(row)
+    psi = np.where(cnt == 0, F32(0), psi).astype(F32)       # :180-187
+    return psi, stats, avg
+
+
+# --------------------------------------------------------------------------------------------
+# J/spim/process/cuda/BlockGeneratorFixedSizePrecise.java:25-101; all vectors in (x,y,z) order
+def divide_into_blocks(img_size, kernel_size, block_size):
+    n = len(img_size)
+    eff = [block_size[d] - kernel_size[d] + 1 for d in range(n)]
+    if any(e <= 0 for e in eff):
+        return None  # :38-42
+    loc = [kernel_size[d] // 2 for d in range(n)]
+    num = [img_size[d] // eff[d] + (1 if img_size[d] % eff[d] else 0) for d in range(n)]
+    blocks = []
+    total = 1
+    for v in num:
+        total *= v
+    cur = [0] * n
+    for _ in range(total):  # dimension 0 fastest (:68-76)
+        eoff = [cur[d] * eff[d] for d in range(n)]
+        off = [eoff[d] - kernel_size[d] // 2 for d in range(n)]
+        esize = [min(eff[d], img_size[d] - eoff[d]) for d in range(n)]
+        blocks.append(dict(blockSize=list(block_size), offset=off, effectiveSize=esize, effectiveOffset=eoff,
+                           effectiveLocalOffset=list(loc)))
+        for d in range(n):
+            cur[d] += 1
+            if cur[d] < num[d]:
+                break
+            cur[d] = 0
+    return blocks
+
+
+# Block.copyBlock (Block.java:114-153, 233-271): block[p] = extended_source(p + offset)
+def copy_block(source, block, mode, value=0.0):
+    src = np.asarray(source, dtype=F32)
+    bs, off = block["blockSize"], block["offset"]
+    n = src.shape[::-1]  # (x,y,z)
+    lo = [max(0, -off[d]) for d in range(3)]
+    hi = [max(0, off[d] + bs[d] - n[d]) for d in range(3)]
+    ext = extend(src, lo[::-1], hi[::-1], mode, value)
+    s = [off[d] + lo[d] for d in range(3)]
+    return np.ascontiguousarray(ext[s[2]:s[2] + bs[2], s[1]:s[1] + bs[1], s[0]:s[0] + bs[0]]).astype(F32)
+
+
+# Block.pasteBlock (Block.java:155-195, 313-359)
+def paste_block(target, block_data, block):
+    eo, es, el = block["effectiveOffset"], block["effectiveSize"], block["effectiveLocalOffset"]
+    target[eo[2]:eo[2] + es[2], eo[1]:eo[1] + es[1], eo[0]:eo[0] + es[0]] = \
+        block_data[el[2]:el[2] + es[2], el[1]:el[1] + es[1], el[0]:el[0] + es[0]]
+
+
+def convolve_blockwise(f, kernel, mode, value, block_size, block_conv):
+    """The reference's blocked path (MVDeconFFTThreads.java:52-94): copyBlock from the extended
+    source, convolve the block with `block_conv(block, kernel)` (any extension), pasteBlock."""
+    f = np.asarray(f, dtype=F32)
+    ks = list(np.asarray(kernel).shape[::-1])
+    blocks = divide_into_blocks(list(f.shape[::-1]), ks, list(block_size))
+    out = np.zeros_like(f)
+    for b in blocks:
+        data = copy_block(f, b, mode, value)
+        paste_block(out, block_conv(data, kernel), b)
+    return out

@@ -1,0 +1,635 @@
+// extern "C" surface of libmvdecon.so (include/mvdecon.h).
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <limits>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/mvdecon.h"
+#include "engine.h"
+#include "volume_kernels.h"
+
+using namespace mvd;
+
+// ---- error latch ---------------------------------------------------------------------------
+static thread_local std::string t_err;
+static thread_local int t_err_code = 0;
+static std::mutex g_err_mutex;
+static std::string g_err;  // last error of any thread (legacy void symbols run on Java worker threads)
+static int g_err_code = 0;
+
+static int latch(int code, const std::string& msg) {
+    t_err = msg;
+    t_err_code = code;
+    {
+        std::lock_guard<std::mutex> lk(g_err_mutex);
+        g_err = msg;
+        g_err_code = code;
+    }
+    std::fprintf(stderr, "[libmvdecon] error %d: %s\n", code, msg.c_str());
+    return code;
+}
+
+template <class F> static int guarded(F&& f) {
+    try {
+        f();
+        return 0;
+    } catch (const CudaError& e) {
+        cudaGetLastError();  // clear the sticky flag of non-fatal errors
+        return latch(2, e.what());
+    } catch (const std::invalid_argument& e) {
+        return latch(1, e.what());
+    } catch (const std::bad_alloc&) {
+        return latch(3, "out of host memory");
+    } catch (const std::exception& e) {
+        return latch(4, e.what());
+    } catch (...) {
+        return latch(5, "unknown failure");
+    }
+}
+
+extern "C" int mvdGetLastError(char* buf, int n) {
+    int code = t_err_code;
+    std::string msg = t_err;
+    if (code == 0) {
+        std::lock_guard<std::mutex> lk(g_err_mutex);
+        code = g_err_code;
+        msg = g_err;
+        g_err_code = 0;
+        g_err.clear();
+    }
+    t_err_code = 0;
+    t_err.clear();
+    if (buf && n > 0) {
+        std::strncpy(buf, msg.c_str(), (size_t)n - 1);
+        buf[n - 1] = 0;
+    }
+    return code;
+}
+
+extern "C" const char* mvdVersion(void) { return "mvdecon-b200 0.1 sm_100a (tiled overlap-save FFT, fused epilogues)"; }
+extern "C" long long mvdKernelLaunchCount(void) { return g_kernel_launches.load(); }
+
+// ---- context -------------------------------------------------------------------------------
+struct ViewData {
+    float* img = nullptr;
+    float* weight = nullptr;
+    float weight_const = 1.f;
+    int plan1 = -1, plan2 = -1;
+    std::unique_ptr<KernelSpectra> spec1, spec2;
+};
+
+struct mvdContext {
+    int device = 0;
+    Device* dev = nullptr;
+    int gdim[3], boff[3], bdim[3], glo[3], ghi[3];
+    int adim[3];  // ghosted array extent
+    double lambda = 0.0;
+    float min_value = 1e-4f;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    float* psi = nullptr;
+    float* quot = nullptr;
+    std::vector<ViewData> views;
+    std::vector<std::unique_ptr<ConvPlan>> plans;
+    Scratch scratch;
+    double* d_sum = nullptr;
+    unsigned int* d_max = nullptr;
+    int stat_capacity = 0;
+    double* d_fi_sum = nullptr;
+    unsigned long long* d_fi_count = nullptr;
+
+    size_t brick_elems() const { return (size_t)bdim[0] * bdim[1] * bdim[2]; }
+    size_t array_elems() const { return (size_t)adim[0] * adim[1] * adim[2]; }
+    bool has_ghost() const {
+        for (int d = 0; d < 3; ++d)
+            if (glo[d] || ghi[d]) return true;
+        return false;
+    }
+    void activate() const { MVD_CUDA(cudaSetDevice(device)); }
+    int plan_for(const int k[3]) {
+        for (size_t i = 0; i < plans.size(); ++i)
+            if (same_plan(*plans[i], bdim, k)) return (int)i;
+        plans.push_back(make_plan(bdim, k));
+        return (int)plans.size() - 1;
+    }
+    void ensure_stats(int n) {
+        if (n <= stat_capacity) return;
+        int cap = std::max(n, std::max(256, stat_capacity * 2));
+        double* ns = nullptr;
+        unsigned int* nm = nullptr;
+        MVD_CUDA(cudaMalloc(&ns, cap * sizeof(double)));
+        MVD_CUDA(cudaMalloc(&nm, cap * sizeof(unsigned int)));
+        MVD_CUDA(cudaMemsetAsync(ns, 0, cap * sizeof(double), stream));
+        MVD_CUDA(cudaMemsetAsync(nm, 0, cap * sizeof(unsigned int), stream));
+        if (d_sum) {
+            MVD_CUDA(cudaMemcpyAsync(ns, d_sum, stat_capacity * sizeof(double), cudaMemcpyDeviceToDevice, stream));
+            MVD_CUDA(cudaMemcpyAsync(nm, d_max, stat_capacity * sizeof(unsigned int), cudaMemcpyDeviceToDevice, stream));
+            MVD_CUDA(cudaStreamSynchronize(stream));
+            cudaFree(d_sum);
+            cudaFree(d_max);
+        }
+        d_sum = ns;
+        d_max = nm;
+        stat_capacity = cap;
+    }
+    Volume ghosted_volume(const float* data, int ext, float ext_value) const {
+        Volume v;
+        v.data = data;
+        for (int d = 0; d < 3; ++d) { v.dim[d] = adim[d]; v.off[d] = glo[d]; v.gmin[d] = boff[d]; v.gdim[d] = gdim[d]; }
+        v.ext = ext;
+        v.ext_value = ext_value;
+        return v;
+    }
+    EpilogueArgs epilogue_base(float* out) const {
+        EpilogueArgs ep;
+        std::memset(&ep, 0, sizeof(ep));
+        ep.out = out;
+        ep.lambda = lambda;
+        ep.min_value = min_value;
+        for (int d = 0; d < 3; ++d) { ep.out_dim[d] = adim[d]; ep.out_off[d] = glo[d]; ep.aux_dim[d] = bdim[d]; }
+        return ep;
+    }
+    ViewPtrs view_ptrs() const {
+        ViewPtrs p;
+        p.n = (int)views.size();
+        for (int i = 0; i < p.n; ++i) p.img[i] = views[i].img;
+        return p;
+    }
+};
+
+static void require(bool ok, const char* msg) {
+    if (!ok) throw std::invalid_argument(msg);
+}
+
+// copy between a dense brick-sized array and the interior of a ghosted array
+static void copy_brick(const mvdContext& c, float* ghosted, float* brick, bool to_ghosted, cudaMemcpyKind kind) {
+    cudaMemcpy3DParms p;
+    std::memset(&p, 0, sizeof(p));
+    cudaPitchedPtr g = make_cudaPitchedPtr(ghosted, (size_t)c.adim[0] * sizeof(float), c.adim[0], c.adim[1]);
+    cudaPitchedPtr b = make_cudaPitchedPtr(brick, (size_t)c.bdim[0] * sizeof(float), c.bdim[0], c.bdim[1]);
+    const cudaPos gpos = make_cudaPos((size_t)c.glo[0] * sizeof(float), c.glo[1], c.glo[2]);
+    const cudaPos zero = make_cudaPos(0, 0, 0);
+    if (to_ghosted) { p.srcPtr = b; p.srcPos = zero; p.dstPtr = g; p.dstPos = gpos; }
+    else { p.srcPtr = g; p.srcPos = gpos; p.dstPtr = b; p.dstPos = zero; }
+    p.extent = make_cudaExtent((size_t)c.bdim[0] * sizeof(float), c.bdim[1], c.bdim[2]);
+    p.kind = kind;
+    MVD_CUDA(cudaMemcpy3DAsync(&p, c.stream));
+}
+
+extern "C" int mvdCreate(mvdContext** out, int device, const int globalDim[3], const int brickOffset[3], const int brickDim[3],
+                         const int ghost[3], double lambda, float minValue) {
+    return guarded([&] {
+        require(out && globalDim, "mvdCreate: null argument");
+        *out = nullptr;
+        std::unique_ptr<mvdContext> c(new mvdContext);
+        c->device = device;
+        c->dev = &Device::get(device);
+        for (int d = 0; d < 3; ++d) {
+            c->gdim[d] = globalDim[d];
+            c->boff[d] = brickOffset ? brickOffset[d] : 0;
+            c->bdim[d] = brickDim ? brickDim[d] : globalDim[d];
+            require(c->gdim[d] > 0 && c->bdim[d] > 0 && c->boff[d] >= 0 && c->boff[d] + c->bdim[d] <= c->gdim[d],
+                    "mvdCreate: brick outside the volume");
+            const int g = ghost ? ghost[d] : 0;
+            require(g >= 0, "mvdCreate: negative ghost width");
+            c->glo[d] = std::min(g, c->boff[d]);
+            c->ghi[d] = std::min(g, c->gdim[d] - (c->boff[d] + c->bdim[d]));
+            c->adim[d] = c->bdim[d] + c->glo[d] + c->ghi[d];
+        }
+        require((double)c->array_elems() < 2147483647.0 * 4.0, "mvdCreate: brick too large");
+        c->lambda = lambda;
+        c->min_value = minValue;
+        MVD_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        c->own_stream = true;
+        MVD_CUDA(cudaMalloc(&c->psi, c->array_elems() * sizeof(float)));
+        MVD_CUDA(cudaMalloc(&c->quot, c->array_elems() * sizeof(float)));
+        MVD_CUDA(cudaMalloc(&c->d_fi_sum, sizeof(double)));
+        MVD_CUDA(cudaMalloc(&c->d_fi_count, sizeof(unsigned long long)));
+        MVD_CUDA(launch_fill(c->psi, c->array_elems(), 0.f, c->stream));
+        MVD_CUDA(launch_fill(c->quot, c->array_elems(), 1.f, c->stream));
+        g_kernel_launches += 2;
+        *out = c.release();
+    });
+}
+
+extern "C" int mvdDestroy(mvdContext* c) {
+    if (!c) return 0;
+    return guarded([&] {
+        cudaSetDevice(c->device);
+        if (c->stream) cudaStreamSynchronize(c->stream);
+        for (auto& v : c->views) {
+            if (v.img) cudaFree(v.img);
+            if (v.weight) cudaFree(v.weight);
+        }
+        c->views.clear();
+        c->plans.clear();
+        if (c->psi) cudaFree(c->psi);
+        if (c->quot) cudaFree(c->quot);
+        if (c->d_sum) cudaFree(c->d_sum);
+        if (c->d_max) cudaFree(c->d_max);
+        if (c->d_fi_sum) cudaFree(c->d_fi_sum);
+        if (c->d_fi_count) cudaFree(c->d_fi_count);
+        if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+        delete c;
+    });
+}
+
+extern "C" int mvdSetStream(mvdContext* c, void* s) {
+    return guarded([&] {
+        require(c, "mvdSetStream: null context");
+        c->activate();
+        MVD_CUDA(cudaStreamSynchronize(c->stream));
+        if (c->own_stream) cudaStreamDestroy(c->stream);
+        c->stream = (cudaStream_t)s;
+        c->own_stream = false;
+    });
+}
+
+extern "C" int mvdSynchronize(mvdContext* c) {
+    return guarded([&] {
+        require(c, "mvdSynchronize: null context");
+        c->activate();
+        MVD_CUDA(cudaStreamSynchronize(c->stream));
+    });
+}
+
+// ---- views ---------------------------------------------------------------------------------
+extern "C" int mvdAddView(mvdContext* c, const float* img, const float* weight, float weightConst, const float* kernel1,
+                          const int k1[3], const float* kernel2, const int k2[3], int memKind, int* viewIndex) {
+    return guarded([&] {
+        require(c && img && kernel1 && kernel2 && k1 && k2, "mvdAddView: null argument");
+        require((int)c->views.size() < kMaxViews, "mvdAddView: too many views");
+        c->activate();
+        for (int d = 0; d < 3; ++d) {
+            const int need1 = k1[d] - 1 - k1[d] / 2, need2 = k2[d] - 1 - k2[d] / 2;
+            const bool lo_nb = c->boff[d] > 0, hi_nb = c->boff[d] + c->bdim[d] < c->gdim[d];
+            if (lo_nb) require(c->glo[d] >= std::max(k1[d] / 2, need1) && c->glo[d] >= std::max(k2[d] / 2, need2),
+                               "mvdAddView: ghost layer narrower than the kernel halo");
+            if (hi_nb) require(c->ghi[d] >= std::max(k1[d] / 2, need1) && c->ghi[d] >= std::max(k2[d] / 2, need2),
+                               "mvdAddView: ghost layer narrower than the kernel halo");
+        }
+        const cudaMemcpyKind kind = memKind == MVD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+        ViewData v;
+        const size_t bytes = c->brick_elems() * sizeof(float);
+        MVD_CUDA(cudaMalloc(&v.img, bytes));
+        MVD_CUDA(cudaMemcpyAsync(v.img, img, bytes, kind, c->stream));
+        if (weight) {
+            MVD_CUDA(cudaMalloc(&v.weight, bytes));
+            MVD_CUDA(cudaMemcpyAsync(v.weight, weight, bytes, kind, c->stream));
+        }
+        v.weight_const = weightConst;
+        v.plan1 = c->plan_for(k1);
+        v.plan2 = c->plan_for(k2);
+        v.spec1 = build_spectra(*c->dev, *c->plans[v.plan1], kernel1, c->stream);
+        v.spec2 = build_spectra(*c->dev, *c->plans[v.plan2], kernel2, c->stream);
+        MVD_CUDA(cudaStreamSynchronize(c->stream));  // caller buffers may go away after return
+        c->views.push_back(std::move(v));
+        if (viewIndex) *viewIndex = (int)c->views.size() - 1;
+    });
+}
+
+extern "C" int mvdNumViews(mvdContext* c) { return c ? (int)c->views.size() : -1; }
+
+// ---- psi -----------------------------------------------------------------------------------
+extern "C" int mvdFirstIterationSums(mvdContext* c, double* sum, long long* count) {
+    return guarded([&] {
+        require(c && sum && count, "mvdFirstIterationSums: null argument");
+        require(!c->views.empty(), "mvdFirstIterationSums: no views");
+        c->activate();
+        MVD_CUDA(cudaMemsetAsync(c->d_fi_sum, 0, sizeof(double), c->stream));
+        MVD_CUDA(cudaMemsetAsync(c->d_fi_count, 0, sizeof(unsigned long long), c->stream));
+        MVD_CUDA(launch_first_iteration_sums(c->view_ptrs(), c->brick_elems(), c->d_fi_sum, c->d_fi_count, c->stream));
+        ++g_kernel_launches;
+        unsigned long long cnt = 0;
+        MVD_CUDA(cudaMemcpyAsync(sum, c->d_fi_sum, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        MVD_CUDA(cudaMemcpyAsync(&cnt, c->d_fi_count, sizeof(cnt), cudaMemcpyDeviceToHost, c->stream));
+        MVD_CUDA(cudaStreamSynchronize(c->stream));
+        *count = (long long)cnt;
+    });
+}
+
+extern "C" int mvdFillPsi(mvdContext* c, float value) {
+    return guarded([&] {
+        require(c, "mvdFillPsi: null context");
+        c->activate();
+        MVD_CUDA(launch_fill(c->psi, c->array_elems(), value, c->stream));
+        ++g_kernel_launches;
+    });
+}
+
+extern "C" int mvdInitPsiAverage(mvdContext* c, double* avg_out) {
+    double sum = 0.0;
+    long long count = 0;
+    int rc = mvdFirstIterationSums(c, &sum, &count);
+    if (rc) return rc;
+    // MVDeconvolution.java:112-126: avg = sum / count, NaN -> 0.5
+    double avg = sum / (double)count;
+    if (std::isnan(avg)) avg = 0.5;
+    if (avg_out) *avg_out = avg;
+    return mvdFillPsi(c, (float)avg);
+}
+
+extern "C" int mvdSetPsi(mvdContext* c, const float* psi, int memKind) {
+    return guarded([&] {
+        require(c && psi, "mvdSetPsi: null argument");
+        c->activate();
+        copy_brick(*c, c->psi, const_cast<float*>(psi), true, memKind == MVD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice);
+        MVD_CUDA(cudaStreamSynchronize(c->stream));
+    });
+}
+
+extern "C" int mvdGetPsi(mvdContext* c, float* psi, int memKind) {
+    return guarded([&] {
+        require(c && psi, "mvdGetPsi: null argument");
+        c->activate();
+        copy_brick(*c, c->psi, psi, false, memKind == MVD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost);
+        MVD_CUDA(cudaStreamSynchronize(c->stream));
+    });
+}
+
+// ---- the loop ------------------------------------------------------------------------------
+static void step_quotient(mvdContext* c, int v) {
+    ViewData& vd = c->views[v];
+    // conv1: psi extended by mirror-single (MVDeconFFTThreads.java:23,57), fused quotient (MVDeconvolution.java:473-525)
+    const Volume src = c->ghosted_volume(c->psi, EXT_MIRROR_SINGLE, 0.f);
+    EpilogueArgs ep = c->epilogue_base(c->quot);
+    ep.img = vd.img;
+    run_convolution(*c->dev, *c->plans[vd.plan1], *vd.spec1, src, EPI_QUOTIENT, ep, c->scratch, c->stream);
+}
+
+static void step_update(mvdContext* c, int v, int slot) {
+    ViewData& vd = c->views[v];
+    c->ensure_stats(slot + 1);
+    MVD_CUDA(cudaMemsetAsync(c->d_sum + slot, 0, sizeof(double), c->stream));
+    MVD_CUDA(cudaMemsetAsync(c->d_max + slot, 0, sizeof(unsigned int), c->stream));
+    // conv2: quotient extended by the constant 1 (MVDeconFFTThreads.java:42,82), fused update (MVDeconvolution.java:582-703)
+    const Volume src = c->ghosted_volume(c->quot, EXT_CONST, 1.f);
+    EpilogueArgs ep = c->epilogue_base(c->psi);
+    ep.weight = vd.weight;
+    ep.weight_const = vd.weight_const;
+    ep.sum_change = c->d_sum + slot;
+    ep.max_change_bits = c->d_max + slot;
+    run_convolution(*c->dev, *c->plans[vd.plan2], *vd.spec2, src, EPI_UPDATE, ep, c->scratch, c->stream);
+}
+
+static void read_stats(mvdContext* c, int first, int n, double* sum, double* mx) {
+    if (n <= 0) return;
+    require(first >= 0 && first + n <= c->stat_capacity, "statistics slot out of range");
+    std::vector<unsigned int> bits(n);
+    std::vector<double> s(n);
+    MVD_CUDA(cudaMemcpyAsync(s.data(), c->d_sum + first, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    MVD_CUDA(cudaMemcpyAsync(bits.data(), c->d_max + first, n * sizeof(unsigned int), cudaMemcpyDeviceToHost, c->stream));
+    MVD_CUDA(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < n; ++i) {
+        if (sum) sum[i] = s[i];
+        if (mx) {
+            float f;
+            std::memcpy(&f, &bits[i], sizeof(f));
+            mx[i] = (double)f;
+        }
+    }
+}
+
+extern "C" int mvdRunIterations(mvdContext* c, int numIterations, double* sumChange, double* maxChange) {
+    return guarded([&] {
+        require(c, "mvdRunIterations: null context");
+        require(!c->views.empty(), "mvdRunIterations: no views");
+        require(!c->has_ghost(), "mvdRunIterations: context has ghost layers, use the step API");
+        require(numIterations >= 0, "mvdRunIterations: negative iteration count");
+        c->activate();
+        const int nv = (int)c->views.size();
+        c->ensure_stats(numIterations * nv);
+        for (int it = 0; it < numIterations; ++it)
+            for (int v = 0; v < nv; ++v) {  // strictly in order, psi updated after every view (MVDeconvolution.java:353-441)
+                step_quotient(c, v);
+                step_update(c, v, it * nv + v);
+            }
+        if (sumChange || maxChange) read_stats(c, 0, numIterations * nv, sumChange, maxChange);
+        else MVD_CUDA(cudaStreamSynchronize(c->stream));
+    });
+}
+
+extern "C" int mvdStepQuotient(mvdContext* c, int view) {
+    return guarded([&] {
+        require(c && view >= 0 && view < (int)c->views.size(), "mvdStepQuotient: bad view");
+        c->activate();
+        step_quotient(c, view);
+    });
+}
+
+extern "C" int mvdStepUpdate(mvdContext* c, int view, int statSlot) {
+    return guarded([&] {
+        require(c && view >= 0 && view < (int)c->views.size() && statSlot >= 0, "mvdStepUpdate: bad argument");
+        c->activate();
+        step_update(c, view, statSlot);
+    });
+}
+
+extern "C" int mvdGetStats(mvdContext* c, int firstSlot, int numSlots, double* sumChange, double* maxChange) {
+    return guarded([&] {
+        require(c, "mvdGetStats: null context");
+        c->activate();
+        read_stats(c, firstSlot, numSlots, sumChange, maxChange);
+    });
+}
+
+extern "C" int mvdArrayInfo(mvdContext* c, int which, void** ptr, int dim[3], int off[3]) {
+    return guarded([&] {
+        require(c && (which == MVD_ARRAY_PSI || which == MVD_ARRAY_QUOTIENT), "mvdArrayInfo: bad argument");
+        if (ptr) *ptr = which == MVD_ARRAY_PSI ? c->psi : c->quot;
+        for (int d = 0; d < 3; ++d) {
+            if (dim) dim[d] = c->adim[d];
+            if (off) off[d] = c->glo[d];
+        }
+    });
+}
+
+extern "C" int mvdMaskNeverUpdated(mvdContext* c) {
+    return guarded([&] {
+        require(c && !c->views.empty(), "mvdMaskNeverUpdated: no views");
+        c->activate();
+        MVD_CUDA(launch_mask_never_updated(c->view_ptrs(), c->bdim, c->psi, c->adim, c->glo, c->stream));
+        ++g_kernel_launches;
+        MVD_CUDA(cudaStreamSynchronize(c->stream));
+    });
+}
+
+// ---- stand-alone convolution ---------------------------------------------------------------
+// dims in (x,y,z); src/out host pointers.
+static void convolve_host(int device, const float* src, const int dim[3], const float* kernel, const int k[3], int ext, float ext_value,
+                          float* out) {
+    Device& dev = Device::get(device);
+    const size_t n = (size_t)dim[0] * dim[1] * dim[2];
+    cudaStream_t st = nullptr;
+    float *d_src = nullptr, *d_out = nullptr;
+    struct Cleanup {
+        cudaStream_t& st; float*& a; float*& b;
+        ~Cleanup() { if (a) cudaFree(a); if (b) cudaFree(b); if (st) cudaStreamDestroy(st); }
+    } cleanup{st, d_src, d_out};
+    MVD_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    MVD_CUDA(cudaMalloc(&d_src, n * sizeof(float)));
+    MVD_CUDA(cudaMalloc(&d_out, n * sizeof(float)));
+    MVD_CUDA(cudaMemcpyAsync(d_src, src, n * sizeof(float), cudaMemcpyHostToDevice, st));
+    auto plan = make_plan(dim, k);
+    auto spec = build_spectra(dev, *plan, kernel, st);
+    Volume v;
+    v.data = d_src;
+    for (int d = 0; d < 3; ++d) { v.dim[d] = dim[d]; v.off[d] = 0; v.gmin[d] = 0; v.gdim[d] = dim[d]; }
+    v.ext = ext;
+    v.ext_value = ext_value;
+    EpilogueArgs ep;
+    std::memset(&ep, 0, sizeof(ep));
+    ep.out = d_out;
+    for (int d = 0; d < 3; ++d) { ep.out_dim[d] = dim[d]; ep.out_off[d] = 0; ep.aux_dim[d] = dim[d]; }
+    Scratch scratch;
+    run_convolution(dev, *plan, *spec, v, EPI_STORE, ep, scratch, st);
+    MVD_CUDA(cudaMemcpyAsync(out, d_out, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    MVD_CUDA(cudaStreamSynchronize(st));
+}
+
+extern "C" int mvdConvolve(int device, const float* src, const int dim[3], const float* kernel, const int kernelDim[3], int extMode,
+                           float extValue, float* out) {
+    return guarded([&] {
+        require(src && dim && kernel && kernelDim && out, "mvdConvolve: null argument");
+        require(extMode >= 0 && extMode <= 2, "mvdConvolve: bad extension mode");
+        convolve_host(device, src, dim, kernel, kernelDim, extMode, extValue, out);
+    });
+}
+
+extern "C" int mvdPlanTiles(const int dim[3], const int kernelDim[3], int* out, int maxTiles) {
+    int count = -1;
+    guarded([&] {
+        require(dim && kernelDim, "mvdPlanTiles: null argument");
+        static const int xy[] = {32, 64, 128};
+        static const int zs[] = {16, 32, 64, 128, 256, 512};
+        std::vector<AxisTile> ax[3] = {plan_axis(dim[0], kernelDim[0], 4, xy, 3), plan_axis(dim[1], kernelDim[1], 1, xy, 3),
+                                       plan_axis(dim[2], kernelDim[2], 1, zs, 6)};
+        require(!ax[0].empty() && !ax[1].empty() && !ax[2].empty(), "mvdPlanTiles: kernel too large");
+        int n = 0;
+        for (const auto& tz : ax[2])
+            for (const auto& ty : ax[1])
+                for (const auto& tx : ax[0]) {
+                    if (out && n < maxTiles) {
+                        const AxisTile* t[3] = {&tx, &ty, &tz};
+                        for (int d = 0; d < 3; ++d) {
+                            out[n * 12 + d] = t[d]->b;
+                            out[n * 12 + 3 + d] = t[d]->o;
+                            out[n * 12 + 6 + d] = t[d]->e;
+                            out[n * 12 + 9 + d] = t[d]->n;
+                        }
+                    }
+                    ++n;
+                }
+        count = n;
+    });
+    return count;
+}
+
+// ---- reference block tiling, bit-exact (BlockGeneratorFixedSizePrecise.java:25-101) ----------
+extern "C" long long mvdDivideIntoBlocks(const long long* imgSize, const long long* kernelSize, const long long* blockSize, int nd,
+                                         long long* out, long long maxBlocks) {
+    if (!imgSize || !kernelSize || !blockSize || nd <= 0 || nd > 8) return -1;
+    long long eff[8], loc[8], num[8], total = 1;
+    for (int d = 0; d < nd; ++d) {
+        eff[d] = blockSize[d] - kernelSize[d] + 1;  // :36
+        if (eff[d] <= 0) return 0;                  // :38-42 (returns null)
+        loc[d] = kernelSize[d] / 2;                 // :44
+        num[d] = imgSize[d] / eff[d];               // :52
+        if (imgSize[d] % eff[d] != 0) ++num[d];     // :55-56
+        total *= num[d];
+    }
+    if (!out) return total;
+    if (total > maxBlocks) return -1;
+    long long cur[8] = {0};
+    for (long long b = 0; b < total; ++b) {  // dimension 0 fastest (LocalizingZeroMinIntervalIterator, :68-76)
+        long long* o = out + b * 5 * nd;
+        for (int d = 0; d < nd; ++d) {
+            const long long eoff = cur[d] * eff[d];  // :85
+            long long esize = eff[d];
+            if (eoff + esize > imgSize[d]) esize = imgSize[d] - eoff;  // :88-89
+            o[0 * nd + d] = blockSize[d];
+            o[1 * nd + d] = eoff - kernelSize[d] / 2;  // :86
+            o[2 * nd + d] = esize;
+            o[3 * nd + d] = eoff;
+            o[4 * nd + d] = loc[d];
+        }
+        for (int d = 0; d < nd; ++d) {
+            if (++cur[d] < num[d]) break;
+            cur[d] = 0;
+        }
+    }
+    return total;
+}
+
+// ---- legacy JNA symbols ----------------------------------------------------------------------
+extern "C" int getNumDevicesCUDA(void) {
+    int n = 0;
+    const cudaError_t e = cudaGetDeviceCount(&n);
+    if (e == cudaErrorNoDevice) return 0;
+    if (e != cudaSuccess) { cudaGetLastError(); return -1; }  // CUDATools.java:39-43 "driver crashed"
+    return n;
+}
+
+static bool device_prop(int dev, cudaDeviceProp& p) {
+    if (cudaGetDeviceProperties(&p, dev) != cudaSuccess) { cudaGetLastError(); return false; }
+    return true;
+}
+
+extern "C" int getCUDAcomputeCapabilityMajorVersion(int dev) {
+    cudaDeviceProp p;
+    return device_prop(dev, p) ? p.major : -1;
+}
+extern "C" int getCUDAcomputeCapabilityMinorVersion(int dev) {
+    cudaDeviceProp p;
+    return device_prop(dev, p) ? p.minor : -1;
+}
+extern "C" void getNameDeviceCUDA(int dev, char* name) {
+    if (!name) return;
+    cudaDeviceProp p;
+    if (!device_prop(dev, p)) { name[0] = 0; return; }
+    std::strncpy(name, p.name, 255);  // caller's buffer is 256 bytes (CUDATools.java:55)
+    name[255] = 0;
+}
+extern "C" long long getMemDeviceCUDA(int dev) {
+    cudaDeviceProp p;
+    return device_prop(dev, p) ? (long long)p.totalGlobalMem : -1;
+}
+extern "C" long long getFreeMemDeviceCUDA(int dev) {
+    size_t f = 0, t = 0;
+    if (cudaSetDevice(dev) != cudaSuccess || cudaMemGetInfo(&f, &t) != cudaSuccess) { cudaGetLastError(); return -1; }
+    return (long long)f;
+}
+
+static int legacy_convolve(const float* im, const int* imDim, const float* kernel, const int* kernelDim, int dev, float* out) {
+    return guarded([&] {
+        require(im && imDim && kernel && kernelDim && out, "convolution3DfftCUDA: null argument");
+        // the reference passes (z,y,x) (MVDeconFFTThreads.java:136-144)
+        const int dim[3] = {imDim[2], imDim[1], imDim[0]};
+        const int k[3] = {kernelDim[2], kernelDim[1], kernelDim[0]};
+        Device& d = Device::get(dev);
+        std::lock_guard<std::mutex> lk(d.legacy_mutex);
+        convolve_host(dev, im, dim, kernel, k, EXT_ZERO, 0.f, out);
+    });
+}
+
+extern "C" void convolution3DfftCUDAInPlace(float* im, int* imDim, float* kernel, int* kernelDim, int devCUDA) {
+    if (!im || !imDim) { latch(1, "convolution3DfftCUDAInPlace: null argument"); return; }
+    const size_t n = (size_t)imDim[0] * imDim[1] * imDim[2];
+    float* tmp = (float*)std::malloc(n * sizeof(float));
+    if (!tmp) { latch(3, "out of host memory"); return; }
+    if (legacy_convolve(im, imDim, kernel, kernelDim, devCUDA, tmp) == 0) std::memcpy(im, tmp, n * sizeof(float));
+    std::free(tmp);  // on failure im is untouched
+}
+
+extern "C" float* convolution3DfftCUDA(float* im, int* imDim, float* kernel, int* kernelDim, int devCUDA) {
+    if (!im || !imDim) { latch(1, "convolution3DfftCUDA: null argument"); return nullptr; }
+    const size_t n = (size_t)imDim[0] * imDim[1] * imDim[2];
+    float* out = (float*)std::malloc(n * sizeof(float));
+    if (!out) { latch(3, "out of host memory"); return nullptr; }
+    if (legacy_convolve(im, imDim, kernel, kernelDim, devCUDA, out) != 0) { std::free(out); return nullptr; }
+    return out;
+}

@@ -1,0 +1,29 @@
+// Launchers of the tiled FFT-convolution kernels (conv_kernels.cu).
+#pragma once
+#include "conv_types.h"
+
+namespace mvd {
+
+struct Twiddles;  // fft_device.cuh
+
+struct TwiddleTables {
+    const float2* t[11];
+};
+
+// true when (bx,by) / bz are sizes the kernels are instantiated for
+bool xy_size_supported(int b);
+bool z_size_supported(int b);
+
+size_t plane_elems(int bx, int by);                 // (bx/2+1)*by complex per z-plane
+size_t tile_scratch_elems(int bx, int by, int bz);  // complex elements per tile
+
+cudaError_t launch_fwd_xy(int bx, int by, int bz, const Volume& src, const Tile* d_tiles, int n_tiles, float2* scratch,
+                          const TwiddleTables& tw, cudaStream_t st);
+// mode 0: forward only + scale (kernel spectrum); mode 1: forward * kspec -> inverse
+cudaError_t launch_z_pass(int bx, int by, int bz, int mode, float2* scratch, const float2* kspec, const Tile* d_tiles, int n_tiles,
+                          float scale, const TwiddleTables& tw, cudaStream_t st);
+cudaError_t launch_inv_xy(int bx, int by, int bz, int epilogue, const float2* scratch, const Tile* d_tiles, int n_tiles, int max_nz,
+                          const EpilogueArgs& ep, const TwiddleTables& tw, cudaStream_t st);
+cudaError_t configure_conv_kernels();  // opt in to > 48 KB dynamic shared memory
+
+}  // namespace mvd

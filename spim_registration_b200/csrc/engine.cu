@@ -1,0 +1,263 @@
+// Host side of the tiled convolution engine (see engine.h).
+#include "engine.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+
+namespace mvd {
+
+std::atomic<long long> g_kernel_launches{0};
+
+void cuda_check(cudaError_t e, const char* what) {
+    if (e != cudaSuccess) throw CudaError(std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+// ---- planner ---------------------------------------------------------------------------
+static inline int round_up(int v, int a) { return (v + a - 1) / a * a; }
+
+std::vector<AxisTile> plan_axis(int n, int k, int align, const int* sizes, int num_sizes) {
+    const int hl = k - 1 - k / 2, hr = k / 2;
+    const int lo = round_up(hl, align);
+    std::vector<int> eff(num_sizes);
+    bool any = false;
+    for (int i = 0; i < num_sizes; ++i) {
+        int e = sizes[i] - lo - hr;
+        e = e / align * align;
+        eff[i] = e;
+        any |= e > 0;
+    }
+    if (!any || n <= 0) return {};
+    // dynamic programme over the first uncovered voxel; cost = sum of window lengths (+ small per-window charge)
+    const long long per_tile = 6;
+    std::vector<long long> cost(n + 1, 0);
+    std::vector<int> pick(n + 1, -1);
+    for (int pos = n - 1; pos >= 0; --pos) {
+        long long best = -1;
+        int bi = -1;
+        for (int i = num_sizes - 1; i >= 0; --i) {  // ties prefer the larger window
+            if (eff[i] <= 0) continue;
+            const long long c = sizes[i] + per_tile + cost[std::min(n, pos + eff[i])];
+            if (best < 0 || c < best) { best = c; bi = i; }
+        }
+        cost[pos] = best;
+        pick[pos] = bi;
+    }
+    std::vector<int> chosen;
+    for (int pos = 0; pos < n;) {
+        chosen.push_back(pick[pos]);
+        pos += eff[pick[pos]];
+    }
+    std::sort(chosen.begin(), chosen.end(), [&](int a, int b) { return sizes[a] > sizes[b]; });
+    std::vector<AxisTile> out;
+    int e = 0;
+    for (int i : chosen) {
+        if (e >= n) break;
+        AxisTile t;
+        t.b = sizes[i];
+        t.e = e;
+        t.o = e - lo;
+        t.n = std::min(eff[i], n - e);
+        out.push_back(t);
+        e += eff[i];
+    }
+    return out;
+}
+
+ConvPlan::~ConvPlan() {
+    for (auto& c : classes)
+        if (c.d_tiles) cudaFree(c.d_tiles);
+}
+
+bool same_plan(const ConvPlan& p, const int dim[3], const int k[3]) {
+    for (int d = 0; d < 3; ++d)
+        if (p.dim[d] != dim[d] || p.k[d] != k[d]) return false;
+    return true;
+}
+
+static const int kXYSizes[] = {32, 64, 128};
+static const int kZSizes[] = {16, 32, 64, 128, 256, 512};
+
+static std::vector<AxisTile> plan_axes(const int dim[3], const int k[3], int d) {
+    if (d == 0) return plan_axis(dim[0], k[0], 4, kXYSizes, 3);
+    if (d == 1) return plan_axis(dim[1], k[1], 1, kXYSizes, 3);
+    return plan_axis(dim[2], k[2], 1, kZSizes, 6);
+}
+
+std::unique_ptr<ConvPlan> make_plan(const int dim[3], const int k[3]) {
+    auto plan = std::make_unique<ConvPlan>();
+    std::vector<AxisTile> ax[3];
+    for (int d = 0; d < 3; ++d) {
+        plan->dim[d] = dim[d];
+        plan->k[d] = k[d];
+        if (dim[d] <= 0 || k[d] <= 0) throw std::invalid_argument("make_plan: non-positive size");
+        ax[d] = plan_axes(dim, k, d);
+        if (ax[d].empty())
+            throw std::invalid_argument("make_plan: kernel size " + std::to_string(k[d]) + " in dimension " + std::to_string(d) +
+                                        " exceeds the largest supported FFT window");
+    }
+    std::map<std::vector<int>, size_t> index;
+    for (const auto& tz : ax[2])
+        for (const auto& ty : ax[1])
+            for (const auto& tx : ax[0]) {
+                std::vector<int> key = {tx.b, ty.b, tz.b};
+                auto it = index.find(key);
+                if (it == index.end()) {
+                    TileClass c;
+                    c.b[0] = tx.b; c.b[1] = ty.b; c.b[2] = tz.b;
+                    plan->classes.push_back(std::move(c));
+                    it = index.emplace(key, plan->classes.size() - 1).first;
+                }
+                TileClass& c = plan->classes[it->second];
+                Tile t;
+                t.o[0] = tx.o; t.o[1] = ty.o; t.o[2] = tz.o;
+                t.e[0] = tx.e; t.e[1] = ty.e; t.e[2] = tz.e;
+                t.n[0] = tx.n; t.n[1] = ty.n; t.n[2] = tz.n;
+                c.tiles.push_back(t);
+                c.max_nz = std::max(c.max_nz, tz.n);
+            }
+    for (auto& c : plan->classes) {
+        MVD_CUDA(cudaMalloc(&c.d_tiles, c.tiles.size() * sizeof(Tile)));
+        MVD_CUDA(cudaMemcpy(c.d_tiles, c.tiles.data(), c.tiles.size() * sizeof(Tile), cudaMemcpyHostToDevice));
+        plan->max_tile_elems = std::max(plan->max_tile_elems, tile_scratch_elems(c.b[0], c.b[1], c.b[2]));
+    }
+    return plan;
+}
+
+KernelSpectra::~KernelSpectra() {
+    for (auto* p : per_class)
+        if (p) cudaFree(p);
+}
+
+// ---- device ----------------------------------------------------------------------------
+static std::mutex g_dev_mutex;
+static std::map<int, std::unique_ptr<Device>> g_devices;
+
+Device& Device::get(int id) {
+    std::lock_guard<std::mutex> lk(g_dev_mutex);
+    auto it = g_devices.find(id);
+    if (it != g_devices.end()) {
+        MVD_CUDA(cudaSetDevice(id));
+        return *it->second;
+    }
+    int n = 0;
+    MVD_CUDA(cudaGetDeviceCount(&n));
+    if (id < 0 || id >= n) throw CudaError("invalid CUDA device " + std::to_string(id));
+    MVD_CUDA(cudaSetDevice(id));
+    std::unique_ptr<Device> d(new Device(id));
+    Device& ref = *d;
+    g_devices.emplace(id, std::move(d));
+    return ref;
+}
+
+Device::Device(int id) : id_(id) {
+    cudaDeviceProp prop;
+    MVD_CUDA(cudaGetDeviceProperties(&prop, id));
+    if (prop.major < 10)
+        throw CudaError(std::string("libmvdecon is built for sm_100a (B200); device '") + prop.name + "' is sm_" +
+                        std::to_string(prop.major) + std::to_string(prop.minor));
+    MVD_CUDA(configure_conv_kernels());
+    const double two_pi = 6.283185307179586476925286766559;
+    for (int l = 0; l < 11; ++l) {
+        const int n = 1 << l;
+        std::vector<float2> h(n);
+        for (int i = 0; i < n; ++i) {
+            const double a = -two_pi * (double)i / (double)n;
+            h[i] = make_float2((float)std::cos(a), (float)std::sin(a));
+        }
+        float2* d = nullptr;
+        MVD_CUDA(cudaMalloc(&d, n * sizeof(float2)));
+        MVD_CUDA(cudaMemcpy(d, h.data(), n * sizeof(float2), cudaMemcpyHostToDevice));
+        tw_.t[l] = d;
+    }
+    size_t mb = 256;
+    if (const char* s = std::getenv("MVD_SCRATCH_MB")) {
+        const long v = std::atol(s);
+        if (v > 0) mb = (size_t)v;
+    }
+    scratch_budget_ = mb << 20;
+}
+
+void Scratch::reserve(size_t n) {
+    if (n <= elems) return;
+    if (data) MVD_CUDA(cudaFree(data));
+    data = nullptr;
+    elems = 0;
+    MVD_CUDA(cudaMalloc(&data, n * sizeof(float2)));
+    elems = n;
+}
+Scratch::~Scratch() {
+    if (data) cudaFree(data);
+}
+
+// ---- spectra ---------------------------------------------------------------------------
+std::unique_ptr<KernelSpectra> build_spectra(Device& dev, const ConvPlan& plan, const float* kernel_host, cudaStream_t st) {
+    auto spec = std::make_unique<KernelSpectra>();
+    const int* k = plan.k;
+    double sum = 0.0;
+    for (size_t i = 0; i < (size_t)k[0] * k[1] * k[2]; ++i) sum += kernel_host[i];
+    spec->kernel_sum = sum;
+    for (const auto& c : plan.classes) {
+        const int bx = c.b[0], by = c.b[1], bz = c.b[2];
+        // kernel centre (k/2) moved to index 0, wrapped circularly (FFTConvolution.java:506-516)
+        std::vector<float> kc((size_t)bx * by * bz, 0.f);
+        for (int z = 0; z < k[2]; ++z)
+            for (int y = 0; y < k[1]; ++y)
+                for (int x = 0; x < k[0]; ++x) {
+                    const int px = ((x - k[0] / 2) % bx + bx) % bx, py = ((y - k[1] / 2) % by + by) % by,
+                              pz = ((z - k[2] / 2) % bz + bz) % bz;
+                    kc[px + (size_t)bx * (py + (size_t)by * pz)] = kernel_host[x + (size_t)k[0] * (y + (size_t)k[1] * z)];
+                }
+        float* d_kc = nullptr;
+        Tile* d_tile = nullptr;
+        float2* d_spec = nullptr;
+        MVD_CUDA(cudaMalloc(&d_spec, tile_scratch_elems(bx, by, bz) * sizeof(float2)));
+        spec->per_class.push_back(d_spec);
+        MVD_CUDA(cudaMalloc(&d_kc, kc.size() * sizeof(float)));
+        MVD_CUDA(cudaMalloc(&d_tile, sizeof(Tile)));
+        Tile t;
+        for (int d = 0; d < 3; ++d) { t.o[d] = 0; t.e[d] = 0; t.n[d] = c.b[d]; }
+        MVD_CUDA(cudaMemcpyAsync(d_kc, kc.data(), kc.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+        MVD_CUDA(cudaMemcpyAsync(d_tile, &t, sizeof(Tile), cudaMemcpyHostToDevice, st));
+        Volume v;
+        v.data = d_kc;
+        for (int d = 0; d < 3; ++d) { v.dim[d] = c.b[d]; v.off[d] = 0; v.gmin[d] = 0; v.gdim[d] = c.b[d]; }
+        v.ext = EXT_ZERO;
+        v.ext_value = 0.f;
+        MVD_CUDA(launch_fwd_xy(bx, by, bz, v, d_tile, 1, d_spec, dev.twiddles(), st));
+        // the forward x untangle omits its 1/2 for the image AND for this kernel spectrum (factor 4),
+        // the unnormalised inverse contributes bx*by*bz
+        const float scale = (float)(1.0 / (4.0 * (double)bx * (double)by * (double)bz));
+        MVD_CUDA(launch_z_pass(bx, by, bz, 0, d_spec, nullptr, d_tile, 1, scale, dev.twiddles(), st));
+        g_kernel_launches += 2;
+        MVD_CUDA(cudaStreamSynchronize(st));
+        cudaFree(d_kc);
+        cudaFree(d_tile);
+    }
+    return spec;
+}
+
+// ---- convolution -----------------------------------------------------------------------
+void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spec, const Volume& src, int epilogue,
+                     const EpilogueArgs& ep, Scratch& scratch, cudaStream_t st) {
+    for (size_t ci = 0; ci < plan.classes.size(); ++ci) {
+        const TileClass& c = plan.classes[ci];
+        const int bx = c.b[0], by = c.b[1], bz = c.b[2];
+        const size_t te = tile_scratch_elems(bx, by, bz);
+        const int n = (int)c.tiles.size();
+        int batch = (int)std::max<size_t>(1, dev.scratch_budget_bytes() / (te * sizeof(float2)));
+        batch = std::min(batch, n);
+        scratch.reserve((size_t)batch * te);
+        for (int s = 0; s < n; s += batch) {
+            const int cnt = std::min(batch, n - s);
+            MVD_CUDA(launch_fwd_xy(bx, by, bz, src, c.d_tiles + s, cnt, scratch.data, dev.twiddles(), st));
+            MVD_CUDA(launch_z_pass(bx, by, bz, 1, scratch.data, spec.per_class[ci], c.d_tiles + s, cnt, 1.f, dev.twiddles(), st));
+            MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, scratch.data, c.d_tiles + s, cnt, c.max_nz, ep, dev.twiddles(), st));
+            g_kernel_launches += 3;
+        }
+    }
+}
+
+}  // namespace mvd

@@ -1,0 +1,97 @@
+// Host side of the tiled convolution engine: tile planner, per-device resources,
+// kernel-spectrum construction and the batched launch sequence.
+#pragma once
+#include <cuda_runtime.h>
+#include <atomic>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "conv_kernels.h"
+#include "conv_types.h"
+
+namespace mvd {
+
+struct CudaError : std::runtime_error {
+    explicit CudaError(const std::string& s) : std::runtime_error(s) {}
+};
+void cuda_check(cudaError_t e, const char* what);
+#define MVD_CUDA(x) ::mvd::cuda_check((x), #x)
+
+extern std::atomic<long long> g_kernel_launches;
+
+// ---- planner ---------------------------------------------------------------------------
+struct AxisTile {
+    int b;  // FFT length of the window
+    int o;  // window origin (brick coordinates, may be negative)
+    int e;  // first output voxel
+    int n;  // number of output voxels
+};
+// Cover [0,n) with overlap-save windows for a kernel of length k whose centre sits at k/2.
+// Outputs of a window start `lo` voxels after its origin, lo = roundup(k-1-k/2, align).
+std::vector<AxisTile> plan_axis(int n, int k, int align, const int* sizes, int num_sizes);
+
+struct TileClass {
+    int b[3];
+    std::vector<Tile> tiles;
+    Tile* d_tiles = nullptr;  // device copy
+    int max_nz = 0;
+};
+
+struct ConvPlan {
+    int dim[3];
+    int k[3];
+    std::vector<TileClass> classes;
+    size_t max_tile_elems = 0;  // largest per-tile scratch (complex elements)
+    ~ConvPlan();
+    ConvPlan() = default;
+    ConvPlan(const ConvPlan&) = delete;
+    ConvPlan& operator=(const ConvPlan&) = delete;
+};
+// Builds the plan and uploads the tile lists to the current device.
+std::unique_ptr<ConvPlan> make_plan(const int dim[3], const int k[3]);
+bool same_plan(const ConvPlan& p, const int dim[3], const int k[3]);
+
+// Spectra of one kernel for every tile class of a plan (resident in HBM).
+struct KernelSpectra {
+    std::vector<float2*> per_class;
+    double kernel_sum = 0.0;
+    ~KernelSpectra();
+    KernelSpectra() = default;
+    KernelSpectra(const KernelSpectra&) = delete;
+    KernelSpectra& operator=(const KernelSpectra&) = delete;
+};
+
+// ---- per-device resources --------------------------------------------------------------
+class Device {
+public:
+    static Device& get(int id);  // throws CudaError
+    int id() const { return id_; }
+    const TwiddleTables& twiddles() const { return tw_; }
+    size_t scratch_budget_bytes() const { return scratch_budget_; }
+    std::mutex legacy_mutex;  // serialises the drop-in symbol per device
+
+private:
+    explicit Device(int id);
+    int id_;
+    TwiddleTables tw_{};
+    size_t scratch_budget_;
+};
+
+// Scratch for the tile batches of one stream.
+struct Scratch {
+    float2* data = nullptr;
+    size_t elems = 0;
+    void reserve(size_t n);
+    ~Scratch();
+};
+
+std::unique_ptr<KernelSpectra> build_spectra(Device& dev, const ConvPlan& plan, const float* kernel_host, cudaStream_t st);
+
+// out-of-place tiled convolution of `src`; the epilogue decides what is stored.
+void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spec, const Volume& src, int epilogue,
+                     const EpilogueArgs& ep, Scratch& scratch, cudaStream_t st);
+
+}  // namespace mvd

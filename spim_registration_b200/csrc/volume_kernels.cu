@@ -1,0 +1,86 @@
+#include "volume_kernels.h"
+
+namespace mvd {
+
+static constexpr int kSMs = 148;
+
+__global__ void fill_kernel(float* __restrict__ p, size_t n, float v) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) p[i] = v;
+}
+
+cudaError_t launch_fill(float* p, size_t n, float v, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const int blocks = (int)((n + 255) / 256 < (size_t)(kSMs * 8) ? (n + 255) / 256 : (size_t)(kSMs * 8));
+    fill_kernel<<<blocks, 256, 0, st>>>(p, n, v);
+    return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) first_iteration_kernel(ViewPtrs views, size_t n, double* __restrict__ d_sum,
+                                                              unsigned long long* __restrict__ d_count) {
+    __shared__ double s_sum[8];
+    __shared__ unsigned long long s_cnt[8];
+    double lsum = 0.0;
+    unsigned long long lcnt = 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        double sum = 0.0;
+        int count = 0;
+        for (int v = 0; v < views.n; ++v) {
+            const double x = (double)__ldg(views.img[v] + i);
+            if (x > 0) { sum += x; ++count; }
+        }
+        if (count > 0) { lsum += sum / (double)count; ++lcnt; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lsum += __shfl_xor_sync(0xffffffffu, lsum, o);
+        lcnt += __shfl_xor_sync(0xffffffffu, lcnt, o);
+    }
+    if ((threadIdx.x & 31) == 0) { s_sum[threadIdx.x >> 5] = lsum; s_cnt[threadIdx.x >> 5] = lcnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        unsigned long long c = 0;
+        for (int i = 0; i < 8; ++i) { s += s_sum[i]; c += s_cnt[i]; }
+        atomicAdd(d_sum, s);
+        atomicAdd(d_count, c);
+    }
+}
+
+cudaError_t launch_first_iteration_sums(const ViewPtrs& views, size_t n, double* d_sum, unsigned long long* d_count, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const int blocks = (int)((n + 255) / 256 < (size_t)(kSMs * 8) ? (n + 255) / 256 : (size_t)(kSMs * 8));
+    first_iteration_kernel<<<blocks, 256, 0, st>>>(views, n, d_sum, d_count);
+    return cudaGetLastError();
+}
+
+struct Int3 { int v[3]; };
+
+__global__ void __launch_bounds__(256) mask_kernel(ViewPtrs views, Int3 brick, float* __restrict__ psi, Int3 pdim, Int3 poff) {
+    const size_t n = (size_t)brick.v[0] * brick.v[1] * brick.v[2];
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        bool any = false;
+        for (int v = 0; v < views.n; ++v) any |= __ldg(views.img[v] + i) > 0.f;
+        if (!any) {
+            const int x = (int)(i % brick.v[0]);
+            const size_t r = i / brick.v[0];
+            const int y = (int)(r % brick.v[1]), z = (int)(r / brick.v[1]);
+            psi[(x + poff.v[0]) + (size_t)pdim.v[0] * ((y + poff.v[1]) + (size_t)pdim.v[1] * (z + poff.v[2]))] = 0.f;
+        }
+    }
+}
+
+cudaError_t launch_mask_never_updated(const ViewPtrs& views, const int brick[3], float* psi, const int psi_dim[3], const int psi_off[3],
+                                      cudaStream_t st) {
+    const size_t n = (size_t)brick[0] * brick[1] * brick[2];
+    if (n == 0) return cudaSuccess;
+    const int blocks = (int)((n + 255) / 256 < (size_t)(kSMs * 8) ? (n + 255) / 256 : (size_t)(kSMs * 8));
+    Int3 b, d, o;
+    for (int i = 0; i < 3; ++i) { b.v[i] = brick[i]; d.v[i] = psi_dim[i]; o.v[i] = psi_off[i]; }
+    mask_kernel<<<blocks, 256, 0, st>>>(views, b, psi, d, o);
+    return cudaGetLastError();
+}
+
+}  // namespace mvd

@@ -1,0 +1,21 @@
+// Streaming per-voxel kernels around the convolution engine.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace mvd {
+
+static constexpr int kMaxViews = 64;
+struct ViewPtrs {
+    const float* img[kMaxViews];
+    int n;
+};
+
+cudaError_t launch_fill(float* p, size_t n, float v, cudaStream_t st);
+// FirstIteration.java:103-135: per voxel mean of the views with img > 0; accumulates the sum of
+// those means (double) and the number of voxels with at least one view.
+cudaError_t launch_first_iteration_sums(const ViewPtrs& views, size_t n, double* d_sum, unsigned long long* d_count, cudaStream_t st);
+// MVDeconvolution.java:180-187: psi = 0 where no view has data. psi is a ghosted array.
+cudaError_t launch_mask_never_updated(const ViewPtrs& views, const int brick[3], float* psi, const int psi_dim[3], const int psi_off[3],
+                                      cudaStream_t st);
+
+}  // namespace mvd
