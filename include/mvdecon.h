@@ -143,6 +143,11 @@ int mvdMaskNeverUpdated(mvdContext* ctx);
 int mvdConvolve(int device, const float* src, const int dim[3], const float* kernel, const int kernelDim[3], int extMode,
                 float extValue, float* out);
 
+/* Same with device-resident src/out (dSrc != dOut) on the given stream (cudaStream_t as void*,
+ * NULL = legacy default stream); the kernel stays a host array.  Synchronises before returning. */
+int mvdConvolveDevice(int device, const float* dSrc, const int dim[3], const float* kernel, const int kernelDim[3], int extMode,
+                      float extValue, float* dOut, void* cudaStream);
+
 /* Tile plan chosen for (dim, kernelDim): writes up to maxTiles records of 12 ints
  * (window size b[3], window origin o[3], first output voxel e[3], output count n[3]) and returns
  * the tile count, or -1. */

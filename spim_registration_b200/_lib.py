@@ -46,6 +46,7 @@ PROTOTYPES = {
     "mvdArrayInfo": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), c_int_p, c_int_p]),
     "mvdMaskNeverUpdated": (C.c_int, [C.c_void_p]),
     "mvdConvolve": (C.c_int, [C.c_int, c_float_p, c_int_p, c_float_p, c_int_p, C.c_int, C.c_float, c_float_p]),
+    "mvdConvolveDevice": (C.c_int, [C.c_int, C.c_void_p, c_int_p, c_float_p, c_int_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
     "mvdPlanTiles": (C.c_int, [c_int_p, c_int_p, c_int_p, C.c_int]),
     "mvdDivideIntoBlocks": (C.c_longlong, [c_ll_p, c_ll_p, c_ll_p, C.c_int, c_ll_p, C.c_longlong]),
     "mvdKernelLaunchCount": (C.c_longlong, []),

@@ -460,6 +460,24 @@ extern "C" int mvdMaskNeverUpdated(mvdContext* c) {
 
 // ---- stand-alone convolution ---------------------------------------------------------------
 // dims in (x,y,z); src/out host pointers.
+static void convolve_device(Device& dev, const float* d_src, const int dim[3], const float* kernel, const int k[3], int ext,
+                            float ext_value, float* d_out, cudaStream_t st) {
+    auto plan = make_plan(dim, k);
+    auto spec = build_spectra(dev, *plan, kernel, st);
+    Volume v;
+    v.data = d_src;
+    for (int d = 0; d < 3; ++d) { v.dim[d] = dim[d]; v.off[d] = 0; v.gmin[d] = 0; v.gdim[d] = dim[d]; }
+    v.ext = ext;
+    v.ext_value = ext_value;
+    EpilogueArgs ep;
+    std::memset(&ep, 0, sizeof(ep));
+    ep.out = d_out;
+    for (int d = 0; d < 3; ++d) { ep.out_dim[d] = dim[d]; ep.out_off[d] = 0; ep.aux_dim[d] = dim[d]; }
+    Scratch scratch;
+    run_convolution(dev, *plan, *spec, v, EPI_STORE, ep, scratch, st);
+    MVD_CUDA(cudaStreamSynchronize(st));  // plan, spectra and scratch die with this frame
+}
+
 static void convolve_host(int device, const float* src, const int dim[3], const float* kernel, const int k[3], int ext, float ext_value,
                           float* out) {
     Device& dev = Device::get(device);
@@ -474,21 +492,20 @@ static void convolve_host(int device, const float* src, const int dim[3], const 
     MVD_CUDA(cudaMalloc(&d_src, n * sizeof(float)));
     MVD_CUDA(cudaMalloc(&d_out, n * sizeof(float)));
     MVD_CUDA(cudaMemcpyAsync(d_src, src, n * sizeof(float), cudaMemcpyHostToDevice, st));
-    auto plan = make_plan(dim, k);
-    auto spec = build_spectra(dev, *plan, kernel, st);
-    Volume v;
-    v.data = d_src;
-    for (int d = 0; d < 3; ++d) { v.dim[d] = dim[d]; v.off[d] = 0; v.gmin[d] = 0; v.gdim[d] = dim[d]; }
-    v.ext = ext;
-    v.ext_value = ext_value;
-    EpilogueArgs ep;
-    std::memset(&ep, 0, sizeof(ep));
-    ep.out = d_out;
-    for (int d = 0; d < 3; ++d) { ep.out_dim[d] = dim[d]; ep.out_off[d] = 0; ep.aux_dim[d] = dim[d]; }
-    Scratch scratch;
-    run_convolution(dev, *plan, *spec, v, EPI_STORE, ep, scratch, st);
+    convolve_device(dev, d_src, dim, kernel, k, ext, ext_value, d_out, st);
     MVD_CUDA(cudaMemcpyAsync(out, d_out, n * sizeof(float), cudaMemcpyDeviceToHost, st));
     MVD_CUDA(cudaStreamSynchronize(st));
+}
+
+extern "C" int mvdConvolveDevice(int device, const float* dSrc, const int dim[3], const float* kernel, const int kernelDim[3],
+                                 int extMode, float extValue, float* dOut, void* cudaStream) {
+    return guarded([&] {
+        require(dSrc && dim && kernel && kernelDim && dOut, "mvdConvolveDevice: null argument");
+        require(extMode >= 0 && extMode <= 2, "mvdConvolveDevice: bad extension mode");
+        require(dSrc != dOut, "mvdConvolveDevice: in-place convolution is not possible (tiles overlap)");
+        Device& dev = Device::get(device);
+        convolve_device(dev, dSrc, dim, kernel, kernelDim, extMode, extValue, dOut, (cudaStream_t)cudaStream);
+    });
 }
 
 extern "C" int mvdConvolve(int device, const float* src, const int dim[3], const float* kernel, const int kernelDim[3], int extMode,

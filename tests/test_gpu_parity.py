@@ -1,0 +1,227 @@
+"""GPU parity tests: CUDA path through the C ABI vs the CPU oracle (oracle/oracle_np.py).
+
+Tolerance: relative L2 <= 1e-4 after the configured iterations (BASELINE.json north_star);
+single convolutions are held to 2e-6.  Integer work (tiling, copy/paste maps) is bit-exact.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+CONV_TOL = 2e-6
+LOOP_TOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def m():
+    import spim_registration_b200 as mod
+    mod.load()
+    devs = mod.CUDATools.queryCUDADetails()
+    assert devs, "no CUDA device"
+    return mod
+
+
+@pytest.fixture(scope="module")
+def o():
+    import oracle_np
+    return oracle_np
+
+
+def _rand(shape, seed):
+    return (np.random.default_rng(seed).random(shape, dtype=np.float32) + np.float32(0.1))
+
+
+def _kernel(shape, seed):
+    k = np.random.default_rng(seed).random(shape, dtype=np.float32)
+    return (k / k.sum()).astype(np.float32)
+
+
+@pytest.mark.parametrize("shape,ks", [
+    ((20, 24, 28), (3, 5, 7)),       # smaller than one window
+    ((33, 37, 41), (4, 6, 8)),       # ragged, even kernel
+    ((5, 6, 7), (15, 15, 15)),       # volume smaller than the kernel halo: repeated reflection
+    ((1, 40, 40), (1, 9, 9)),        # degenerate z
+    ((64, 64, 64), (15, 15, 15)),
+    ((70, 130, 150), (15, 11, 9)),   # several windows per axis, mixed window sizes
+    ((96, 200, 260), (31, 31, 31)),
+])
+@pytest.mark.parametrize("mode", ["zero", "const", "mirror"])
+def test_convolution_matches_oracle(m, o, shape, ks, mode):
+    f, k = _rand(shape, 1), _kernel(ks, 2)
+    ref = o.convolve_extended(f, k, mode, 1.0)
+    got = m.convolve(f, k, mode, 1.0)
+    assert rel_l2(got, ref) <= CONV_TOL
+
+
+def test_delta_lands_kernel_unflipped(m):
+    """conv, not correlation (SURVEY 8c caveat): a delta at p puts kernel[j] at p + j - K//2."""
+    k = np.arange(1, 3 * 5 * 7 + 1, dtype=np.float32).reshape(3, 5, 7)
+    d = np.zeros((21, 23, 25), np.float32)
+    d[10, 11, 12] = 1
+    got = m.convolve(d, k, "zero")
+    np.testing.assert_allclose(got[10 - 1:10 + 2, 11 - 2:11 + 3, 12 - 3:12 + 4], k, rtol=0, atol=2e-4)
+    got[10 - 1:10 + 2, 11 - 2:11 + 3, 12 - 3:12 + 4] = 0
+    assert np.abs(got).max() < 2e-4
+
+
+def test_linearity(m):
+    f, g, k = _rand((40, 44, 48), 3), _rand((40, 44, 48), 4), _kernel((7, 7, 7), 5)
+    a = m.convolve(f + 2 * g, k, "zero")
+    b = m.convolve(f, k, "zero") + 2 * m.convolve(g, k, "zero")
+    assert rel_l2(a, b) <= CONV_TOL
+
+
+def test_legacy_symbol_blockwise_equals_whole_volume(m, o):
+    """Tiling invariance (SURVEY 8a invariant i): reference-style blocks through the drop-in
+    symbol == whole-volume convolution, for both out-of-bounds rules."""
+    f, k = _rand((50, 70, 90), 6), _kernel((9, 11, 13), 7)
+    cuda = m.CUDAFourierConvolution()
+    for mode, val in (("mirror", 0.0), ("const", 1.0)):
+        whole = m.convolve(f, k, mode, val)
+        blocks = m.BlockGeneratorFixedSizePrecise([64, 48, 40]).divideIntoBlocks(list(f.shape[::-1]), list(k.shape[::-1]))
+        out = np.zeros_like(f)
+        for b in blocks:
+            data = o.copy_block(f, b.as_dict(), mode, val)  # Block.copyBlock from the extended source
+            kk = k.copy()
+            cuda.convolution3DfftCUDAInPlace(data, data.shape, kk, kk.shape, 0)  # dims (z,y,x) like the reference
+            b.pasteBlock(out, data)
+        assert rel_l2(out, whole) <= CONV_TOL
+        assert rel_l2(out, o.convolve_extended(f, k, mode, val)) <= CONV_TOL
+
+
+def test_legacy_device_queries(m, lib):
+    n = lib.getNumDevicesCUDA()
+    assert n >= 1
+    assert lib.getCUDAcomputeCapabilityMajorVersion(0) == 10
+    assert lib.getMemDeviceCUDA(0) > 100 * (1 << 30)
+    assert 0 < lib.getFreeMemDeviceCUDA(0) <= lib.getMemDeviceCUDA(0)
+    name = C.create_string_buffer(256)
+    lib.getNameDeviceCUDA(0, name)
+    assert b"B200" in name.value
+
+
+def test_legacy_failure_leaves_block_untouched(m, lib):
+    import spim_registration_b200._lib as L
+    f = _rand((8, 8, 8), 8)
+    before = f.copy()
+    k = _kernel((3, 3, 3), 9)
+    dim = (C.c_int * 3)(8, 8, 8)
+    kd = (C.c_int * 3)(3, 3, 3)
+    lib.convolution3DfftCUDAInPlace(f.ctypes.data_as(L.c_float_p), dim, k.ctypes.data_as(L.c_float_p), kd, 99)  # bad device
+    code, msg = L.last_error()
+    assert code != 0 and "device" in msg
+    np.testing.assert_array_equal(f, before)
+    kbig = np.ones((3, 3, 200), np.float32)  # x kernel wider than the largest xy window
+    kd3 = (C.c_int * 3)(3, 3, 200)
+    lib.convolution3DfftCUDAInPlace(f.ctypes.data_as(L.c_float_p), dim, kbig.ctypes.data_as(L.c_float_p), kd3, 0)
+    code, msg = L.last_error()
+    assert code != 0 and "window" in msg
+    np.testing.assert_array_equal(f, before)
+
+
+def _views(m, imgs, weights, psfs):
+    inp = m.MVDeconInput()
+    for img, w, p in zip(imgs, weights, psfs):
+        inp.add(m.MVDeconFFT(img, w, p))
+    return inp
+
+
+def _dataset(o, shape, V, ksize, seed=0):
+    from spim_registration_b200 import synthetic
+    return synthetic.make_dataset(shape, V, ksize, seed=synthetic.SEED0 + seed, convolve=lambda f, k: o.convolve_extended(f, k, "mirror"))
+
+
+@pytest.mark.parametrize("psftype", ["EFFICIENT_BAYESIAN", "OPTIMIZATION_I", "OPTIMIZATION_II", "INDEPENDENT"])
+def test_kernel_preparation_matches_oracle(m, o, psftype):
+    from spim_registration_b200 import synthetic
+    psfs = synthetic.make_psfs(3, (9, 7, 11), extracted=True)
+    inp = _views(m, [np.ones((4, 4, 4), np.float32)] * 3, [1.0] * 3, psfs)
+    inp.init(psftype, 8)
+    k1, k2 = o.init_kernels(psfs, psftype, 8)
+    for v, view in enumerate(inp.getViews()):
+        np.testing.assert_array_equal(view.getKernel1(), k1[v])  # host arithmetic only: bit-exact
+        assert rel_l2(view.getKernel2(), k2[v]) <= 5e-6
+
+
+@pytest.mark.parametrize("psftype,lam,use_weights", [
+    ("EFFICIENT_BAYESIAN", 0.006, False),
+    ("OPTIMIZATION_I", 0.006, True),
+    ("OPTIMIZATION_II", 0.0, False),
+    ("INDEPENDENT", 0.006, True),
+])
+def test_loop_matches_oracle(m, o, psftype, lam, use_weights):
+    from spim_registration_b200 import synthetic
+    shape, V, iters = (40, 52, 60), 3, 5
+    ds = _dataset(o, shape, V, (9, 9, 9))
+    weights = synthetic.blending_weights(shape, V) if use_weights else [np.float32(1.0 / V)] * V
+    k1, k2 = o.init_kernels(ds["psfs"], psftype, 8)
+    ref, stats, avg = o.run_deconvolution(ds["imgs"], weights, k1, k2, iters, lam)
+    inp = _views(m, ds["imgs"], [w if use_weights else float(w) for w in weights], ds["psfs"])
+    dec = m.MVDeconvolution(inp, psftype, iters, lam)
+    assert abs(dec.avg - avg) <= 1e-12 * abs(avg)
+    assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
+    rs = np.array([[s for s, _ in row] for row in stats])
+    rm = np.array([[x for _, x in row] for row in stats])
+    np.testing.assert_allclose(dec.sumChange, rs, rtol=2e-3)
+    np.testing.assert_allclose(dec.maxChange, rm, rtol=5e-3)
+    assert (dec.getPsi()[ref == 0] == 0).all()  # never-updated voxels masked (MVDeconvolution.java:180-187)
+
+
+def test_golden_fixture(m):
+    """CUDA path vs the frozen oracle output (tests/golden/make_golden.py)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "loop_3view_32.npz"))
+    V = int(g["num_views"])
+    inp = m.MVDeconInput()
+    for v in range(V):
+        view = m.MVDeconFFT(g["img%d" % v], g["weight%d" % v], g["k1_%d" % v])
+        view.kernel2 = g["k2_%d" % v]
+        inp.add(view)
+    dec = m.MVDeconvolution(inp, str(g["psftype"]), int(g["iterations"]), float(g["lam"]), prepared=True)
+    assert rel_l2(dec.getPsi(), g["psi"]) <= LOOP_TOL
+
+
+def test_fixed_point_independent(m, o):
+    """SURVEY 8a invariant ii: with sum(kernel1) = 1 and img = conv1(truth), psi = truth is a
+    fixed point of the INDEPENDENT update (lambda = 0, weight 1)."""
+    from spim_registration_b200 import synthetic
+    shape = (36, 40, 44)
+    truth = synthetic.make_truth(shape, "blob", 5) + np.float32(0.05)
+    k = _kernel((7, 7, 7), 11)
+    img = o.convolve_extended(truth, k, "mirror")
+    view = m.MVDeconFFT(img, 1.0, k)
+    view.kernel2 = m.MVDeconFFT.computeInvertedKernel(k)
+    inp = m.MVDeconInput()
+    inp.add(view)
+    dec = m.MVDeconvolution(inp, "INDEPENDENT", 3, 0.0, initialImage=truth, prepared=True)
+    # conv2 of a quotient that is 1 inside is 1 only away from the border, where ext(q)=1 anyway
+    assert rel_l2(dec.getPsi(), truth) <= 2e-5
+
+
+def test_no_data_and_constant_weight_edge_cases(m, o):
+    shape = (24, 28, 36)
+    rng = np.random.default_rng(3)
+    imgs = [rng.random(shape, dtype=np.float32), np.zeros(shape, np.float32)]  # second view: no data at all
+    imgs[0][:, :, :5] = 0
+    psfs = [_kernel((5, 5, 5), 1), _kernel((5, 5, 5), 2)]
+    k1, k2 = o.init_kernels(psfs, "INDEPENDENT", 8)
+    ref, stats, avg = o.run_deconvolution(imgs, [np.float32(1.0), np.float32(0.3)], k1, k2, 3, 0.006)
+    dec = m.MVDeconvolution(_views(m, imgs, [1.0, 0.3], psfs), "INDEPENDENT", 3, 0.006)
+    assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
+    assert (dec.getPsi()[:, :, :5] == 0).all()
+
+
+def test_config1_full_size(m, o):
+    """BASELINE.json configs[0]: 3 views 128^3, Gaussian PSFs 15^3, efficient Bayesian, 10 iterations."""
+    from spim_registration_b200 import synthetic
+    shape, V, iters = (128, 128, 128), 3, 10
+    ds = _dataset(o, shape, V, (15, 15, 15), seed=1)
+    w = [np.float32(1.0 / V)] * V
+    k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
+    ref, stats, avg = o.run_deconvolution(ds["imgs"], w, k1, k2, iters, 0.006)
+    dec = m.MVDeconvolution(_views(m, ds["imgs"], [float(x) for x in w], ds["psfs"]), "EFFICIENT_BAYESIAN", iters, 0.006)
+    assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
