@@ -1,0 +1,406 @@
+#!/usr/bin/env python
+"""bench.py -- Gvoxel-iterations/s of the multi-view deconvolution loop on N B200s.
+
+  python bench.py --gpus N --steps K --warmup W [--impl reference] [--config 3]
+
+A step is one iteration of the loop (all views: conv1 -> quotient -> conv2 -> update) on the
+synthetic workload of BASELINE.json configs[2] (7 views, 1024x1024x512, PSF 31^3, efficient
+Bayesian), the configuration the north_star target is quoted on; it fits one GPU.  One JSON line
+is printed by rank 0 (see the task contract).  `--impl reference` times the CPU port of the
+reference's CPU path (oracle/cpu_baseline.py) on a bounded sample of the same workload.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+CONFIGS = {
+    # shape is (z, y, x)
+    1: dict(name="cfg1: 3-view 128^3 blob volume, Gaussian PSF 15^3, efficient Bayesian", views=3, shape=(128, 128, 128), k=15,
+            psftype="EFFICIENT_BAYESIAN", kind="blob", extracted=False, dense_weights=False),
+    2: dict(name="cfg2: 6-view 512x512x256 bead phantom, extracted PSF 31^3, OptimizationII", views=6, shape=(256, 512, 512), k=31,
+            psftype="OPTIMIZATION_II", kind="bead", extracted=True, dense_weights=False),
+    3: dict(name="cfg3: 7-view 1024x1024x512 volume, PSF 31^3, efficient Bayesian, dense blending weights", views=7,
+            shape=(512, 1024, 1024), k=31, psftype="EFFICIENT_BAYESIAN", kind="blob", extracted=False, dense_weights=True),
+    4: dict(name="cfg4: 6-view 1024x1024x512 independent RL with per-view weight images", views=6, shape=(512, 1024, 1024), k=31,
+            psftype="INDEPENDENT", kind="blob", extracted=False, dense_weights=True),
+    # debugging size
+    0: dict(name="cfg0: 3-view 96x160x192 debug volume, PSF 15^3", views=3, shape=(96, 160, 192), k=15,
+            psftype="EFFICIENT_BAYESIAN", kind="blob", extracted=False, dense_weights=True),
+}
+LAMBDA = 0.006
+ALG_BYTES_PER_VOXEL_VIEW = {True: 36.0, False: 32.0}  # SURVEY.md 8d / BASELINE.md section 3
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.lines, self.proc, self.idx = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None, reasons=sorted(reasons),
+                    samples=len(sm))
+
+
+# ------------------------------------------------------------------------------------------
+def prepare_kernels(cfg):
+    """PSFs -> kernel1/kernel2 through the host mirror of MVDeconFFT.init (device convolutions)."""
+    import spim_registration_b200 as m
+    from spim_registration_b200 import synthetic
+    psfs = synthetic.make_psfs(cfg["views"], (cfg["k"],) * 3, cfg["extracted"])
+    inp = m.MVDeconInput()
+    dummy = np.ones((2, 2, 2), np.float32)
+    for p in psfs:
+        inp.add(m.MVDeconFFT(dummy, 1.0, p, deviceList=(local_device(),)))
+    inp.init(cfg["psftype"], 8)
+    return psfs, [v.getKernel1() for v in inp.getViews()], [v.getKernel2() for v in inp.getViews()]
+
+
+def local_device():
+    return int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def device_convolve(lib, t_src, kernel, mode, value=0.0):
+    import torch
+    from spim_registration_b200 import _lib as L
+    out = torch.empty_like(t_src)
+    k = np.ascontiguousarray(kernel, dtype=np.float32)
+    rc = lib.mvdConvolveDevice(t_src.device.index, C.c_void_p(t_src.data_ptr()), L.int3(tuple(t_src.shape)[::-1]),
+                               k.ctypes.data_as(L.c_float_p), L.int3(k.shape[::-1]), {"zero": 0, "const": 1, "mirror": 2}[mode],
+                               float(value), C.c_void_p(out.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    L.check(rc, "mvdConvolveDevice")
+    return out
+
+
+def gen_dataset_device(cfg, lib, psfs, sub=None):
+    """Synthetic views generated on the device (not timed, not the product): sparse sources blurred
+    into blobs/beads, blurred by every view's PSF, Poisson-like noise, a no-data slab per view,
+    cosine blending weights normalised over the views.  `sub` = (offset_zyx, dim_zyx) of a brick."""
+    import torch
+    from spim_registration_b200 import synthetic
+    dev = torch.device("cuda", local_device())
+    Z, Y, X = cfg["shape"]
+    g = torch.Generator(device=dev)
+    g.manual_seed(synthetic.SEED0 + 3)
+    dens = 1.0 / 4096 if cfg["kind"] == "blob" else 1.0 / 32768
+    src = (torch.rand((Z, Y, X), generator=g, device=dev) < dens).float() * (0.2 + 0.8 * torch.rand((Z, Y, X), generator=g, device=dev))
+    sig = 2.5 if cfg["kind"] == "blob" else 0.8
+    kb = synthetic.gaussian_psf((15, 15, 15), sig, sig, 0.0)
+    truth = device_convolve(lib, src, kb, "mirror") + 0.01
+    del src
+    imgs, weights = [], []
+    V = cfg["views"]
+    for v in range(V):
+        k = (psfs[v].astype(np.float64) / psfs[v].astype(np.float64).sum()).astype(np.float32)
+        b = device_convolve(lib, truth, k, "mirror")
+        g.manual_seed(synthetic.SEED0 + 17 * (v + 1))
+        b = b + torch.sqrt(torch.clamp(b, min=0) / 200.0) * torch.randn(b.shape, generator=g, device=dev)
+        b.clamp_(min=1e-4)
+        b /= b.max()
+        w = int(round(0.12 * X))
+        if v % 2 == 0:
+            b[:, :, :w] = 0
+        else:
+            b[:, :, X - w:] = 0
+        imgs.append(b)
+    del truth
+    if cfg["dense_weights"]:
+        def ramp(n, border, shift):
+            pos = torch.arange(n, device=dev, dtype=torch.float32) - shift
+            d = torch.minimum(pos, (n - 1) - pos) - border
+            rel = torch.clamp(d / 12.0, 0.0, 1.0)
+            return 0.5 * (torch.cos((1.0 - rel) * np.pi) + 1.0)
+        total = torch.zeros((Z, Y, X), device=dev)
+        for v in range(V):
+            shift = (v - (V - 1) / 2.0) * 0.05 * X
+            total += ramp(Z, 3, 0)[:, None, None] * ramp(Y, 8, 0)[None, :, None] * ramp(X, 8, shift)[None, None, :]
+        total.clamp_(min=1e-12)
+        for v in range(V):
+            shift = (v - (V - 1) / 2.0) * 0.05 * X
+            w = ramp(Z, 3, 0)[:, None, None] * ramp(Y, 8, 0)[None, :, None] * ramp(X, 8, shift)[None, None, :]
+            weights.append(torch.clamp(w / total, max=1.0).contiguous())
+        del total
+    else:
+        weights = [None] * V
+    if sub is not None:
+        (oz, oy, ox), (dz, dy, dx) = sub
+        imgs = [i[oz:oz + dz, oy:oy + dy, ox:ox + dx].contiguous() for i in imgs]
+        weights = [None if w is None else w[oz:oz + dz, oy:oy + dy, ox:ox + dx].contiguous() for w in weights]
+    torch.cuda.synchronize()
+    return imgs, weights
+
+
+# ------------------------------------------------------------------------------------------
+def run_ours(args, cfg):
+    import torch
+    import torch.distributed as dist
+    import spim_registration_b200 as m
+    from spim_registration_b200 import _lib as L
+    from spim_registration_b200.parallel import ShardedDeconvolution, brick_grid, brick_of
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    dev_index = local_device()
+    torch.cuda.set_device(dev_index)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", dev_index))
+    lib = m.load()
+    Z, Y, X = cfg["shape"]
+    dim_xyz = (X, Y, Z)
+    V = cfg["views"]
+    nvox = float(X) * Y * Z
+    psfs, k1, k2 = prepare_kernels(cfg)
+    grid = brick_grid(world, dim_xyz)
+    off, size, _ = brick_of(rank, grid, dim_xyz)
+    sub = None if world == 1 else (off[::-1], size[::-1])
+    imgs, weights = gen_dataset_device(cfg, lib, psfs, sub)
+    dz = dist if world > 1 else None
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident throughput (`value`) ------------------------------------------------
+    dec = ShardedDeconvolution(dim_xyz, imgs, weights, k1, k2, LAMBDA, dz, dev_index, grid=grid)
+    dec.init_psi_average()
+    if world > 1:
+        dec._exchange(0)
+    for _ in range(args.warmup):
+        dec.run_iterations(1)
+    barrier()
+    sampler = ClockSampler(dev_index)
+    if rank == 0:
+        sampler.start()
+    launches0 = dec.kernel_launches()
+    L.check(lib.mvdProfileStart(dec.ctx), "mvdProfileStart")
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    dec.run_iterations(args.steps)
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    clocks = sampler.stop() if rank == 0 else None
+    launches = dec.kernel_launches() - launches0
+    pms, pl, pb = (C.c_double * 3)(), (C.c_longlong * 3)(), (C.c_double * 3)()
+    L.check(lib.mvdProfileStop(dec.ctx, pms, pl, pb), "mvdProfileStop")
+    dec.close()
+    del dec
+    value = nvox * args.steps / (ms * 1e-3) / 1e9
+
+    # ---- end to end through the public API with host buffers (`e2e`) ---------------------------
+    h_imgs = [torch.empty(i.shape, dtype=torch.float32).pin_memory() for i in imgs]
+    for h, d in zip(h_imgs, imgs):
+        h.copy_(d)
+    h_w = [None if w is None else torch.empty(w.shape, dtype=torch.float32).pin_memory() for w in weights]
+    for h, d in zip(h_w, weights):
+        if h is not None:
+            h.copy_(d)
+    del imgs, weights
+    torch.cuda.empty_cache()
+    h_psi = torch.empty(size[::-1], dtype=torch.float32).pin_memory()
+    np_imgs = [h.numpy() for h in h_imgs]
+    np_w = [(1.0 / V) if h is None else h.numpy() for h in h_w]
+    h2d = sum(a.nbytes for a in np_imgs) + sum(a.nbytes for a in np_w if not np.isscalar(a))
+    d2h = h_psi.numpy().nbytes
+    barrier()
+    t0 = time.perf_counter()
+    dec = ShardedDeconvolution(dim_xyz, np_imgs, np_w, k1, k2, LAMBDA, dz, dev_index, grid=grid)  # H2D of every view
+    dec.init_psi_average()
+    if world > 1:
+        dec._exchange(0)
+    dec.run_iterations(args.steps)
+    dec.mask_never_updated()
+    dec.get_psi_brick(h_psi.numpy())  # D2H of the result
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_s.item())
+    dec.close()
+    e2e_value = nvox * args.steps / e2e_s / 1e9
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = peaks()
+    names = ("fwd_xy", "z_pass", "inv_xy")
+    kern = {names[i]: dict(ms=pms[i], launches=int(pl[i]), alg_gb=pb[i] / 1e9,
+                           gbs=(pb[i] / 1e9) / (pms[i] * 1e-3) if pms[i] > 0 else 0.0) for i in range(3)}
+    top = max(range(3), key=lambda i: pms[i])
+    achieved = kern[names[top]]["gbs"]
+    loop_bytes = ALG_BYTES_PER_VOXEL_VIEW[cfg["dense_weights"]] * V * nvox * args.steps / world
+    line = {
+        "metric": "Gvoxel-iterations/sec (all views)", "value": value, "unit": "Gvoxel-iterations/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfg["name"], "views": V, "volume_xyz": list(dim_xyz), "psf": cfg["k"], "iteration_type": cfg["psftype"],
+                   "lambda": LAMBDA, "step": "one iteration over all views", "brick_grid_xyz": list(grid),
+                   "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % ((2 * V + 2) * nvox * 4 / world / 1e9),
+                   "scratch_mb": int(os.environ.get("MVD_SCRATCH_MB", "256"))},
+        "roofline": {"bound": "hbm", "kernel": names[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "share_of_step": pms[top] / ms, "kernels": kern,
+                     "loop": {"alg_bytes_per_voxel_view_iteration": ALG_BYTES_PER_VOXEL_VIEW[cfg["dense_weights"]],
+                              "achieved": loop_bytes / 1e9 / (ms * 1e-3), "frac": loop_bytes / 1e9 / (ms * 1e-3) / peak,
+                              "frac_of_8TBs": loop_bytes / 1e9 / (ms * 1e-3) / 8000.0}},
+        "e2e": {"value": e2e_value, "unit": "Gvoxel-iterations/s", "h2d_bytes_per_step": h2d / args.steps,
+                "d2h_bytes_per_step": d2h / args.steps, "seconds": e2e_s,
+                "includes": "context creation, H2D of all views and weights (pinned), kernel spectra, psi init, %d iterations, mask, D2H of psi" % args.steps},
+        "gpu_launches": int(launches), "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_sample(cfg, k1, k2, budget_s=args.cpu_seconds)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------
+def cpu_sample(cfg, k1, k2, budget_s=20.0, steps=1):
+    """CPU port of the reference's CPU path (oracle/cpu_baseline.py) on a bounded sample: a crop of
+    the workload with the reference's 256^3 blocks (64^3 for tiny configs), all views, `steps`
+    iterations; throughput scaled per voxel.  numpy-generated inputs of the same statistics."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import cpu_baseline as cb
+    V = cfg["views"]
+    Z, Y, X = cfg["shape"]
+    cores = cb.host_threads()
+    block = [256, 256, 256] if min(cfg["shape"]) >= 256 else [64, 64, 64]
+    e = block[0] - cfg["k"] + 1
+    # sample = a whole number of effective blocks; grow while the estimated time fits the budget
+    crop = [min(n, e) for n in (Z, Y, X)]
+    rng = np.random.default_rng(7)
+    def make(c):
+        imgs = [(rng.random(c, dtype=np.float32) * 0.9 + 0.05) for _ in range(V)]
+        w = [np.full(c, 1.0 / V, np.float32) if cfg["dense_weights"] else np.float32(1.0 / V) for _ in range(V)]
+        return imgs, w
+    imgs, w = make(crop)
+    psi = np.full(crop, 0.3, np.float32)
+    _, t = cb.run_iterations(imgs, w, k1, k2, 1, LAMBDA, block, psi, cores)  # also warms the FFT plans
+    vox = float(np.prod(crop))
+    nblk = max(1, int(budget_s / max(t, 1e-3)))
+    if nblk >= 2:
+        mult = [1, 1, 1]
+        ax = 2
+        while np.prod(mult) * 2 <= nblk and any(crop[a] * mult[a] * 2 <= (Z, Y, X)[a] for a in range(3)):
+            for _ in range(3):
+                if crop[ax] * mult[ax] * 2 <= (Z, Y, X)[ax]:
+                    mult[ax] *= 2
+                    break
+                ax = (ax - 1) % 3
+            ax = (ax - 1) % 3
+        crop = [crop[a] * mult[a] for a in range(3)]
+        imgs, w = make(crop)
+        psi = np.full(crop, 0.3, np.float32)
+        _, t = cb.run_iterations(imgs, w, k1, k2, steps, LAMBDA, block, psi, cores)
+        vox = float(np.prod(crop)) * steps
+    return {"value": vox / t / 1e9, "unit": "Gvoxel-iterations/s", "cores": cores, "kind": "port",
+            "sample": "%d view(s), crop %dx%dx%d (xyz) of the workload in %d^3 blocks, %d iteration(s), %.1f s, scipy pocketfft float32 with %d workers"
+                      % (V, crop[2], crop[1], crop[0], block[0], steps, t, cores), "seconds": t}
+
+
+def run_reference(args, cfg):
+    """--impl reference: the CPU port on the host cores (rank 0 only)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_np as o
+    from spim_registration_b200 import synthetic
+    psfs = synthetic.make_psfs(cfg["views"], (cfg["k"],) * 3, cfg["extracted"])
+    k1, k2 = o.init_kernels(psfs, cfg["psftype"], 8)
+    per_step = max(5.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    vals, secs, sample = [], [], None
+    for i in range(args.warmup + args.steps):
+        r = cpu_sample(cfg, k1, k2, budget_s=per_step)
+        if i >= args.warmup:
+            vals.append(r["value"])
+            secs.append(r["seconds"])
+        sample = r
+    value = float(np.mean(vals))
+    Z, Y, X = cfg["shape"]
+    line = {"impl": "reference", "metric": "Gvoxel-iterations/sec (all views)", "value": value, "unit": "Gvoxel-iterations/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": float(X) * Y * Z / (value * 1e9) * 1e3, "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": cfg["name"], "views": cfg["views"], "volume_xyz": [X, Y, Z], "psf": cfg["k"],
+                       "iteration_type": cfg["psftype"], "lambda": LAMBDA, "step": "bounded sample of one iteration over all views, scaled per voxel"},
+            "cpu_baseline": {"value": value, "unit": "Gvoxel-iterations/s", "cores": sample["cores"], "kind": "port", "sample": sample["sample"]},
+            "e2e": {"value": value, "unit": "Gvoxel-iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=20.0)
+    args = ap.parse_args()
+    cfg = CONFIGS[args.config]
+    if args.impl == "reference":
+        run_reference(args, cfg)
+    else:
+        run_ours(args, cfg)
+
+
+if __name__ == "__main__":
+    main()

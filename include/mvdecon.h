@@ -129,6 +129,13 @@ int mvdStepQuotient(mvdContext* ctx, int view);
 int mvdStepUpdate(mvdContext* ctx, int view, int statSlot);
 int mvdGetStats(mvdContext* ctx, int firstSlot, int numSlots, double* sumChange, double* maxChange);
 
+/* Per-kernel timing with CUDA events on the context's stream, for bench.py's roofline: between
+ * Start and Stop every launch of the three convolution kernels is bracketed by an event pair.
+ * Stop returns, per kernel (0 fwd_xy, 1 z_pass, 2 inv_xy), the summed duration in ms, the launch
+ * count and the summed ALGORITHMIC bytes (DESIGN.md byte model). */
+int mvdProfileStart(mvdContext* ctx);
+int mvdProfileStop(mvdContext* ctx, double ms[3], long long launches[3], double bytes[3]);
+
 #define MVD_ARRAY_PSI 0
 #define MVD_ARRAY_QUOTIENT 1
 /* Device pointer and geometry of a ghosted array: dim = extent, off = index of brick voxel 0. */

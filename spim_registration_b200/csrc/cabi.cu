@@ -96,6 +96,7 @@ struct mvdContext {
     std::vector<ViewData> views;
     std::vector<std::unique_ptr<ConvPlan>> plans;
     Scratch scratch;
+    std::unique_ptr<Profiler> prof;
     double* d_sum = nullptr;
     unsigned int* d_max = nullptr;
     int stat_capacity = 0;
@@ -227,6 +228,7 @@ extern "C" int mvdDestroy(mvdContext* c) {
         }
         c->views.clear();
         c->plans.clear();
+        c->prof.reset();
         if (c->psi) cudaFree(c->psi);
         if (c->quot) cudaFree(c->quot);
         if (c->d_sum) cudaFree(c->d_sum);
@@ -358,7 +360,7 @@ static void step_quotient(mvdContext* c, int v) {
     const Volume src = c->ghosted_volume(c->psi, EXT_MIRROR_SINGLE, 0.f);
     EpilogueArgs ep = c->epilogue_base(c->quot);
     ep.img = vd.img;
-    run_convolution(*c->dev, *c->plans[vd.plan1], *vd.spec1, src, EPI_QUOTIENT, ep, c->scratch, c->stream);
+    run_convolution(*c->dev, *c->plans[vd.plan1], *vd.spec1, src, EPI_QUOTIENT, ep, c->scratch, c->stream, c->prof.get());
 }
 
 static void step_update(mvdContext* c, int v, int slot) {
@@ -373,7 +375,7 @@ static void step_update(mvdContext* c, int v, int slot) {
     ep.weight_const = vd.weight_const;
     ep.sum_change = c->d_sum + slot;
     ep.max_change_bits = c->d_max + slot;
-    run_convolution(*c->dev, *c->plans[vd.plan2], *vd.spec2, src, EPI_UPDATE, ep, c->scratch, c->stream);
+    run_convolution(*c->dev, *c->plans[vd.plan2], *vd.spec2, src, EPI_UPDATE, ep, c->scratch, c->stream, c->prof.get());
 }
 
 static void read_stats(mvdContext* c, int first, int n, double* sum, double* mx) {
@@ -434,6 +436,22 @@ extern "C" int mvdGetStats(mvdContext* c, int firstSlot, int numSlots, double* s
         require(c, "mvdGetStats: null context");
         c->activate();
         read_stats(c, firstSlot, numSlots, sumChange, maxChange);
+    });
+}
+
+extern "C" int mvdProfileStart(mvdContext* c) {
+    return guarded([&] {
+        require(c, "mvdProfileStart: null context");
+        c->prof.reset(new Profiler);
+    });
+}
+
+extern "C" int mvdProfileStop(mvdContext* c, double ms[3], long long launches[3], double bytes[3]) {
+    return guarded([&] {
+        require(c && c->prof && ms && launches && bytes, "mvdProfileStop: profiling not started");
+        c->activate();
+        c->prof->collect(ms, launches, bytes);
+        c->prof.reset();
     });
 }
 
@@ -523,7 +541,7 @@ extern "C" int mvdPlanTiles(const int dim[3], const int kernelDim[3], int* out, 
         require(dim && kernelDim, "mvdPlanTiles: null argument");
         static const int xy[] = {32, 64, 128};
         static const int zs[] = {16, 32, 64, 128, 256, 512};
-        std::vector<AxisTile> ax[3] = {plan_axis(dim[0], kernelDim[0], 4, xy, 3), plan_axis(dim[1], kernelDim[1], 1, xy, 3),
+        std::vector<AxisTile> ax[3] = {plan_axis(dim[0], kernelDim[0], 4, xy, 3), plan_axis(dim[1], kernelDim[1], 4, xy, 3),
                                        plan_axis(dim[2], kernelDim[2], 1, zs, 6)};
         require(!ax[0].empty() && !ax[1].empty() && !ax[2].empty(), "mvdPlanTiles: kernel too large");
         int n = 0;

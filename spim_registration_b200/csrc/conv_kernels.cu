@@ -51,7 +51,7 @@ __device__ __forceinline__ int map_coord(int c, int dim, int off, int gmin, int 
 }
 
 template <int BX, int BY>
-__global__ void __launch_bounds__(NT) fwd_xy_kernel(Volume src, const Tile* __restrict__ tiles, float2* __restrict__ scratch,
+__global__ void __launch_bounds__(NT, 3) fwd_xy_kernel(Volume src, const Tile* __restrict__ tiles, float2* __restrict__ scratch,
                                                     size_t tile_stride, int bz, Twiddles tw) {
     using L = PlaneLayout<BX>;
     constexpr int H = BX / 2;
@@ -187,10 +187,11 @@ template <int BZ> struct ZCfg {
     static constexpr int PW = (256 / TZ) < 16 ? 16 : (256 / TZ);
     static constexpr int THREADS = PW * TZ;
     static constexpr size_t SMEM = (size_t)PW * BZ * sizeof(float2);
+    static constexpr int MIN_CTAS = THREADS >= 512 ? 2 : 3;
 };
 
 template <int BZ, int MODE>
-__global__ void __launch_bounds__(ZCfg<BZ>::THREADS) z_pass_kernel(float2* __restrict__ scratch, size_t tile_stride,
+__global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_kernel(float2* __restrict__ scratch, size_t tile_stride,
                                                                    const float2* __restrict__ kspec, const Tile* __restrict__ tiles,
                                                                    int plane_elems, float scale, Twiddles tw) {
     using C = ZCfg<BZ>;
@@ -264,13 +265,12 @@ __device__ __forceinline__ float next_psi_value(float last, float integral, floa
 }
 
 template <int BX, int BY, int EPI>
-__global__ void __launch_bounds__(NT) inv_xy_kernel(const float2* __restrict__ scratch, size_t tile_stride, const Tile* __restrict__ tiles,
+__global__ void __launch_bounds__(NT, 3) inv_xy_kernel(const float2* __restrict__ scratch, size_t tile_stride, const Tile* __restrict__ tiles,
                                                     EpilogueArgs ep, Twiddles tw) {
     using L = PlaneLayout<BX>;
     constexpr int H = BX / 2;
     constexpr int TX = H / 8;
     constexpr int RPR = NT / TX;
-    constexpr int RROUNDS = (BY + RPR - 1) / RPR;
     constexpr int TY = BY / 16;
     constexpr int CPR = NT / TY;
     constexpr int CROUNDS = (H + CPR - 1) / CPR;
@@ -315,15 +315,19 @@ __global__ void __launch_bounds__(NT) inv_xy_kernel(const float2* __restrict__ s
     }
     __syncthreads();
 
-    // ---- phase 2: inverse rows (C2R through the packed half-length transform) + epilogue
+    // ---- phase 2: inverse rows (C2R through the packed half-length transform) + epilogue.
+    // Only the rows of the effective region are transformed; the others would be discarded.
     double lsum = 0.0;
     float lmax = 0.f;
     const int lx = tile.e[0] - tile.o[0], ly = tile.e[1] - tile.o[1];
+    const int n0 = tile.n[0], n1 = tile.n[1];
+    const int rrounds = (n1 + RPR - 1) / RPR;
 #pragma unroll 1
-    for (int rr = 0; rr < RROUNDS; ++rr) {
-        const int row = rr * RPR + tid / TX;
+    for (int rr = 0; rr < rrounds; ++rr) {
+        const int yl = rr * RPR + tid / TX;  // row inside the effective region
+        const int row = ly + yl;
         const int t = tid % TX;
-        const bool valid = row < BY;
+        const bool valid = yl < n1;
         float2 v[8];
 #pragma unroll
         for (int m = 0; m < 8; ++m) {
@@ -349,32 +353,81 @@ __global__ void __launch_bounds__(NT) inv_xy_kernel(const float2* __restrict__ s
         auto sync = [] { __syncwarp(); };
         line_fft<H, 8, true>(v, t, twx, put, get, sync);
 
-        const int yl = row - ly;
-        if (valid && yl >= 0 && yl < tile.n[1]) {
+        if (valid) {
             const size_t rowbase = ((size_t)(zv + ep.out_off[2]) * ep.out_dim[1] + (tile.e[1] + yl + ep.out_off[1])) * (size_t)ep.out_dim[0] +
                                    tile.e[0] + ep.out_off[0];
             const size_t auxbase = ((size_t)zv * ep.aux_dim[1] + (tile.e[1] + yl)) * (size_t)ep.aux_dim[0] + tile.e[0];
+            // thread owns the pairs x = 2k-lx, 2k-lx+1; lx is a multiple of 4, so a pair is 8-byte
+            // aligned whenever the row start is
+            const bool vec = ((rowbase | auxbase) & 1) == 0;
+            float2 a[8], b[8];
+            unsigned full = 0, part = 0;
 #pragma unroll
             for (int m = 0; m < 8; ++m) {
                 const int xl = 2 * (t + m * TX) - lx;
-                const float c[2] = {v[m].x + ep.add_const, v[m].y + ep.add_const};
+                if (xl >= 0 && xl + 1 < n0) full |= 1u << m;
+                else if (xl + 1 == 0 || xl == n0 - 1) part |= 1u << m;
+            }
+            if (vec) {
+                // issue every load before the first use
 #pragma unroll
-                for (int q = 0; q < 2; ++q) {
-                    const int x = xl + q;
-                    if (x < 0 || x >= tile.n[0]) continue;
-                    const size_t idx = rowbase + x, aidx = auxbase + x;
-                    if constexpr (EPI == EPI_STORE) {
-                        ep.out[idx] = c[q];
-                    } else if constexpr (EPI == EPI_QUOTIENT) {
-                        ep.out[idx] = quotient_value(__ldg(ep.img + aidx), c[q]);
-                    } else {
-                        const float last = ep.out[idx];
-                        const float w = ep.weight ? __ldg(ep.weight + aidx) : ep.weight_const;
-                        const float nv = next_psi_value(last, c[q], w, ep.lambda, ep.min_value);
-                        ep.out[idx] = nv;
-                        const float ch = fabsf(__fsub_rn(nv, last));
-                        lsum += (double)ch;
-                        lmax = fmaxf(lmax, ch);  // fmaxf drops NaN
+                for (int m = 0; m < 8; ++m) {
+                    const int xl = 2 * (t + m * TX) - lx;
+                    a[m] = make_float2(0.f, 0.f);
+                    b[m] = make_float2(ep.weight_const, ep.weight_const);
+                    if (full >> m & 1) {
+                        if constexpr (EPI == EPI_QUOTIENT) a[m] = __ldg(reinterpret_cast<const float2*>(ep.img + auxbase + xl));
+                        if constexpr (EPI == EPI_UPDATE) {
+                            a[m] = *reinterpret_cast<const float2*>(ep.out + rowbase + xl);
+                            if (ep.weight) b[m] = __ldg(reinterpret_cast<const float2*>(ep.weight + auxbase + xl));
+                        }
+                    }
+                }
+#pragma unroll
+                for (int m = 0; m < 8; ++m) {
+                    if (!(full >> m & 1)) continue;
+                    const int xl = 2 * (t + m * TX) - lx;
+                    const float c0 = v[m].x + ep.add_const, c1 = v[m].y + ep.add_const;
+                    float2 r;
+                    if constexpr (EPI == EPI_STORE) r = make_float2(c0, c1);
+                    else if constexpr (EPI == EPI_QUOTIENT) r = make_float2(quotient_value(a[m].x, c0), quotient_value(a[m].y, c1));
+                    else {
+                        r.x = next_psi_value(a[m].x, c0, b[m].x, ep.lambda, ep.min_value);
+                        r.y = next_psi_value(a[m].y, c1, b[m].y, ep.lambda, ep.min_value);
+                        const float ch0 = fabsf(__fsub_rn(r.x, a[m].x)), ch1 = fabsf(__fsub_rn(r.y, a[m].y));
+                        lsum += (double)ch0 + (double)ch1;
+                        lmax = fmaxf(lmax, fmaxf(ch0, ch1));  // fmaxf drops NaN
+                    }
+                    *reinterpret_cast<float2*>(ep.out + rowbase + xl) = r;
+                }
+            } else {
+                part |= full;
+            }
+            // scalar path: pairs straddling the region border, or unaligned rows
+            if (part) {
+#pragma unroll
+                for (int m = 0; m < 8; ++m) {
+                    if (!(part >> m & 1)) continue;
+                    const int xl = 2 * (t + m * TX) - lx;
+                    const float c[2] = {v[m].x + ep.add_const, v[m].y + ep.add_const};
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        const int x = xl + q;
+                        if (x < 0 || x >= n0) continue;
+                        const size_t idx = rowbase + x, aidx = auxbase + x;
+                        if constexpr (EPI == EPI_STORE) {
+                            ep.out[idx] = c[q];
+                        } else if constexpr (EPI == EPI_QUOTIENT) {
+                            ep.out[idx] = quotient_value(__ldg(ep.img + aidx), c[q]);
+                        } else {
+                            const float last = ep.out[idx];
+                            const float w = ep.weight ? __ldg(ep.weight + aidx) : ep.weight_const;
+                            const float nv = next_psi_value(last, c[q], w, ep.lambda, ep.min_value);
+                            ep.out[idx] = nv;
+                            const float ch = fabsf(__fsub_rn(nv, last));
+                            lsum += (double)ch;
+                            lmax = fmaxf(lmax, ch);
+                        }
                     }
                 }
             }

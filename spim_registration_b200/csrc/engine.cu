@@ -82,7 +82,7 @@ static const int kZSizes[] = {16, 32, 64, 128, 256, 512};
 
 static std::vector<AxisTile> plan_axes(const int dim[3], const int k[3], int d) {
     if (d == 0) return plan_axis(dim[0], k[0], 4, kXYSizes, 3);
-    if (d == 1) return plan_axis(dim[1], k[1], 1, kXYSizes, 3);
+    if (d == 1) return plan_axis(dim[1], k[1], 4, kXYSizes, 3);  // multiples of 4 rows: whole row rounds in inv_xy
     return plan_axis(dim[2], k[2], 1, kZSizes, 6);
 }
 
@@ -239,22 +239,63 @@ std::unique_ptr<KernelSpectra> build_spectra(Device& dev, const ConvPlan& plan, 
     return spec;
 }
 
+// ---- profiler -------------------------------------------------------------------------
+void Profiler::begin(int cat, double bytes, cudaStream_t st) {
+    Rec r;
+    r.cat = cat;
+    r.bytes = bytes;
+    MVD_CUDA(cudaEventCreate(&r.a));
+    MVD_CUDA(cudaEventCreate(&r.b));
+    MVD_CUDA(cudaEventRecord(r.a, st));
+    recs.push_back(r);
+}
+void Profiler::end(cudaStream_t st) { MVD_CUDA(cudaEventRecord(recs.back().b, st)); }
+void Profiler::collect(double ms[3], long long launches[3], double bytes[3]) {
+    for (int i = 0; i < 3; ++i) { ms[i] = 0; launches[i] = 0; bytes[i] = 0; }
+    for (auto& r : recs) {
+        MVD_CUDA(cudaEventSynchronize(r.b));
+        float t = 0.f;
+        MVD_CUDA(cudaEventElapsedTime(&t, r.a, r.b));
+        ms[r.cat] += t;
+        launches[r.cat] += 1;
+        bytes[r.cat] += r.bytes;
+        cudaEventDestroy(r.a);
+        cudaEventDestroy(r.b);
+    }
+    recs.clear();
+}
+Profiler::~Profiler() {
+    for (auto& r : recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+}
+
 // ---- convolution -----------------------------------------------------------------------
 void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spec, const Volume& src, int epilogue,
-                     const EpilogueArgs& ep, Scratch& scratch, cudaStream_t st) {
+                     const EpilogueArgs& ep, Scratch& scratch, cudaStream_t st, Profiler* prof) {
+    const double epi_bytes = epilogue == EPI_STORE ? 4.0 : (epilogue == EPI_QUOTIENT ? 8.0 : (ep.weight ? 12.0 : 8.0));
     for (size_t ci = 0; ci < plan.classes.size(); ++ci) {
         const TileClass& c = plan.classes[ci];
         const int bx = c.b[0], by = c.b[1], bz = c.b[2];
         const size_t te = tile_scratch_elems(bx, by, bz);
+        const double pe = (double)plane_elems(bx, by);
         const int n = (int)c.tiles.size();
         int batch = (int)std::max<size_t>(1, dev.scratch_budget_bytes() / (te * sizeof(float2)));
         batch = std::min(batch, n);
         scratch.reserve((size_t)batch * te);
         for (int s = 0; s < n; s += batch) {
             const int cnt = std::min(batch, n - s);
+            double nz_sum = 0, out_vox = 0;
+            if (prof)
+                for (int i = s; i < s + cnt; ++i) {
+                    nz_sum += c.tiles[i].n[2];
+                    out_vox += (double)c.tiles[i].n[0] * c.tiles[i].n[1] * c.tiles[i].n[2];
+                }
+            if (prof) prof->begin(0, cnt * ((double)bx * by * bz * 4.0 + pe * bz * 8.0), st);
             MVD_CUDA(launch_fwd_xy(bx, by, bz, src, c.d_tiles + s, cnt, scratch.data, dev.twiddles(), st));
+            if (prof) { prof->end(st); prof->begin(1, cnt * pe * bz * 8.0 + pe * bz * 8.0 + nz_sum * pe * 8.0, st); }
             MVD_CUDA(launch_z_pass(bx, by, bz, 1, scratch.data, spec.per_class[ci], c.d_tiles + s, cnt, 1.f, dev.twiddles(), st));
+            if (prof) { prof->end(st); prof->begin(2, nz_sum * pe * 8.0 + out_vox * epi_bytes, st); }
             MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, scratch.data, c.d_tiles + s, cnt, c.max_nz, ep, dev.twiddles(), st));
+            if (prof) prof->end(st);
             g_kernel_launches += 3;
         }
     }

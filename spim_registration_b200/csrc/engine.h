@@ -88,10 +88,24 @@ struct Scratch {
     ~Scratch();
 };
 
+// Optional per-kernel timing with CUDA events on the launching stream (bench.py roofline).
+// Categories: 0 fwd_xy, 1 z_pass, 2 inv_xy.  `bytes` are the ALGORITHMIC bytes of the launch
+// (DESIGN.md "byte model"): each pass counts its input once and its output once, the z pass
+// additionally the kernel spectrum once per launch, inv_xy the arrays of its fused epilogue.
+struct Profiler {
+    struct Rec { int cat; cudaEvent_t a, b; double bytes; };
+    std::vector<Rec> recs;
+    void begin(int cat, double bytes, cudaStream_t st);
+    void end(cudaStream_t st);
+    // synchronises the events and accumulates; clears the records
+    void collect(double ms[3], long long launches[3], double bytes[3]);
+    ~Profiler();
+};
+
 std::unique_ptr<KernelSpectra> build_spectra(Device& dev, const ConvPlan& plan, const float* kernel_host, cudaStream_t st);
 
 // out-of-place tiled convolution of `src`; the epilogue decides what is stored.
 void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spec, const Volume& src, int epilogue,
-                     const EpilogueArgs& ep, Scratch& scratch, cudaStream_t st);
+                     const EpilogueArgs& ep, Scratch& scratch, cudaStream_t st, Profiler* prof = nullptr);
 
 }  // namespace mvd

@@ -1,0 +1,202 @@
+"""Spatial sharding of the deconvolution over the GPUs of one box.
+
+One process per GPU (torch.distributed, NCCL over NVLink; gloo for the CPU tests).  The volume is
+cut into a grid of bricks; every rank keeps psi and the quotient for its brick plus a ghost layer
+of the kernel half-width.  Per view and iteration there are exactly two exchanges -- the quotient
+ghosts before conv2 and the psi ghosts before the next conv1 -- done axis by axis (x, y, z) with
+full-extent slabs so that edges and corners arrive through the later axes.  The reference has no
+counterpart (its multi-GPU mode is one Java thread per device pulling blocks through host RAM,
+MVDeconFFTThreads.java:96-134).
+"""
+import ctypes as C
+
+import numpy as np
+
+
+def brick_grid(world, dim_xyz):
+    """Grid (gx, gy, gz) with gx*gy*gz = world: split the longest axes first, z before y before x
+    on ties (z/y slabs keep rows contiguous)."""
+    grid = [1, 1, 1]
+    n = world
+    assert n >= 1 and (n & (n - 1)) == 0, "world size must be a power of two"
+    while n > 1:
+        per = [dim_xyz[d] / grid[d] for d in range(3)]
+        d = max((2, 1, 0), key=lambda a: (per[a], a))
+        grid[d] *= 2
+        n //= 2
+    return tuple(grid)
+
+
+def brick_of(rank, grid, dim_xyz):
+    """(offset_xyz, size_xyz, coords) of `rank`; x fastest in the rank order."""
+    cx, cy, cz = rank % grid[0], (rank // grid[0]) % grid[1], rank // (grid[0] * grid[1])
+    # brick boundaries b_i = floor4(n*i/g) (b_0 = 0, b_g = n) keep x bricks float4-aligned
+    off, size = [], []
+    for c, g, n in zip((cx, cy, cz), grid, dim_xyz):
+        def bound(i):
+            if i == 0:
+                return 0
+            if i == g:
+                return n
+            return (n * i) // g // 4 * 4
+        off.append(bound(c))
+        size.append(bound(c + 1) - bound(c))
+    return tuple(off), tuple(size), (cx, cy, cz)
+
+
+def rank_of(coords, grid):
+    return coords[0] + grid[0] * (coords[1] + grid[1] * coords[2])
+
+
+def exchange_ghosts(t, off_zyx, brick_zyx, ghost_xyz, coords, grid, dist, group=None):
+    """Fill the ghost layers of the ghosted tensor `t` ([z,y,x], brick interior starting at
+    off_zyx) from the neighbouring ranks.  Works for CUDA tensors (NCCL) and CPU tensors (gloo)."""
+    import torch
+    for axis_xyz in (0, 1, 2):
+        g = ghost_xyz[axis_xyz]
+        if g == 0 or grid[axis_xyz] == 1:
+            continue
+        dim = 2 - axis_xyz  # tensor dim
+        o, b = off_zyx[dim], brick_zyx[dim]
+        c = coords[axis_xyz]
+        ops, recvs = [], []
+        for side in (-1, 1):
+            nc = c + side
+            if nc < 0 or nc >= grid[axis_xyz]:
+                continue
+            nco = list(coords)
+            nco[axis_xyz] = nc
+            peer = rank_of(nco, grid)
+            if side < 0:
+                send = t.narrow(dim, o, g).contiguous()        # my low interior -> peer's high ghost
+                ghost = t.narrow(dim, o - g, g)                 # my low ghost <- peer's high interior
+            else:
+                send = t.narrow(dim, o + b - g, g).contiguous()
+                ghost = t.narrow(dim, o + b, g)
+            rbuf = torch.empty(ghost.shape, dtype=t.dtype, device=t.device)
+            ops.append(dist.P2POp(dist.isend, send, peer, group))
+            ops.append(dist.P2POp(dist.irecv, rbuf, peer, group))
+            recvs.append((ghost, rbuf))
+        if ops:
+            for r in dist.batch_isend_irecv(ops):
+                r.wait()
+            for ghost, rbuf in recvs:
+                ghost.copy_(rbuf)
+
+
+class _CudaArray:
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = dict(shape=tuple(shape), typestr="<f4", data=(int(ptr), False), version=2)
+
+
+class ShardedDeconvolution:
+    """MVDeconvolution (MVDeconvolution.java:73-190) on one brick per rank through the step API of
+    libmvdecon.so.  imgs/weights are this rank's brick ([z,y,x] torch CUDA tensors or numpy arrays)."""
+
+    def __init__(self, dim_xyz, imgs, weights, kernel1, kernel2, lam, dist=None, device=0, min_value=1e-4, grid=None):
+        import torch
+        from . import _lib as L
+        self.L, self.lib, self.torch, self.dist = L, L.load(), torch, dist
+        self.world = dist.get_world_size() if dist is not None else 1
+        self.rank = dist.get_rank() if dist is not None else 0
+        self.dim = tuple(dim_xyz)
+        self.grid = grid or brick_grid(self.world, self.dim)
+        self.off, self.size, self.coords = brick_of(self.rank, self.grid, self.dim)
+        self.device = device
+        self.V = len(imgs)
+        gh = [0, 0, 0]
+        for k in list(kernel1) + list(kernel2):
+            ks = k.shape[::-1]
+            for d in range(3):
+                if self.grid[d] > 1:
+                    gh[d] = max(gh[d], ks[d] // 2, ks[d] - 1 - ks[d] // 2)
+        self.ghost = tuple(gh)
+        self.ctx = C.c_void_p()
+        L.check(self.lib.mvdCreate(C.byref(self.ctx), device, L.int3(self.dim), L.int3(self.off), L.int3(self.size), L.int3(self.ghost),
+                                   float(lam), float(min_value)), "mvdCreate")
+        L.check(self.lib.mvdSetStream(self.ctx, C.c_void_p(torch.cuda.current_stream().cuda_stream)), "mvdSetStream")
+        for v in range(self.V):
+            img, w = imgs[v], weights[v]
+            is_dev = hasattr(img, "data_ptr")
+            ip = C.c_void_p(img.data_ptr()) if is_dev else img.ctypes.data_as(C.c_void_p)
+            if w is None or np.isscalar(w):
+                wp, wc = None, (1.0 if w is None else float(w))
+            else:
+                wp, wc = (C.c_void_p(w.data_ptr()) if is_dev else w.ctypes.data_as(C.c_void_p)), 1.0
+            k1 = np.ascontiguousarray(kernel1[v], dtype=np.float32)
+            k2 = np.ascontiguousarray(kernel2[v], dtype=np.float32)
+            L.check(self.lib.mvdAddView(self.ctx, ip, wp, wc, k1.ctypes.data_as(L.c_float_p), L.int3(k1.shape[::-1]),
+                                        k2.ctypes.data_as(L.c_float_p), L.int3(k2.shape[::-1]), 1 if is_dev else 0, None), "mvdAddView")
+        self._arrays = {}
+        for which in (0, 1):
+            ptr, dim, off = C.c_void_p(), (C.c_int * 3)(), (C.c_int * 3)()
+            L.check(self.lib.mvdArrayInfo(self.ctx, which, C.byref(ptr), dim, off), "mvdArrayInfo")
+            t = torch.as_tensor(_CudaArray(ptr.value, (dim[2], dim[1], dim[0])), device=torch.device("cuda", device))
+            self._arrays[which] = (t, (off[2], off[1], off[0]))
+        self.slot = 0
+
+    # -- pieces of the MVDeconvolution constructor ------------------------------------------
+    def init_psi_average(self):
+        s, n = C.c_double(), C.c_longlong()
+        self.L.check(self.lib.mvdFirstIterationSums(self.ctx, C.byref(s), C.byref(n)), "mvdFirstIterationSums")
+        tot = self.torch.tensor([s.value, float(n.value)], dtype=self.torch.float64, device=self._arrays[0][0].device)
+        if self.world > 1:
+            self.dist.all_reduce(tot)
+        avg = float(tot[0] / tot[1])
+        if avg != avg:
+            avg = 0.5
+        self.L.check(self.lib.mvdFillPsi(self.ctx, avg), "mvdFillPsi")
+        return avg
+
+    def _exchange(self, which):
+        if self.world == 1:
+            return
+        t, off = self._arrays[which]
+        exchange_ghosts(t, off, self.size[::-1], self.ghost, self.coords, self.grid, self.dist)
+
+    def run_iterations(self, n):
+        first = self.slot
+        if self.world == 1:
+            for _ in range(n):
+                for v in range(self.V):
+                    self.L.check(self.lib.mvdStepQuotient(self.ctx, v), "mvdStepQuotient")
+                    self.L.check(self.lib.mvdStepUpdate(self.ctx, v, self.slot), "mvdStepUpdate")
+                    self.slot += 1
+            return first, self.slot
+        for _ in range(n):
+            for v in range(self.V):
+                self.L.check(self.lib.mvdStepQuotient(self.ctx, v), "mvdStepQuotient")
+                self._exchange(1)
+                self.L.check(self.lib.mvdStepUpdate(self.ctx, v, self.slot), "mvdStepUpdate")
+                self._exchange(0)
+                self.slot += 1
+        return first, self.slot
+
+    def stats(self, first, last):
+        n = last - first
+        s, m = (C.c_double * n)(), (C.c_double * n)()
+        self.L.check(self.lib.mvdGetStats(self.ctx, first, n, s, m), "mvdGetStats")
+        ts = self.torch.tensor(list(s), dtype=self.torch.float64, device=self._arrays[0][0].device)
+        tm = self.torch.tensor(list(m), dtype=self.torch.float64, device=self._arrays[0][0].device)
+        if self.world > 1:
+            self.dist.all_reduce(ts)
+            self.dist.all_reduce(tm, op=self.dist.ReduceOp.MAX)
+        return ts.cpu().numpy().reshape(-1, self.V), tm.cpu().numpy().reshape(-1, self.V)
+
+    def mask_never_updated(self):
+        self.L.check(self.lib.mvdMaskNeverUpdated(self.ctx), "mvdMaskNeverUpdated")
+
+    def get_psi_brick(self, out=None):
+        """Brick of psi as numpy [z,y,x] (device -> host)."""
+        if out is None:
+            out = np.empty(self.size[::-1], dtype=np.float32)
+        self.L.check(self.lib.mvdGetPsi(self.ctx, out.ctypes.data_as(C.c_void_p), 0), "mvdGetPsi")
+        return out
+
+    def kernel_launches(self):
+        return self.lib.mvdKernelLaunchCount()
+
+    def close(self):
+        if self.ctx:
+            self.lib.mvdDestroy(self.ctx)
+            self.ctx = None
