@@ -1,0 +1,227 @@
+"""CPU tests of the oracle (oracle/oracle_np.py) -- no GPU needed.
+
+The reference ships no tests or golden data for this path, so the oracle
+is pinned against (a) the known answers derivable from the reference's own `main` smoke programs
+(Block.java:367-402, MVDeconvolution.java:707-714), (b) an FFT-free brute-force restatement of
+the convolution formula, (c) the invariants the reference's structure implies (tiling invariance,
+fixed point, delta placement), and (d) the frozen golden fixture tests/golden/loop_3view_32.npz.
+"""
+import math
+import os
+
+import numpy as np
+import pytest
+
+import oracle_np as o
+from conftest import rel_l2
+
+F32 = np.float32
+
+
+# ---- (a) known answers from the reference's main() programs -----------------------------------
+def test_block_kat_from_block_main():
+    """Block.java:367-402: image 1024x1024, block 384x384, kernel (16, 32)."""
+    blocks = o.divide_into_blocks([1024, 1024], [16, 32], [384, 384])
+    assert len(blocks) == 9  # 3 x 3
+    eff = [384 - 16 + 1, 384 - 32 + 1]
+    assert eff == [369, 353]
+    b0, b1, b3, last = blocks[0], blocks[1], blocks[3], blocks[-1]
+    assert b0["effectiveOffset"] == [0, 0] and b0["offset"] == [-8, -16] and b0["effectiveSize"] == eff
+    assert b1["effectiveOffset"] == [369, 0]  # dimension 0 fastest
+    assert b3["effectiveOffset"] == [0, 353]
+    assert last["effectiveOffset"] == [738, 706] and last["effectiveSize"] == [286, 318]
+    assert all(b["blockSize"] == [384, 384] and b["effectiveLocalOffset"] == [8, 16] for b in blocks)
+    # the effective regions partition the image exactly
+    cover = np.zeros((1024, 1024), np.int32)
+    for b in blocks:
+        eo, es = b["effectiveOffset"], b["effectiveSize"]
+        cover[eo[1]:eo[1] + es[1], eo[0]:eo[0] + es[0]] += 1
+    assert (cover == 1).all()
+
+
+def test_block_counts_at_baseline_configs():
+    """cfg3 B=256,K=31 -> E=226, 5x5x3 = 75 blocks, last effective (120,120,60)."""
+    blocks = o.divide_into_blocks([1024, 1024, 512], [31, 31, 31], [256, 256, 256])
+    assert len(blocks) == 75
+    assert blocks[-1]["effectiveSize"] == [120, 120, 60]
+    assert len(o.divide_into_blocks([512, 512, 256], [31] * 3, [256] * 3)) == 18
+    assert len(o.divide_into_blocks([2048, 2048, 1024], [31] * 3, [256] * 3)) == 500
+    assert len(o.divide_into_blocks([2048, 2048, 1024], [31] * 3, [512] * 3)) == 75
+    assert o.divide_into_blocks([64, 64, 64], [31] * 3, [30] * 3) is None  # :38-42 returns null
+
+
+def test_tikhonov_table():
+    """MVDeconvolution.java:705-714: tikhonov(d, 0.0006) for d in [0, 10) and 10000*d."""
+    lam = 0.0006
+    d = 0.0
+    while d < 10:
+        for v in (d * 10000, d):
+            want = (math.sqrt(1.0 + 2.0 * lam * v) - 1.0) / lam
+            assert o.tikhonov(np.float64(v), lam) == pytest.approx(want, rel=1e-15, abs=0)
+        d += 0.1
+    # the regulariser shrinks, is monotone and tends to the identity for small values
+    v = np.linspace(1e-3, 50, 1000)
+    t = o.tikhonov(v, 0.006)
+    assert (t < v).all() and (np.diff(t) > 0).all()
+    assert o.tikhonov(np.float64(1e-6), 0.006) == pytest.approx(1e-6, rel=1e-5)
+
+
+def test_update_rule_scalar_cases():
+    """computeNextValue (MVDeconvolution.java:671-703) on hand-evaluated cases."""
+    psi = np.array([0.5, 0.5, 0.5, 0.5, 2.0], F32)
+    integral = np.array([2.0, -1.0, np.nan, 0.0, 1e-6], F32)
+    w = np.array([1.0, 1.0, 1.0, 0.25, 0.5], F32)
+    new, s, m = o.compute_final_values(psi, integral, w, 0.0)
+    # value>0 -> value ; value<=0 -> minValue ; NaN -> minValue ; weights blend
+    nxt = np.array([1.0, 1e-4, 1e-4, 1e-4, 1e-4], F32)
+    want = (psi + ((nxt - psi).astype(F32) * w).astype(F32)).astype(F32)  # float arithmetic, as in Java (:702)
+    assert want[0] == 1.0 and abs(float(want[1]) - 1e-4) < 1e-7 and want[3] == F32(0.5) + (F32(1e-4) - F32(0.5)) * F32(0.25)
+    np.testing.assert_array_equal(new, want)
+    assert m == pytest.approx(float(np.abs(want - psi).max()))
+    assert s == pytest.approx(float(np.abs((want - psi).astype(F32)).astype(np.float64).sum()))
+    new, _, _ = o.compute_final_values(np.array([0.5], F32), np.array([2.0], F32), F32(1.0), 0.006)
+    assert new[0] == F32((math.sqrt(1.0 + 2.0 * 0.006 * 1.0) - 1.0) / 0.006)
+
+
+def test_quotient_rule():
+    """MVDeconvolution.java:496-499: img > 0 ? img / blurred : 1; no guard on blurred == 0."""
+    q = o.compute_quotient(np.array([2.0, 0.0, 4.0, 1.0], F32), np.array([1.0, 1.0, 0.0, -1.0], F32))
+    assert q[0] == F32(0.5) and np.isinf(q[1]) and q[2] == 1.0 and q[3] == 1.0
+
+
+# ---- kernel preparation quirks -----------------------------------------------------------------
+def test_sum_img_double_counts_first_portion():
+    """AdjustInput.java:62,72,93-97."""
+    img = np.arange(1, 101, dtype=F32)
+    T = 4
+    chunk = 100 // (2 * T)
+    assert o.sum_img(img, T) == pytest.approx(float(img.sum()) + float(img[:chunk].sum()))
+    k = o.norm_img(np.ones((5, 5, 5), F32), 8)
+    assert float(k.astype(np.float64).sum()) < 1.0  # normalised kernels sum to slightly < 1
+
+
+def test_mirror_odd_is_flip_even_keeps_middle_pair():
+    a = np.arange(7, dtype=F32).reshape(1, 1, 7)
+    np.testing.assert_array_equal(o.mirror(a, 0)[0, 0], a[0, 0, ::-1])
+    b = np.arange(6, dtype=F32).reshape(1, 1, 6)
+    # Mirror.java:72: sizeMirrorH = dim/2 and the loop runs p <= sizeMirrorH... the middle pair is swapped twice
+    np.testing.assert_array_equal(o.mirror(b, 0)[0, 0], np.array([5, 4, 2, 3, 1, 0], F32))
+
+
+@pytest.mark.parametrize("psftype", o.PSFTYPES)
+def test_kernel2_properties(psftype):
+    from spim_registration_b200 import synthetic
+    psfs = synthetic.make_psfs(3, (7, 5, 9), extracted=True)
+    k1, k2 = o.init_kernels(psfs, psftype, 8)
+    for v in range(3):
+        assert k1[v].dtype == F32 and k2[v].dtype == F32 and k2[v].shape == k1[v].shape
+        assert 0.9 < float(k1[v].astype(np.float64).sum()) < 1.0
+    if psftype == "INDEPENDENT":
+        for v in range(3):
+            np.testing.assert_array_equal(k2[v], k1[v][::-1, ::-1, ::-1])
+    if psftype == "OPTIMIZATION_II":
+        e = (k1[0] * k1[0]).astype(F32)
+        e = (e * k1[0]).astype(F32)
+        np.testing.assert_array_equal(k2[0], o.norm_img(e, 8)[::-1, ::-1, ::-1])
+    if psftype in ("EFFICIENT_BAYESIAN", "OPTIMIZATION_I"):
+        assert 0.9 < float(k2[0].astype(np.float64).sum()) < 1.0
+
+
+def test_single_view_uses_flipped_kernel_for_every_type():
+    """MVDeconFFT.java:174-180: numViews == 1 -> kernel2 = flip(kernel1) whatever the type."""
+    from spim_registration_b200 import synthetic
+    psf = synthetic.make_psfs(1, (5, 5, 5))
+    for t in o.PSFTYPES:
+        k1, k2 = o.init_kernels(psf, t, 8)
+        np.testing.assert_array_equal(k2[0], k1[0][::-1, ::-1, ::-1])
+
+
+# ---- (b) convolution formula against brute force ----------------------------------------------
+@pytest.mark.parametrize("mode", ["zero", "const", "mirror"])
+@pytest.mark.parametrize("shape,ks", [((6, 7, 8), (3, 5, 3)), ((5, 4, 9), (4, 2, 6)), ((3, 3, 3), (7, 7, 7))])
+def test_fft_oracle_equals_direct_sum(mode, shape, ks):
+    rng = np.random.default_rng(5)
+    f = rng.random(shape, dtype=F32)
+    k = rng.random(ks, dtype=F32)
+    a = o.convolve_extended(f, k, mode, 1.0)
+    b = o.convolve_direct(f, k, mode, 1.0)
+    np.testing.assert_allclose(a, b, rtol=2e-6, atol=1e-6)
+
+
+def test_delta_places_kernel_unflipped():
+    """Convolution, not correlation (SURVEY.md 8c caveat): delta at p -> kernel[j] at p + j - K//2."""
+    k = np.arange(1, 3 * 5 * 7 + 1, dtype=F32).reshape(3, 5, 7)
+    d = np.zeros((9, 11, 13), F32)
+    d[4, 5, 6] = 1
+    out = o.convolve_extended(d, k, "zero")
+    np.testing.assert_allclose(out[3:6, 3:8, 3:10], k, atol=1e-4)
+
+
+def test_mirror_single_extension_indices():
+    a = np.arange(5, dtype=F32).reshape(1, 1, 5)
+    e = o.extend(a, (0, 0, 3), (0, 0, 3), "mirror")
+    np.testing.assert_array_equal(e[0, 0], np.array([3, 2, 1, 0, 1, 2, 3, 4, 3, 2, 1], F32))
+    e = o.extend(a, (0, 0, 9), (0, 0, 9), "mirror")  # halo wider than the image: period 2n-2
+    idx = np.arange(-9, 14)
+    p = np.mod(idx, 8)
+    np.testing.assert_array_equal(e[0, 0], np.where(p >= 5, 8 - p, p).astype(F32))
+
+
+# ---- (c) structural invariants ---------------------------------------------------------------
+@pytest.mark.parametrize("mode,val", [("mirror", 0.0), ("const", 1.0)])
+def test_tiling_invariance(mode, val):
+    """SURVEY.md 8a invariant (i): reference-style blocks with ANY in-block extension == whole volume."""
+    rng = np.random.default_rng(9)
+    f = rng.random((20, 26, 30), dtype=F32)
+    k = rng.random((5, 7, 3), dtype=F32)
+    whole = o.convolve_extended(f, k, mode, val)
+    tiled = o.convolve_blockwise(f, k, mode, val, [16, 14, 12], lambda blk, kk: o.convolve_extended(blk, kk, "zero"))
+    assert rel_l2(tiled, whole) < 1e-6
+
+
+def test_copy_paste_block_roundtrip_is_identity_on_effective_regions():
+    rng = np.random.default_rng(2)
+    f = rng.random((10, 12, 14), dtype=F32)
+    blocks = o.divide_into_blocks([14, 12, 10], [3, 5, 3], [8, 8, 8])
+    out = np.full_like(f, -1)
+    for b in blocks:
+        o.paste_block(out, o.copy_block(f, b, "mirror"), b)
+    np.testing.assert_array_equal(out, f)  # bit exact: pure index arithmetic
+
+
+def test_fixed_point_of_independent_update():
+    from spim_registration_b200 import synthetic
+    truth = synthetic.make_truth((14, 16, 18), "blob", 5) + F32(0.05)
+    k = np.random.default_rng(1).random((5, 5, 5), dtype=F32)
+    k = (k / k.sum()).astype(F32)
+    img = o.convolve_extended(truth, k, "mirror")
+    psi, _, _ = o.run_deconvolution([img], [F32(1.0)], [k], [k[::-1, ::-1, ::-1].copy()], 3, 0.0, psi0=truth)
+    assert rel_l2(psi, truth) < 2e-5
+
+
+def test_first_iteration_average_and_mask():
+    a = np.array([[[0.0, 2.0, 4.0, 0.0]]], F32)
+    b = np.array([[[0.0, 4.0, 0.0, 0.0]]], F32)
+    avg, cnt = o.fuse_first_iteration([a, b])
+    assert avg == pytest.approx((3.0 + 4.0) / 2) and cnt.ravel().tolist() == [0, 2, 1, 0]
+    k = np.ones((1, 1, 1), F32)
+    psi, stats, _ = o.run_deconvolution([a, b], [F32(0.5), F32(0.5)], [k, k], [k, k], 1, 0.0)
+    assert psi[0, 0, 0] == 0 and psi[0, 0, 3] == 0 and (psi[0, 0, 1:3] > 0).all()
+    avg, _ = o.fuse_first_iteration([np.zeros((2, 2, 2), F32)])
+    assert math.isnan(avg)  # -> 0.5 in run_deconvolution (MVDeconvolution.java:117-121)
+
+
+# ---- (d) the golden fixture is reproducible ---------------------------------------------------
+def test_golden_fixture_reproduced_by_oracle():
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "loop_3view_32.npz"))
+    V = int(g["num_views"])
+    psfs = [g["psf%d" % v] for v in range(V)]
+    k1, k2 = o.init_kernels(psfs, str(g["psftype"]), 8)
+    for v in range(V):
+        np.testing.assert_array_equal(k1[v], g["k1_%d" % v])
+        np.testing.assert_allclose(k2[v], g["k2_%d" % v], rtol=1e-6, atol=1e-12)
+    psi, stats, avg = o.run_deconvolution([g["img%d" % v] for v in range(V)], [g["weight%d" % v] for v in range(V)],
+                                          [g["k1_%d" % v] for v in range(V)], [g["k2_%d" % v] for v in range(V)],
+                                          int(g["iterations"]), float(g["lam"]))
+    assert avg == pytest.approx(float(g["avg"]), rel=1e-12)
+    assert rel_l2(psi, g["psi"]) < 1e-6
