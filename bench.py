@@ -223,7 +223,6 @@ def run_ours(args, cfg):
     if rank == 0:
         sampler.start()
     launches0 = dec.kernel_launches()
-    L.check(lib.mvdProfileStart(dec.ctx), "mvdProfileStart")
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     dec.run_iterations(args.steps)
@@ -235,6 +234,17 @@ def run_ours(args, cfg):
     ms = float(ms.item())
     clocks = sampler.stop() if rank == 0 else None
     launches = dec.kernel_launches() - launches0
+    # per-kernel durations: the same steps again with every launch bracketed by CUDA events on one
+    # stream (the timed region above deals independent tile batches to several streams, where a
+    # launch's elapsed time would include its neighbours)
+    prof_steps = min(args.steps, 2)
+    L.check(lib.mvdProfileStart(dec.ctx), "mvdProfileStart")
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record()
+    dec.run_iterations(prof_steps)
+    p1.record()
+    barrier()
+    prof_ms = p0.elapsed_time(p1)
     pms, pl, pb = (C.c_double * 3)(), (C.c_longlong * 3)(), (C.c_double * 3)()
     L.check(lib.mvdProfileStop(dec.ctx, pms, pl, pb), "mvdProfileStop")
     dec.close()
@@ -291,10 +301,12 @@ def run_ours(args, cfg):
         "config": {"workload": cfg["name"], "views": V, "volume_xyz": list(dim_xyz), "psf": cfg["k"], "iteration_type": cfg["psftype"],
                    "lambda": LAMBDA, "step": "one iteration over all views", "brick_grid_xyz": list(grid),
                    "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % ((2 * V + 2) * nvox * 4 / world / 1e9),
-                   "scratch_mb": int(os.environ.get("MVD_SCRATCH_MB", "256"))},
+                   "scratch_mb": int(os.environ.get("MVD_SCRATCH_MB", "256")), "batch_streams": int(os.environ.get("MVD_LANES", "3"))},
         "roofline": {"bound": "hbm", "kernel": names[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                     "share_of_step": pms[top] / ms, "kernels": kern,
+                     "share_of_step": pms[top] / prof_ms, "kernels": kern,
+                     "timing": "CUDA events around every launch, %d serial step(s) after the timed region (%.1f ms/step serial vs %.1f ms/step with %s batch streams)"
+                               % (prof_steps, prof_ms / prof_steps, ms / args.steps, os.environ.get("MVD_LANES", "3")),
                      "loop": {"alg_bytes_per_voxel_view_iteration": ALG_BYTES_PER_VOXEL_VIEW[cfg["dense_weights"]],
                               "achieved": loop_bytes / 1e9 / (ms * 1e-3), "frac": loop_bytes / 1e9 / (ms * 1e-3) / peak,
                               "frac_of_8TBs": loop_bytes / 1e9 / (ms * 1e-3) / 8000.0}},

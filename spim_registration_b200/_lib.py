@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmvdecon.so")
+LIB_PATH = os.environ.get("MVD_LIB_PATH") or os.path.join(_HERE, "libmvdecon.so")  # MVD_LIB_PATH: A/B builds during tuning
 
 c_float_p = C.POINTER(C.c_float)
 c_int_p = C.POINTER(C.c_int)

@@ -20,11 +20,18 @@
 // from the constant bank (warp-uniform), and all register arrays are statically indexed.
 #include "conv_kernels.h"
 #include "fft_device.cuh"
+#include "row128.cuh"
 
 namespace mvd {
 
 static constexpr int NT = 256;  // threads per CTA of the xy kernels
-static constexpr int XY_ZPC = 2;  // z-planes per CTA of the xy kernels
+#ifndef MVD_XY_ZPC
+#define MVD_XY_ZPC 2
+#endif
+#ifndef MVD_PREFETCH
+#define MVD_PREFETCH 0
+#endif
+static constexpr int XY_ZPC = MVD_XY_ZPC;  // z-planes per CTA of the xy kernels
 
 // exp(-2 pi i n / 128): column twiddles of the xy kernels (the index is warp-uniform there)
 __constant__ float2 c_tw128[128];
@@ -34,14 +41,21 @@ struct ConstTw128 {
     __device__ __forceinline__ float2 operator[](int i) const { return c_tw128[i << shift]; }
 };
 
-// shared-memory plane: BY rows of H = BX/2 packed complex columns; element k of a row lives in
-// slot k + (k >> 3) and the row pitch is P = H + H/8, i.e. 16 (H=64), 8 (H=32), 4 (H=16) banks
-// modulo 32 -- rows of a warp never collide and a stride-8 scatter becomes a stride-9 one.
+// shared-memory plane: BY rows of H = BX/2 packed complex columns.
+// Generic sizes: element k of a row lives in slot k + (k >> 3) and the row pitch is P = H + H/8,
+// i.e. 16 (H=64), 8 (H=32), 4 (H=16) banks modulo 32 -- rows of a warp never collide and a
+// stride-8 scatter becomes a stride-9 one.
+// BX = 128 (the hot size): natural slots, pitch 68 (= 4 slots modulo 16): the fast row passes put
+// 4 threads on a row and 8 rows in a warp, so the 4 rows of a half-warp sit 4 slots apart and
+// every access pattern below covers the 16 slots (32 banks) exactly once; the column passes read
+// 32 consecutive columns per warp, conflict-free in natural order.
 template <int BX> struct PlaneLayout {
     static constexpr int H = BX / 2;
-    static constexpr int P = H + H / 8;
-    __device__ __forceinline__ static constexpr int slot(int k) { return k + (k >> 3); }
+    static constexpr int P = BX == 128 ? 68 : H + H / 8;
+    __device__ __forceinline__ static constexpr int slot(int k) { return BX == 128 ? k : k + (k >> 3); }
 };
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // Map a local coordinate through the source's out-of-bounds rule.
 // Returns the local array index, -1 for the fill value `ext_value`/0, -2 for zero (outside the brick).
@@ -76,9 +90,11 @@ template <int BX, int BY> struct XYCfg {
     static constexpr bool CFULL = (H % CPR) == 0;
     static constexpr size_t PLANE = (size_t)BY * L::P * sizeof(float2);
     // forward: plane | row twiddles (H) | untangle twiddles (H) | column 0 staging (BY) | x map (BX)
+    // (BX = 128: the two twiddle areas hold the per-thread tables of the fast row pass, 64 + 32 float2)
     static constexpr size_t SMEM_FWD = PLANE + (size_t)(2 * H + BY) * sizeof(float2) + (size_t)BX * sizeof(int);
     // inverse: plane | row twiddles (H) | untangle twiddles (H)
     static constexpr size_t SMEM_INV = PLANE + (size_t)(2 * H) * sizeof(float2);
+    static_assert(BX != 128 || 2 * H >= 96, "fast-row tables need 96 float2");
     // 228 KB per SM, 1 KB reserved per resident CTA (+ the inverse kernel's static reduction arrays)
     static constexpr int MIN_CTAS = (SMEM_FWD + 1024 + 128) * 3 <= 233472 ? 3 : ((SMEM_FWD + 1024 + 128) * 2 <= 233472 ? 2 : 1);
 };
@@ -91,7 +107,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
     using C = XYCfg<BX, BY>;
     using L = PlaneLayout<BX>;
     constexpr int H = C::H, P = L::P, TX = C::TX, RPR = C::RPR, TY = C::TY, CPR = C::CPR;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     float2* plane = reinterpret_cast<float2*>(smem_raw);
     float2* twr = plane + (size_t)BY * P;   // exp(-2 pi i n / H)
     float2* twu = twr + H;                  // exp(-2 pi i n / BX), n < H
@@ -103,9 +119,13 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
     const int z0 = blockIdx.x * XY_ZPC;
 
     // ---- per-CTA setup
-    for (int i = tid; i < H; i += NT) {
-        twr[i] = __ldg(&tw.t[ilog2<H>()][i]);
-        twu[i] = __ldg(&tw.t[ilog2<BX>()][i]);
+    if constexpr (BX == 128) {
+        row128_fill_tables(twr, twu, tw.t[6], tw.t[7], false, tid, NT);
+    } else {
+        for (int i = tid; i < H; i += NT) {
+            twr[i] = __ldg(&tw.t[ilog2<H>()][i]);
+            twu[i] = __ldg(&tw.t[ilog2<BX>()][i]);
+        }
     }
     for (int i = tid; i < BX; i += NT) xmap[i] = map_coord(tile.o[0] + i, src.dim[0], src.off[0], src.gmin[0], src.gdim[0], src.ext);
     const int xo = tile.o[0] + src.off[0];  // array index of the window start
@@ -132,6 +152,54 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
         const float* __restrict__ zbase = src.data + (size_t)(zl < 0 ? 0 : zl) * src.dim[1] * (size_t)src.dim[0];
 
         // ---- phase 1: rows, real -> half spectrum (packed: slot 0 = (X[0], X[H]))
+        if constexpr (BX == 128) {
+            const int q = tid & 3;
+            if (MVD_PREFETCH && xfast && zi + 1 < XY_ZPC && z + 1 < bz) {
+                // pull the next plane's rows towards L2 while this plane is transformed
+                const int zn = map_coord(tile.o[2] + z + 1, src.dim[2], src.off[2], src.gmin[2], src.gdim[2], src.ext);
+                if (zn >= 0) {
+                    for (int row = tid >> 2; row < BY; row += NT / 4) {
+                        const int yn = map_coord(tile.o[1] + row, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
+                        if (yn >= 0) prefetch_l2(src.data + ((size_t)zn * src.dim[1] + yn) * (size_t)src.dim[0] + xo + 32 * q);
+                    }
+                }
+            }
+            const bool xfast4 = xfast && ((xo | src.dim[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(src.data) & 15) == 0;
+#pragma unroll 1
+            for (int row = tid >> 2; row < BY; row += NT / 4) {
+                float2 a[8], b[8];
+                const int yl = zl < 0 ? zl : map_coord(tile.o[1] + row, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
+                if (yl < 0) {
+                    const float f = yl == -1 ? fillv : 0.f;
+#pragma unroll
+                    for (int m = 0; m < 8; ++m) a[m] = b[m] = make_float2(f, f);
+                } else {
+                    const float* __restrict__ rowp = zbase + (size_t)yl * src.dim[0];
+                    if (xfast4) {
+                        const float4* __restrict__ p4 = reinterpret_cast<const float4*>(rowp + xo) + q;
+#pragma unroll
+                        for (int m = 0; m < 8; ++m) {
+                            const float4 f = __ldg(p4 + 4 * m);
+                            a[m] = make_float2(f.x, f.y);
+                            b[m] = make_float2(f.z, f.w);
+                        }
+                    } else {
+#pragma unroll
+                        for (int m = 0; m < 8; ++m) {
+                            float e[4];
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                const int xi = xmap[16 * m + 4 * q + i];
+                                e[i] = xi >= 0 ? __ldg(rowp + xi) : (xi == -1 ? fillv : 0.f);
+                            }
+                            a[m] = make_float2(e[0], e[1]);
+                            b[m] = make_float2(e[2], e[3]);
+                        }
+                    }
+                }
+                row128_forward(a, b, plane + row * P, twr, twu, q, 0xffffffffu);
+            }
+        } else {
 #pragma unroll 1
         for (int row = rrow; row < BY; row += RPR) {
             float2 v[8];
@@ -178,6 +246,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
                 if (m == 0 && rt == 0) xk = make_float2(2.f * (v[0].x + v[0].y), 2.f * (v[0].x - v[0].y));
                 rp[L::slot(k)] = xk;
             }
+        }
         }
         __syncthreads();
 
@@ -234,6 +303,7 @@ template <int BZ> struct ZCfg {
     static constexpr int MIN_CTAS = THREADS >= 512 ? 2 : 4;
 };
 
+
 template <int BZ, int MODE>
 __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_kernel(float2* __restrict__ scratch, size_t tile_stride,
                                                                                      const float2* __restrict__ kspec,
@@ -241,7 +311,7 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
                                                                                      float scale, Twiddles tw) {
     using C = ZCfg<BZ>;
     constexpr int EPT = C::EPT, TZ = C::TZ, PW = C::PW;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     float2* xch = reinterpret_cast<float2*>(smem_raw);
     float2* twz = xch + (size_t)PW * BZ;
     const int tid = threadIdx.x;
@@ -254,7 +324,7 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
     float2 v[EPT];
 #pragma unroll
     for (int m = 0; m < EPT; ++m) v[m] = base[(size_t)(t + m * TZ) * pe];
-    float2 kv[EPT];
+    float2 kv[EPT];  // needed only after the forward transform, loaded now to overlap the latency
     if constexpr (MODE == 1) {
         const float2* __restrict__ kb = kspec + (valid ? pos : 0);
 #pragma unroll
@@ -328,7 +398,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
     using C = XYCfg<BX, BY>;
     using L = PlaneLayout<BX>;
     constexpr int H = C::H, P = L::P, TX = C::TX, RPR = C::RPR, TY = C::TY, CPR = C::CPR;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     float2* plane = reinterpret_cast<float2*>(smem_raw);
     float2* twr = plane + (size_t)BY * P;
     float2* twu = twr + H;
@@ -339,9 +409,13 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
     const int zfirst = blockIdx.x * XY_ZPC;
     if (zfirst >= tile.n[2]) return;
     const int tid = threadIdx.x;
-    for (int i = tid; i < H; i += NT) {
-        twr[i] = __ldg(&tw.t[ilog2<H>()][i]);
-        twu[i] = __ldg(&tw.t[ilog2<BX>()][i]);
+    if constexpr (BX == 128) {
+        row128_fill_tables(twr, twu, tw.t[6], tw.t[7], true, tid, NT);
+    } else {
+        for (int i = tid; i < H; i += NT) {
+            twr[i] = __ldg(&tw.t[ilog2<H>()][i]);
+            twu[i] = __ldg(&tw.t[ilog2<BX>()][i]);
+        }
     }
     const int rt = tid % TX;
     const int rrow = tid / TX;
@@ -372,6 +446,26 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
         const int zv = tile.e[2] + zr;              // plane inside the volume
         const float2* __restrict__ in = scratch + (size_t)blockIdx.y * tile_stride + (size_t)zt * ((H + 1) * BY);
 
+        if constexpr (BX == 128 && MVD_PREFETCH != 0) {
+            // pull this plane's epilogue operands and the next plane's spectrum towards L2
+            for (int yl = tid >> 2; yl < n1; yl += NT / 4) {
+                const int q = tid & 3;
+                const size_t ob = ((size_t)(zv + ep.out_off[2]) * ep.out_dim[1] + (tile.e[1] + yl + ep.out_off[1])) * (size_t)ep.out_dim[0] +
+                                  tile.e[0] + ep.out_off[0] + 32 * q;
+                const size_t ab = ((size_t)zv * ep.aux_dim[1] + (tile.e[1] + yl)) * (size_t)ep.aux_dim[0] + tile.e[0] + 32 * q;
+                if (32 * q < n0) {
+                    if constexpr (EPI == EPI_QUOTIENT) prefetch_l2(ep.img + ab);
+                    if constexpr (EPI == EPI_UPDATE) {
+                        prefetch_l2(ep.out + ob);
+                        if (ep.weight) prefetch_l2(ep.weight + ab);
+                    }
+                }
+            }
+            if (zi + 1 < XY_ZPC && zr + 1 < tile.n[2]) {
+                const float2* __restrict__ nx = in + (H + 1) * BY;
+                for (int i = tid; i < (H + 1) * BY / 16; i += NT) prefetch_l2(nx + 16 * i);
+            }
+        }
         // ---- phase 1: inverse columns; column 0 re-packs DC + i*Nyquist
 #pragma unroll 1
         for (int cr = 0; cr < C::CROUNDS; ++cr) {
@@ -400,6 +494,104 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
 
         // ---- phase 2: inverse rows (C2R through the packed half-length transform) + epilogue.
         // Only the rows of the effective region are transformed; the others would be discarded.
+        if constexpr (BX == 128) {
+            const int q = tid & 3;
+#pragma unroll 1
+            for (int yl0 = 0; yl0 < n1; yl0 += NT / 4) {
+                const int yl = yl0 + (tid >> 2);
+                // rows of the effective region come in multiples of 4, a warp holds 8 of them
+                const unsigned wmask = __ballot_sync(0xffffffffu, yl < n1);
+                if (yl >= n1) continue;
+                float2 e[8], f[8];
+                row128_inverse(e, f, plane + (ly + yl) * P, twr, twu, q, wmask);
+                // (e[m].x, e[m].y, f[m].x, f[m].y) = samples x = 16 m + 4 q .. + 3 of the window
+                const size_t rowbase = ((size_t)(zv + ep.out_off[2]) * ep.out_dim[1] + (tile.e[1] + yl + ep.out_off[1])) * (size_t)ep.out_dim[0] +
+                                       tile.e[0] + ep.out_off[0];
+                const size_t auxbase = ((size_t)zv * ep.aux_dim[1] + (tile.e[1] + yl)) * (size_t)ep.aux_dim[0] + tile.e[0];
+                const bool vec = ((rowbase | auxbase) & 3) == 0 && ((reinterpret_cast<uintptr_t>(ep.out) | reinterpret_cast<uintptr_t>(ep.img) |
+                                                                      reinterpret_cast<uintptr_t>(ep.weight)) & 15) == 0;
+                const int xq = 4 * q - lx;  // first sample of the thread's quad m = 0, in region coordinates
+                unsigned full4 = 0, part4 = 0;
+#pragma unroll
+                for (int m = 0; m < 8; ++m) {
+                    const int xl = xq + 16 * m;
+                    if (xl >= 0 && xl + 3 < n0) full4 |= 1u << m;
+                    else if (xl + 3 >= 0 && xl < n0) part4 |= 1u << m;
+                }
+                float* __restrict__ outp = ep.out + rowbase + xq;
+                const float* __restrict__ imgp = ep.img + auxbase + xq;
+                const float* __restrict__ wp = ep.weight + auxbase + xq;
+                if (vec) {
+#pragma unroll
+                    for (int h = 0; h < 8; h += 4) {  // two halves: 4 quads of loads in flight, registers stay below the cap
+                        float4 a[4], b[4];
+#pragma unroll
+                        for (int i4 = 0; i4 < 4; ++i4) {  // issue the loads before the first use
+                            const int m = h + i4;
+                            a[i4] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            b[i4] = make_float4(ep.weight_const, ep.weight_const, ep.weight_const, ep.weight_const);
+                            if (full4 >> m & 1) {
+                                if constexpr (EPI == EPI_QUOTIENT) a[i4] = __ldg(reinterpret_cast<const float4*>(imgp + 16 * m));
+                                if constexpr (EPI == EPI_UPDATE) {
+                                    a[i4] = *reinterpret_cast<const float4*>(outp + 16 * m);
+                                    if (ep.weight) b[i4] = __ldg(reinterpret_cast<const float4*>(wp + 16 * m));
+                                }
+                            }
+                        }
+#pragma unroll
+                        for (int i4 = 0; i4 < 4; ++i4) {
+                            const int m = h + i4;
+                            if (full4 >> m & 1) {
+                                const float c[4] = {e[m].x + ep.add_const, e[m].y + ep.add_const, f[m].x + ep.add_const, f[m].y + ep.add_const};
+                                const float av[4] = {a[i4].x, a[i4].y, a[i4].z, a[i4].w};
+                                const float bv[4] = {b[i4].x, b[i4].y, b[i4].z, b[i4].w};
+                                float r[4];
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    if constexpr (EPI == EPI_STORE) r[i] = c[i];
+                                    else if constexpr (EPI == EPI_QUOTIENT) r[i] = quotient_value(av[i], c[i]);
+                                    else {
+                                        r[i] = next_psi_value(av[i], c[i], bv[i], use_tik, two_lambda, inv_lambda, ep.min_value);
+                                        const float ch = fabsf(__fsub_rn(r[i], av[i]));
+                                        lsum += (double)ch;
+                                        lmax = fmaxf(lmax, ch);  // fmaxf drops NaN
+                                    }
+                                }
+                                *reinterpret_cast<float4*>(outp + 16 * m) = make_float4(r[0], r[1], r[2], r[3]);
+                            }
+                        }
+                    }
+                } else {
+                    part4 |= full4;
+                }
+                if (part4) {  // quads straddling the region border, or unaligned rows
+#pragma unroll
+                    for (int m = 0; m < 8; ++m) {
+                        if (!(part4 >> m & 1)) continue;
+                        const float c[4] = {e[m].x + ep.add_const, e[m].y + ep.add_const, f[m].x + ep.add_const, f[m].y + ep.add_const};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int x = xq + 16 * m + i;
+                            if (x < 0 || x >= n0) continue;
+                            const size_t idx = rowbase + x, aidx = auxbase + x;
+                            if constexpr (EPI == EPI_STORE) {
+                                ep.out[idx] = c[i];
+                            } else if constexpr (EPI == EPI_QUOTIENT) {
+                                ep.out[idx] = quotient_value(__ldg(ep.img + aidx), c[i]);
+                            } else {
+                                const float last = ep.out[idx];
+                                const float w = ep.weight ? __ldg(ep.weight + aidx) : ep.weight_const;
+                                const float nv = next_psi_value(last, c[i], w, use_tik, two_lambda, inv_lambda, ep.min_value);
+                                ep.out[idx] = nv;
+                                const float ch = fabsf(__fsub_rn(nv, last));
+                                lsum += (double)ch;
+                                lmax = fmaxf(lmax, ch);
+                            }
+                        }
+                    }
+                }
+            }
+        } else {
 #pragma unroll 1
         for (int yl0 = 0; yl0 < n1; yl0 += RPR) {
             const int yl = yl0 + rrow;
@@ -497,6 +689,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                     }
                 }
             }
+        }
         }
         __syncthreads();  // rows are done with the plane before the next plane's columns scatter into it
     }

@@ -178,18 +178,38 @@ Device::Device(int id) : id_(id) {
         if (v > 0) mb = (size_t)v;
     }
     scratch_budget_ = mb << 20;
+    lanes_ = 3;
+    if (const char* s = std::getenv("MVD_LANES")) {
+        const int v = std::atoi(s);
+        if (v > 0) lanes_ = std::min(v, (int)Scratch::kMaxLanes);
+    }
 }
 
-void Scratch::reserve(size_t n) {
-    if (n <= elems) return;
-    if (data) MVD_CUDA(cudaFree(data));
-    data = nullptr;
-    elems = 0;
-    MVD_CUDA(cudaMalloc(&data, n * sizeof(float2)));
-    elems = n;
+void Scratch::init(int n) {
+    if (lanes) return;
+    n = std::max(1, std::min(n, (int)kMaxLanes));
+    MVD_CUDA(cudaEventCreateWithFlags(&fork, cudaEventDisableTiming));
+    for (int i = 0; i < n; ++i) {
+        MVD_CUDA(cudaStreamCreateWithFlags(&lane[i], cudaStreamNonBlocking));
+        MVD_CUDA(cudaEventCreateWithFlags(&join[i], cudaEventDisableTiming));
+    }
+    lanes = n;
+}
+void Scratch::reserve(int i, size_t n) {
+    if (n <= elems[i]) return;
+    if (data[i]) MVD_CUDA(cudaFree(data[i]));
+    data[i] = nullptr;
+    elems[i] = 0;
+    MVD_CUDA(cudaMalloc(&data[i], n * sizeof(float2)));
+    elems[i] = n;
 }
 Scratch::~Scratch() {
-    if (data) cudaFree(data);
+    for (int i = 0; i < kMaxLanes; ++i) {
+        if (lane[i]) { cudaStreamSynchronize(lane[i]); cudaStreamDestroy(lane[i]); }
+        if (join[i]) cudaEventDestroy(join[i]);
+        if (data[i]) cudaFree(data[i]);
+    }
+    if (fork) cudaEventDestroy(fork);
 }
 
 // ---- spectra ---------------------------------------------------------------------------
@@ -272,6 +292,11 @@ Profiler::~Profiler() {
 void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spec, const Volume& src, int epilogue,
                      const EpilogueArgs& ep, Scratch& scratch, cudaStream_t st, Profiler* prof) {
     const double epi_bytes = epilogue == EPI_STORE ? 4.0 : (epilogue == EPI_QUOTIENT ? 8.0 : (ep.weight ? 12.0 : 8.0));
+    scratch.init(dev.lanes());
+    // per-kernel event timing needs the launches back to back on one stream
+    const int lanes = prof ? 1 : scratch.lanes;
+    int used = 0, next = 0;
+    if (lanes > 1) MVD_CUDA(cudaEventRecord(scratch.fork, st));
     for (size_t ci = 0; ci < plan.classes.size(); ++ci) {
         const TileClass& c = plan.classes[ci];
         const int bx = c.b[0], by = c.b[1], bz = c.b[2];
@@ -280,25 +305,40 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
         const int n = (int)c.tiles.size();
         int batch = (int)std::max<size_t>(1, dev.scratch_budget_bytes() / (te * sizeof(float2)));
         batch = std::min(batch, n);
-        scratch.reserve((size_t)batch * te);
+        if (lanes > 1) batch = std::min(batch, std::max(1, (n + lanes - 1) / lanes));  // give every lane something to do
         for (int s = 0; s < n; s += batch) {
             const int cnt = std::min(batch, n - s);
+            const int li = lanes > 1 ? next : 0;
+            next = (next + 1) % lanes;
+            cudaStream_t ls = lanes > 1 ? scratch.lane[li] : st;
+            if (lanes > 1 && !(used >> li & 1)) {
+                MVD_CUDA(cudaStreamWaitEvent(ls, scratch.fork, 0));
+                used |= 1 << li;
+            }
+            scratch.reserve(li, (size_t)batch * te);
+            float2* buf = scratch.data[li];
             double nz_sum = 0, out_vox = 0;
             if (prof)
                 for (int i = s; i < s + cnt; ++i) {
                     nz_sum += c.tiles[i].n[2];
                     out_vox += (double)c.tiles[i].n[0] * c.tiles[i].n[1] * c.tiles[i].n[2];
                 }
-            if (prof) prof->begin(0, cnt * ((double)bx * by * bz * 4.0 + pe * bz * 8.0), st);
-            MVD_CUDA(launch_fwd_xy(bx, by, bz, src, c.d_tiles + s, cnt, scratch.data, dev.twiddles(), st));
-            if (prof) { prof->end(st); prof->begin(1, cnt * pe * bz * 8.0 + pe * bz * 8.0 + nz_sum * pe * 8.0, st); }
-            MVD_CUDA(launch_z_pass(bx, by, bz, 1, scratch.data, spec.per_class[ci], c.d_tiles + s, cnt, 1.f, dev.twiddles(), st));
-            if (prof) { prof->end(st); prof->begin(2, nz_sum * pe * 8.0 + out_vox * epi_bytes, st); }
-            MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, scratch.data, c.d_tiles + s, cnt, c.max_nz, ep, dev.twiddles(), st));
-            if (prof) prof->end(st);
+            if (prof) prof->begin(0, cnt * ((double)bx * by * bz * 4.0 + pe * bz * 8.0), ls);
+            MVD_CUDA(launch_fwd_xy(bx, by, bz, src, c.d_tiles + s, cnt, buf, dev.twiddles(), ls));
+            if (prof) { prof->end(ls); prof->begin(1, cnt * pe * bz * 8.0 + pe * bz * 8.0 + nz_sum * pe * 8.0, ls); }
+            MVD_CUDA(launch_z_pass(bx, by, bz, 1, buf, spec.per_class[ci], c.d_tiles + s, cnt, 1.f, dev.twiddles(), ls));
+            if (prof) { prof->end(ls); prof->begin(2, nz_sum * pe * 8.0 + out_vox * epi_bytes, ls); }
+            MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, buf, c.d_tiles + s, cnt, c.max_nz, ep, dev.twiddles(), ls));
+            if (prof) prof->end(ls);
             g_kernel_launches += 3;
         }
     }
+    if (lanes > 1)
+        for (int li = 0; li < lanes; ++li)
+            if (used >> li & 1) {
+                MVD_CUDA(cudaEventRecord(scratch.join[li], scratch.lane[li]));
+                MVD_CUDA(cudaStreamWaitEvent(st, scratch.join[li], 0));
+            }
 }
 
 }  // namespace mvd

@@ -71,6 +71,7 @@ public:
     int id() const { return id_; }
     const TwiddleTables& twiddles() const { return tw_; }
     size_t scratch_budget_bytes() const { return scratch_budget_; }
+    int lanes() const { return lanes_; }
     std::mutex legacy_mutex;  // serialises the drop-in symbol per device
 
 private:
@@ -78,14 +79,27 @@ private:
     int id_;
     TwiddleTables tw_{};
     size_t scratch_budget_;
+    int lanes_ = 1;
 };
 
-// Scratch for the tile batches of one stream.
+// Scratch for the tile batches of one convolution stream.  Tile batches are independent, so they
+// are dealt round-robin to `lanes` auxiliary streams (each with its own scratch buffer): while one
+// batch sits in its latency-bound z pass another one runs its shared-memory-bound xy pass on the
+// same SMs.  The lanes fork from / join into the caller's stream with events.
 struct Scratch {
-    float2* data = nullptr;
-    size_t elems = 0;
-    void reserve(size_t n);
+    static constexpr int kMaxLanes = 4;
+    float2* data[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
+    size_t elems[kMaxLanes] = {0, 0, 0, 0};
+    cudaStream_t lane[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t fork = nullptr;
+    cudaEvent_t join[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
+    int lanes = 0;  // 0 = not initialised
+    void init(int n);
+    void reserve(int lane_index, size_t n);
     ~Scratch();
+    Scratch() = default;
+    Scratch(const Scratch&) = delete;
+    Scratch& operator=(const Scratch&) = delete;
 };
 
 // Optional per-kernel timing with CUDA events on the launching stream (bench.py roofline).
