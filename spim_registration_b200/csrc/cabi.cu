@@ -54,12 +54,16 @@ template <class F> static int guarded(F&& f) {
 extern "C" int mvdGetLastError(char* buf, int n) {
     int code = t_err_code;
     std::string msg = t_err;
-    if (code == 0) {
+    {
         std::lock_guard<std::mutex> lk(g_err_mutex);
-        code = g_err_code;
-        msg = g_err;
-        g_err_code = 0;
-        g_err.clear();
+        if (code == 0) {  // nothing failed on this thread: report the last failure of any thread
+            code = g_err_code;
+            msg = g_err;
+        }
+        if (code == 0 || g_err == msg) {  // the process-wide latch holds the error just reported
+            g_err_code = 0;
+            g_err.clear();
+        }
     }
     t_err_code = 0;
     t_err.clear();
