@@ -200,3 +200,97 @@ class ShardedDeconvolution:
         if self.ctx:
             self.lib.mvdDestroy(self.ctx)
             self.ctx = None
+
+
+class LocalBrickGroup:
+    """All bricks of a grid on ONE device, stepped in lock-step with in-process ghost copies -- the
+    same library calls and the same exchange schedule as the multi-process path, without
+    torch.distributed.  Used by the single-GPU parity test of the brick/ghost code paths."""
+
+    def __init__(self, dim_xyz, grid, imgs, weights, kernel1, kernel2, lam, device=0):
+        import torch
+        self.torch = torch
+        self.grid, self.dim = tuple(grid), tuple(dim_xyz)
+        self.world = grid[0] * grid[1] * grid[2]
+        self.bricks = []
+        for r in range(self.world):
+            off, size, _ = brick_of(r, self.grid, self.dim)
+            sl = tuple(slice(off[d], off[d] + size[d]) for d in (2, 1, 0))
+            bi = [np.ascontiguousarray(i[sl]) for i in imgs]
+            bw = [w if (w is None or np.isscalar(w)) else np.ascontiguousarray(w[sl]) for w in weights]
+            d = ShardedDeconvolution.__new__(ShardedDeconvolution)
+            _init_brick(d, self.dim, bi, bw, kernel1, kernel2, lam, device, self.grid, r, self.world)
+            self.bricks.append(d)
+
+    def _exchange(self, which):
+        # axis by axis, full-extent slabs (edges and corners travel through the later axes)
+        for axis in (0, 1, 2):
+            dimt = 2 - axis
+            for b in self.bricks:
+                g = b.ghost[axis]
+                if g == 0 or self.grid[axis] == 1:
+                    continue
+                t, off = b._arrays[which]
+                o, n = off[dimt], b.size[axis]
+                for side in (-1, 1):
+                    nc = list(b.coords)
+                    nc[axis] += side
+                    if nc[axis] < 0 or nc[axis] >= self.grid[axis]:
+                        continue
+                    peer = self.bricks[rank_of(nc, self.grid)]
+                    pt, poff = peer._arrays[which]
+                    po, pn = poff[dimt], peer.size[axis]
+                    if side < 0:
+                        t.narrow(dimt, o - g, g).copy_(pt.narrow(dimt, po + pn - g, g))
+                    else:
+                        t.narrow(dimt, o + n, g).copy_(pt.narrow(dimt, po, g))
+
+    def init_psi_average(self):
+        import ctypes as C
+        tot, cnt = 0.0, 0
+        for b in self.bricks:
+            s, n = C.c_double(), C.c_longlong()
+            b.L.check(b.lib.mvdFirstIterationSums(b.ctx, C.byref(s), C.byref(n)), "mvdFirstIterationSums")
+            tot += s.value
+            cnt += n.value
+        avg = tot / cnt if cnt else 0.5
+        for b in self.bricks:
+            b.L.check(b.lib.mvdFillPsi(b.ctx, avg), "mvdFillPsi")
+        return avg
+
+    def run_iterations(self, n):
+        V = self.bricks[0].V
+        for _ in range(n):
+            for v in range(V):
+                for b in self.bricks:
+                    b.L.check(b.lib.mvdStepQuotient(b.ctx, v), "mvdStepQuotient")
+                self.torch.cuda.synchronize()
+                self._exchange(1)
+                for b in self.bricks:
+                    b.L.check(b.lib.mvdStepUpdate(b.ctx, v, b.slot), "mvdStepUpdate")
+                    b.slot += 1
+                self.torch.cuda.synchronize()
+                self._exchange(0)
+
+    def get_psi(self):
+        out = np.empty(self.dim[::-1], dtype=np.float32)
+        for b in self.bricks:
+            b.mask_never_updated()
+            sl = tuple(slice(b.off[d], b.off[d] + b.size[d]) for d in (2, 1, 0))
+            out[sl] = b.get_psi_brick()
+        return out
+
+    def close(self):
+        for b in self.bricks:
+            b.close()
+
+
+def _init_brick(d, dim_xyz, imgs, weights, kernel1, kernel2, lam, device, grid, rank, world):
+    """ShardedDeconvolution.__init__ for an explicit (rank, world) without a process group."""
+    class _FakeDist:
+        def get_world_size(self):
+            return world
+
+        def get_rank(self):
+            return rank
+    ShardedDeconvolution.__init__(d, dim_xyz, imgs, weights, kernel1, kernel2, lam, _FakeDist(), device, grid=grid)

@@ -225,3 +225,26 @@ def test_config1_full_size(m, o):
     ref, stats, avg = o.run_deconvolution(ds["imgs"], w, k1, k2, iters, 0.006)
     dec = m.MVDeconvolution(_views(m, ds["imgs"], [float(x) for x in w], ds["psfs"]), "EFFICIENT_BAYESIAN", iters, 0.006)
     assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
+
+
+@pytest.mark.parametrize("grid", [(2, 1, 1), (1, 2, 2), (2, 2, 2)])
+def test_bricks_with_ghost_layers_equal_whole_volume(m, o, grid):
+    """The brick / ghost-layer code paths of the library (what every rank of the multi-GPU run
+    executes) on one device: all bricks stepped in lock-step with in-process ghost copies must
+    reproduce the single-context result and the oracle."""
+    from spim_registration_b200 import synthetic
+    from spim_registration_b200.parallel import LocalBrickGroup
+    shape, V, iters = (40, 56, 72), 2, 2
+    ds = _dataset(o, shape, V, (9, 7, 11), seed=3)
+    weights = synthetic.blending_weights(shape, V)
+    k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
+    ref, _, avg = o.run_deconvolution(ds["imgs"], weights, k1, k2, iters, 0.006)
+    grp = LocalBrickGroup(shape[::-1], grid, ds["imgs"], weights, k1, k2, 0.006)
+    try:
+        assert abs(grp.init_psi_average() - avg) <= 1e-9 * abs(avg)
+        grp._exchange(0)
+        grp.run_iterations(iters)
+        got = grp.get_psi()
+    finally:
+        grp.close()
+    assert rel_l2(got, ref) <= LOOP_TOL
