@@ -22,6 +22,8 @@
 #include "fft_device.cuh"
 #include "row128.cuh"
 
+#include <algorithm>
+
 namespace mvd {
 
 static constexpr int NT = 256;  // threads per CTA of the xy kernels
@@ -103,7 +105,7 @@ template <int BX, int BY> struct XYCfg {
 template <int BX, int BY>
 __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Volume src, const Tile* __restrict__ tiles,
                                                                            float2* __restrict__ scratch, size_t tile_stride, int bz,
-                                                                           Twiddles tw) {
+                                                                           int n_items, Twiddles tw) {
     using C = XYCfg<BX, BY>;
     using L = PlaneLayout<BX>;
     constexpr int H = C::H, P = L::P, TX = C::TX, RPR = C::RPR, TY = C::TY, CPR = C::CPR;
@@ -114,10 +116,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
     float2* col0 = twu + H;                 // staging of column 0 (DC + i Nyquist)
     int* xmap = reinterpret_cast<int*>(col0 + BY);
 
-    const Tile tile = tiles[blockIdx.y];
     const int tid = threadIdx.x;
-    const int z0 = blockIdx.x * XY_ZPC;
-
     // ---- per-CTA setup
     if constexpr (BX == 128) {
         row128_fill_tables(twr, twu, tw.t[6], tw.t[7], false, tid, NT);
@@ -127,13 +126,22 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
             twu[i] = __ldg(&tw.t[ilog2<BX>()][i]);
         }
     }
+    const float fillv = src.ext == EXT_CONST ? src.ext_value : 0.f;
+    const int chunks = (bz + XY_ZPC - 1) / XY_ZPC;
+    // work items = (tile, chunk of XY_ZPC planes), chunk fastest; the grid may be smaller than the
+    // item count (persistent CTAs) so that CTAs of other kernels fit beside this one on the SM
+#pragma unroll 1
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const int ti = item / chunks;
+    const Tile tile = tiles[ti];
+    const int z0 = (item - ti * chunks) * XY_ZPC;
+    __syncthreads();  // the previous item is done with xmap and the plane
     for (int i = tid; i < BX; i += NT) xmap[i] = map_coord(tile.o[0] + i, src.dim[0], src.off[0], src.gmin[0], src.gdim[0], src.ext);
     const int xo = tile.o[0] + src.off[0];  // array index of the window start
     const int xg = tile.o[0] + src.gmin[0];
     // whole window inside the array and inside the global domain, rows 8-byte aligned
     const bool xfast = xo >= 0 && xo + BX <= src.dim[0] && xg >= 0 && xg + BX <= src.gdim[0] && ((xo | src.dim[0]) & 1) == 0 &&
                        (reinterpret_cast<uintptr_t>(src.data) & 7) == 0;
-    const float fillv = src.ext == EXT_CONST ? src.ext_value : 0.f;
     __syncthreads();
 
     // row phase thread mapping
@@ -164,7 +172,15 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
                     }
                 }
             }
-            const bool xfast4 = xfast && ((xo | src.dim[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(src.data) & 15) == 0;
+            // quads (4 consecutive samples) of this thread that lie inside the array and the global
+            // domain are loaded as float4 even in tiles that touch the volume border
+            const bool al4 = ((xo | src.dim[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(src.data) & 15) == 0;
+            unsigned qmask = 0;
+#pragma unroll
+            for (int m = 0; m < 8; ++m) {
+                const int xa = xo + 16 * m + 4 * q, xgl = xg + 16 * m + 4 * q;
+                if (al4 && xa >= 0 && xa + 3 < src.dim[0] && xgl >= 0 && xgl + 3 < src.gdim[0]) qmask |= 1u << m;
+            }
 #pragma unroll 1
             for (int row = tid >> 2; row < BY; row += NT / 4) {
                 float2 a[8], b[8];
@@ -175,17 +191,14 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
                     for (int m = 0; m < 8; ++m) a[m] = b[m] = make_float2(f, f);
                 } else {
                     const float* __restrict__ rowp = zbase + (size_t)yl * src.dim[0];
-                    if (xfast4) {
-                        const float4* __restrict__ p4 = reinterpret_cast<const float4*>(rowp + xo) + q;
+                    const float4* __restrict__ p4 = reinterpret_cast<const float4*>(rowp + xo) + q;
 #pragma unroll
-                        for (int m = 0; m < 8; ++m) {
+                    for (int m = 0; m < 8; ++m) {
+                        if (qmask >> m & 1) {
                             const float4 f = __ldg(p4 + 4 * m);
                             a[m] = make_float2(f.x, f.y);
                             b[m] = make_float2(f.z, f.w);
-                        }
-                    } else {
-#pragma unroll
-                        for (int m = 0; m < 8; ++m) {
+                        } else {
                             float e[4];
 #pragma unroll
                             for (int i = 0; i < 4; ++i) {
@@ -251,7 +264,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
         __syncthreads();
 
         // ---- phase 2: columns (H packed columns), write out H unpacked columns + the Nyquist column
-        float2* __restrict__ out = scratch + (size_t)blockIdx.y * tile_stride + (size_t)z * ((H + 1) * BY);
+        float2* __restrict__ out = scratch + (size_t)ti * tile_stride + (size_t)z * ((H + 1) * BY);
 #pragma unroll 1
         for (int cr = 0; cr < C::CROUNDS; ++cr) {
             const int col = cr * CPR + cc;
@@ -285,6 +298,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
         }
         // the next plane's row phase rewrites the plane: all column gathers are complete (barrier above)
     }
+    }  // items
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -295,20 +309,23 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
 // z index); a z line is shared by TZ threads with EPT elements each.  The grid is ordered tile
 // fastest so that concurrently running CTAs read the same part of the kernel spectrum (L2 hits).
 template <int BZ> struct ZCfg {
-    static constexpr int EPT = BZ >= 8 ? 8 : BZ;
+    // two passes with ONE exchange each way: 512 = 32 x 16, 256 = 16 x 16, 128 = 16 x 8, 64 = 8 x 8, ...
+    static constexpr int EPT = BZ >= 512 ? 32 : (BZ >= 128 ? 16 : 8);
     static constexpr int TZ = BZ / EPT;
-    static constexpr int THREADS = BZ >= 256 ? 512 : 256;
-    static constexpr int PW = THREADS / TZ;
+#ifndef MVD_Z_PW
+#define MVD_Z_PW 16
+#endif
+    static constexpr int PW = MVD_Z_PW;  // 8 (16): 64 (128) contiguous bytes per z index; small CTAs keep more of them in different phases
+    static constexpr int THREADS = PW * TZ;
     static constexpr size_t SMEM = (size_t)PW * BZ * sizeof(float2) + (size_t)BZ * sizeof(float2);
-    static constexpr int MIN_CTAS = THREADS >= 512 ? 2 : 4;
+    static constexpr int MIN_CTAS = EPT == 32 ? 512 / THREADS : (THREADS >= 256 ? 3 : 4);
 };
-
 
 template <int BZ, int MODE>
 __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_kernel(float2* __restrict__ scratch, size_t tile_stride,
                                                                                      const float2* __restrict__ kspec,
                                                                                      const Tile* __restrict__ tiles, int plane_elems,
-                                                                                     float scale, Twiddles tw) {
+                                                                                     float scale, int n_tiles, int n_items, Twiddles tw) {
     using C = ZCfg<BZ>;
     constexpr int EPT = C::EPT, TZ = C::TZ, PW = C::PW;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -316,22 +333,29 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
     float2* twz = xch + (size_t)PW * BZ;
     const int tid = threadIdx.x;
     const int p = tid % PW, t = tid / PW;
-    const int pos = blockIdx.y * PW + p;
-    const bool valid = pos < plane_elems;
     const size_t pe = (size_t)plane_elems;
-    float2* __restrict__ base = scratch + (size_t)blockIdx.x * tile_stride + (valid ? pos : 0);
+    for (int i = tid; i < BZ; i += C::THREADS) twz[i] = __ldg(&tw.t[ilog2<BZ>()][i]);
+    // work items = (position block, tile), tile fastest
+#pragma unroll 1
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const int pblk = item / n_tiles, ti = item - pblk * n_tiles;
+    const int pos = pblk * PW + p;
+    const bool valid = pos < plane_elems;
+    float2* __restrict__ base = scratch + (size_t)ti * tile_stride + (valid ? pos : 0);
 
     float2 v[EPT];
 #pragma unroll
     for (int m = 0; m < EPT; ++m) v[m] = base[(size_t)(t + m * TZ) * pe];
-    float2 kv[EPT];  // needed only after the forward transform, loaded now to overlap the latency
+    // the kernel spectrum is needed only after the forward transform: pull its lines towards L2
+    // now (no registers held; one lane per 128-byte line), read them then
+    const float2* __restrict__ kb = kspec + (valid ? pos : 0);
     if constexpr (MODE == 1) {
-        const float2* __restrict__ kb = kspec + (valid ? pos : 0);
+        if ((p & 15) == 0) {
 #pragma unroll
-        for (int m = 0; m < EPT; ++m) kv[m] = __ldg(kb + (size_t)(t + m * TZ) * pe);
+            for (int m = 0; m < EPT; ++m) prefetch_l2(kb + (size_t)(t + m * TZ) * pe);
+        }
     }
-    for (int i = tid; i < BZ; i += C::THREADS) twz[i] = __ldg(&tw.t[ilog2<BZ>()][i]);
-    __syncthreads();
+    __syncthreads();  // twiddle table ready; the previous item is done with the exchange buffer
 
     float2* __restrict__ xp = xch + p;
     auto put = [&](int idx, float2 val) { xp[idx * PW] = val; };
@@ -346,10 +370,10 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
         }
     } else {
 #pragma unroll
-        for (int m = 0; m < EPT; ++m) v[m] = cmul(v[m], kv[m]);
+        for (int m = 0; m < EPT; ++m) v[m] = cmul(v[m], __ldg(kb + (size_t)(t + m * TZ) * pe));
         if constexpr (TZ > 1) __syncthreads();
         line_fft<BZ, EPT, true>(v, t, twz, put, get, sync);
-        const Tile tile = tiles[blockIdx.x];
+        const Tile tile = tiles[ti];
         const int zlo = tile.e[2] - tile.o[2], zhi = zlo + tile.n[2];
         if (valid) {
 #pragma unroll
@@ -359,6 +383,7 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
             }
         }
     }
+    }  // items
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -394,7 +419,8 @@ __device__ __forceinline__ float next_psi_value(float last, float integral, floa
 
 template <int BX, int BY, int EPI>
 __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(const float2* __restrict__ scratch, size_t tile_stride,
-                                                                           const Tile* __restrict__ tiles, EpilogueArgs ep, Twiddles tw) {
+                                                                           const Tile* __restrict__ tiles, EpilogueArgs ep, int chunks,
+                                                                           int n_items, Twiddles tw) {
     using C = XYCfg<BX, BY>;
     using L = PlaneLayout<BX>;
     constexpr int H = C::H, P = L::P, TX = C::TX, RPR = C::RPR, TY = C::TY, CPR = C::CPR;
@@ -405,9 +431,6 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
     __shared__ double s_sum[NT / 32];
     __shared__ float s_max[NT / 32];
 
-    const Tile tile = tiles[blockIdx.y];
-    const int zfirst = blockIdx.x * XY_ZPC;
-    if (zfirst >= tile.n[2]) return;
     const int tid = threadIdx.x;
     if constexpr (BX == 128) {
         row128_fill_tables(twr, twu, tw.t[6], tw.t[7], true, tid, NT);
@@ -422,12 +445,20 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
     const int cc = tid % CPR;
     const int cu = tid / CPR;
     const ConstTw128 twc{7 - ilog2<BY>()};
-    const int lx = tile.e[0] - tile.o[0], ly = tile.e[1] - tile.o[1];
-    const int n0 = tile.n[0], n1 = tile.n[1];
     const bool use_tik = ep.lambda > 0.0;
     const double two_lambda = 2.0 * ep.lambda, inv_lambda = use_tik ? 1.0 / ep.lambda : 0.0;
     double lsum = 0.0;
     float lmax = 0.f;
+    __syncthreads();
+    // work items = (tile, chunk of XY_ZPC effective planes), chunk fastest (see fwd_xy_kernel)
+#pragma unroll 1
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const int ti = item / chunks;
+    const Tile tile = tiles[ti];
+    const int zfirst = (item - ti * chunks) * XY_ZPC;
+    if (zfirst >= tile.n[2]) continue;
+    const int lx = tile.e[0] - tile.o[0], ly = tile.e[1] - tile.o[1];
+    const int n0 = tile.n[0], n1 = tile.n[1];
     // x pairs owned by this thread: x = 2*(rt + m*TX) - lx, +1; classify once (lx is a multiple of 4)
     unsigned full = 0, part = 0;
 #pragma unroll
@@ -436,7 +467,6 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
         if (xl >= 0 && xl + 1 < n0) full |= 1u << m;
         else if (xl + 1 == 0 || xl == n0 - 1) part |= 1u << m;
     }
-    __syncthreads();
 
 #pragma unroll 1
     for (int zi = 0; zi < XY_ZPC; ++zi) {
@@ -444,7 +474,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
         if (zr >= tile.n[2]) break;
         const int zt = tile.e[2] - tile.o[2] + zr;  // plane inside the tile
         const int zv = tile.e[2] + zr;              // plane inside the volume
-        const float2* __restrict__ in = scratch + (size_t)blockIdx.y * tile_stride + (size_t)zt * ((H + 1) * BY);
+        const float2* __restrict__ in = scratch + (size_t)ti * tile_stride + (size_t)zt * ((H + 1) * BY);
 
         if constexpr (BX == 128 && MVD_PREFETCH != 0) {
             // pull this plane's epilogue operands and the next plane's spectrum towards L2
@@ -503,6 +533,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                 const unsigned wmask = __ballot_sync(0xffffffffu, yl < n1);
                 if (yl >= n1) continue;
                 float2 e[8], f[8];
+                float rsum = 0.f;  // |change| of this thread's <= 32 voxels of the row, added to the double sum once
                 row128_inverse(e, f, plane + (ly + yl) * P, twr, twu, q, wmask);
                 // (e[m].x, e[m].y, f[m].x, f[m].y) = samples x = 16 m + 4 q .. + 3 of the window
                 const size_t rowbase = ((size_t)(zv + ep.out_off[2]) * ep.out_dim[1] + (tile.e[1] + yl + ep.out_off[1])) * (size_t)ep.out_dim[0] +
@@ -553,7 +584,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                                     else {
                                         r[i] = next_psi_value(av[i], c[i], bv[i], use_tik, two_lambda, inv_lambda, ep.min_value);
                                         const float ch = fabsf(__fsub_rn(r[i], av[i]));
-                                        lsum += (double)ch;
+                                        rsum += ch;
                                         lmax = fmaxf(lmax, ch);  // fmaxf drops NaN
                                     }
                                 }
@@ -584,12 +615,13 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                                 const float nv = next_psi_value(last, c[i], w, use_tik, two_lambda, inv_lambda, ep.min_value);
                                 ep.out[idx] = nv;
                                 const float ch = fabsf(__fsub_rn(nv, last));
-                                lsum += (double)ch;
+                                rsum += ch;
                                 lmax = fmaxf(lmax, ch);
                             }
                         }
                     }
                 }
+                if constexpr (EPI == EPI_UPDATE) lsum += (double)rsum;
             }
         } else {
 #pragma unroll 1
@@ -693,6 +725,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
         }
         __syncthreads();  // rows are done with the plane before the next plane's columns scatter into it
     }
+    }  // items
     if constexpr (EPI == EPI_UPDATE) {
         if (ep.sum_change) {
 #pragma unroll
@@ -714,6 +747,12 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
 
 // ---------------------------------------------------------------------------------------------
 // host launchers
+// grid caps (0 = one CTA per work item): with several batch streams the kernels run as persistent
+// grids of a fraction of the SMs' capacity, so CTAs of different kernels share an SM
+int g_xy_grid_cap = 0;
+int g_z_grid_cap = 0;
+void set_grid_caps(int xy_cap, int z_cap) { g_xy_grid_cap = xy_cap; g_z_grid_cap = z_cap; }
+
 bool xy_size_supported(int b) { return b == 32 || b == 64 || b == 128; }
 bool z_size_supported(int b) { return b == 16 || b == 32 || b == 64 || b == 128 || b == 256 || b == 512; }
 size_t plane_elems(int bx, int by) { return (size_t)(bx / 2 + 1) * by; }
@@ -779,8 +818,9 @@ cudaError_t launch_fwd_xy(int bx, int by, int bz, const Volume& src, const Tile*
                           const TwiddleTables& tw, cudaStream_t st) {
     if (n_tiles <= 0) return cudaSuccess;
     const size_t stride = tile_scratch_elems(bx, by, bz);
-    const dim3 grid((bz + XY_ZPC - 1) / XY_ZPC, n_tiles);
-#define F(BX, BY) fwd_xy_kernel<BX, BY><<<grid, NT, XYCfg<BX, BY>::SMEM_FWD, st>>>(src, d_tiles, scratch, stride, bz, to_dev(tw))
+    const int n_items = ((bz + XY_ZPC - 1) / XY_ZPC) * n_tiles;
+    const int grid = g_xy_grid_cap > 0 ? std::min(n_items, g_xy_grid_cap) : n_items;
+#define F(BX, BY) fwd_xy_kernel<BX, BY><<<grid, NT, XYCfg<BX, BY>::SMEM_FWD, st>>>(src, d_tiles, scratch, stride, bz, n_items, to_dev(tw))
     MVD_XY_DISPATCH(bx, by, F);
 #undef F
     return cudaGetLastError();
@@ -793,9 +833,10 @@ cudaError_t launch_z_pass(int bx, int by, int bz, int mode, float2* scratch, con
     const int pe = (int)plane_elems(bx, by);
 #define F(BZ)                                                                                                          \
     {                                                                                                                  \
-        const dim3 grid(n_tiles, (pe + ZCfg<BZ>::PW - 1) / ZCfg<BZ>::PW);                                              \
-        if (mode == 0) z_pass_kernel<BZ, 0><<<grid, ZCfg<BZ>::THREADS, ZCfg<BZ>::SMEM, st>>>(scratch, stride, kspec, d_tiles, pe, scale, to_dev(tw)); \
-        else z_pass_kernel<BZ, 1><<<grid, ZCfg<BZ>::THREADS, ZCfg<BZ>::SMEM, st>>>(scratch, stride, kspec, d_tiles, pe, scale, to_dev(tw)); \
+        const int n_items = n_tiles * ((pe + ZCfg<BZ>::PW - 1) / ZCfg<BZ>::PW);                                        \
+        const int grid = g_z_grid_cap > 0 ? std::min(n_items, g_z_grid_cap) : n_items;                                 \
+        if (mode == 0) z_pass_kernel<BZ, 0><<<grid, ZCfg<BZ>::THREADS, ZCfg<BZ>::SMEM, st>>>(scratch, stride, kspec, d_tiles, pe, scale, n_tiles, n_items, to_dev(tw)); \
+        else z_pass_kernel<BZ, 1><<<grid, ZCfg<BZ>::THREADS, ZCfg<BZ>::SMEM, st>>>(scratch, stride, kspec, d_tiles, pe, scale, n_tiles, n_items, to_dev(tw)); \
     }
     MVD_Z_DISPATCH(bz, F);
 #undef F
@@ -806,13 +847,15 @@ cudaError_t launch_inv_xy(int bx, int by, int bz, int epilogue, const float2* sc
                           const EpilogueArgs& ep, const TwiddleTables& tw, cudaStream_t st) {
     if (n_tiles <= 0 || max_nz <= 0) return cudaSuccess;
     const size_t stride = tile_scratch_elems(bx, by, bz);
-    const dim3 grid((max_nz + XY_ZPC - 1) / XY_ZPC, n_tiles);
+    const int chunks = (max_nz + XY_ZPC - 1) / XY_ZPC;
+    const int n_items = chunks * n_tiles;
+    const int grid = g_xy_grid_cap > 0 ? std::min(n_items, g_xy_grid_cap) : n_items;
 #define F(BX, BY)                                                                                                        \
     {                                                                                                                    \
         constexpr size_t sm = XYCfg<BX, BY>::SMEM_INV;                                                                       \
-        if (epilogue == EPI_STORE) inv_xy_kernel<BX, BY, EPI_STORE><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, to_dev(tw)); \
-        else if (epilogue == EPI_QUOTIENT) inv_xy_kernel<BX, BY, EPI_QUOTIENT><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, to_dev(tw)); \
-        else inv_xy_kernel<BX, BY, EPI_UPDATE><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, to_dev(tw)); \
+        if (epilogue == EPI_STORE) inv_xy_kernel<BX, BY, EPI_STORE><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else if (epilogue == EPI_QUOTIENT) inv_xy_kernel<BX, BY, EPI_QUOTIENT><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else inv_xy_kernel<BX, BY, EPI_UPDATE><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
     }
     MVD_XY_DISPATCH(bx, by, F);
 #undef F

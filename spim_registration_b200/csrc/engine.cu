@@ -183,6 +183,11 @@ Device::Device(int id) : id_(id) {
         const int v = std::atoi(s);
         if (v > 0) lanes_ = std::min(v, (int)Scratch::kMaxLanes);
     }
+    // MVD_XY_CTAS / MVD_Z_CTAS: CTAs per SM of the persistent xy / z grids (0 = one CTA per item)
+    int xy = 0, z = 0;
+    if (const char* s = std::getenv("MVD_XY_CTAS")) xy = std::atoi(s);
+    if (const char* s = std::getenv("MVD_Z_CTAS")) z = std::atoi(s);
+    set_grid_caps(xy * prop.multiProcessorCount, z * prop.multiProcessorCount);
 }
 
 void Scratch::init(int n) {

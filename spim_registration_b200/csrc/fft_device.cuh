@@ -92,12 +92,39 @@ template <bool INV> __device__ __forceinline__ void dft16(float2* x) {
         }
 }
 
+template <bool INV> __device__ __forceinline__ void dft32(float2* x) {
+    // even / odd radix-16, then X[k] = E[k] + w32^k O[k], X[k+16] = E[k] - w32^k O[k]
+    float2 e[16], o[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { e[i] = x[2 * i]; o[i] = x[2 * i + 1]; }
+    dft16<INV>(e);
+    dft16<INV>(o);
+    const float sg = INV ? -1.f : 1.f;  // conjugate the forward twiddles for the inverse
+    { const float2 t = o[0]; x[0] = cadd(e[0], t); x[16] = csub(e[0], t); }
+    { const float2 t = cmul(o[1], make_float2(0.98078528040323043f, sg * -0.19509032201612825f)); x[1] = cadd(e[1], t); x[17] = csub(e[1], t); }
+    { const float2 t = cmul(o[2], make_float2(0.92387953251128674f, sg * -0.38268343236508978f)); x[2] = cadd(e[2], t); x[18] = csub(e[2], t); }
+    { const float2 t = cmul(o[3], make_float2(0.83146961230254524f, sg * -0.55557023301960218f)); x[3] = cadd(e[3], t); x[19] = csub(e[3], t); }
+    { const float2 t = cmul(o[4], make_float2(0.70710678118654757f, sg * -0.70710678118654746f)); x[4] = cadd(e[4], t); x[20] = csub(e[4], t); }
+    { const float2 t = cmul(o[5], make_float2(0.55557023301960229f, sg * -0.83146961230254524f)); x[5] = cadd(e[5], t); x[21] = csub(e[5], t); }
+    { const float2 t = cmul(o[6], make_float2(0.38268343236508984f, sg * -0.92387953251128674f)); x[6] = cadd(e[6], t); x[22] = csub(e[6], t); }
+    { const float2 t = cmul(o[7], make_float2(0.19509032201612833f, sg * -0.98078528040323043f)); x[7] = cadd(e[7], t); x[23] = csub(e[7], t); }
+    { const float2 t = mul_mi<INV>(o[8]); x[8] = cadd(e[8], t); x[24] = csub(e[8], t); }
+    { const float2 t = cmul(o[9], make_float2(-0.19509032201612819f, sg * -0.98078528040323043f)); x[9] = cadd(e[9], t); x[25] = csub(e[9], t); }
+    { const float2 t = cmul(o[10], make_float2(-0.38268343236508973f, sg * -0.92387953251128674f)); x[10] = cadd(e[10], t); x[26] = csub(e[10], t); }
+    { const float2 t = cmul(o[11], make_float2(-0.55557023301960196f, sg * -0.83146961230254546f)); x[11] = cadd(e[11], t); x[27] = csub(e[11], t); }
+    { const float2 t = cmul(o[12], make_float2(-0.70710678118654746f, sg * -0.70710678118654757f)); x[12] = cadd(e[12], t); x[28] = csub(e[12], t); }
+    { const float2 t = cmul(o[13], make_float2(-0.83146961230254535f, sg * -0.55557023301960218f)); x[13] = cadd(e[13], t); x[29] = csub(e[13], t); }
+    { const float2 t = cmul(o[14], make_float2(-0.92387953251128674f, sg * -0.38268343236508989f)); x[14] = cadd(e[14], t); x[30] = csub(e[14], t); }
+    { const float2 t = cmul(o[15], make_float2(-0.98078528040323043f, sg * -0.19509032201612861f)); x[15] = cadd(e[15], t); x[31] = csub(e[15], t); }
+}
+
 template <int R, bool INV> __device__ __forceinline__ void dftR(float2* x) {
-    static_assert(R == 2 || R == 4 || R == 8 || R == 16, "unsupported radix");
+    static_assert(R == 2 || R == 4 || R == 8 || R == 16 || R == 32, "unsupported radix");
     if constexpr (R == 2) dft2<INV>(x[0], x[1]);
     else if constexpr (R == 4) dft4<INV>(x[0], x[1], x[2], x[3]);
     else if constexpr (R == 8) dft8<INV>(x);
-    else dft16<INV>(x);
+    else if constexpr (R == 16) dft16<INV>(x);
+    else dft32<INV>(x);
 }
 
 // twiddle tables in global memory: tw_N[n] = exp(-2*pi*i*n/N), filled by the host in double precision
