@@ -212,9 +212,12 @@ def run_ours(args, cfg):
             torch.cuda.synchronize()
 
     # ---- device-resident throughput (`value`) ------------------------------------------------
+    fused = world > 1 and os.environ.get("MVD_HALO", "fused") == "fused"
     dec = ShardedDeconvolution(dim_xyz, imgs, weights, k1, k2, LAMBDA, dz, dev_index, grid=grid)
     dec.init_psi_average()
-    if world > 1:
+    if fused:
+        dec.attach_peers()  # step kernels store ghost voxels into the neighbours' arrays over NVLink
+    elif world > 1:
         dec._exchange(0)
     for _ in range(args.warmup):
         dec.run_iterations(1)
@@ -270,7 +273,9 @@ def run_ours(args, cfg):
     t0 = time.perf_counter()
     dec = ShardedDeconvolution(dim_xyz, np_imgs, np_w, k1, k2, LAMBDA, dz, dev_index, grid=grid)  # H2D of every view
     dec.init_psi_average()
-    if world > 1:
+    if fused:
+        dec.attach_peers()
+    elif world > 1:
         dec._exchange(0)
     dec.run_iterations(args.steps)
     dec.mask_never_updated()
@@ -300,6 +305,7 @@ def run_ours(args, cfg):
         "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": cfg["name"], "views": V, "volume_xyz": list(dim_xyz), "psf": cfg["k"], "iteration_type": cfg["psftype"],
                    "lambda": LAMBDA, "step": "one iteration over all views", "brick_grid_xyz": list(grid),
+                   "halo": "none" if world == 1 else ("fused: epilogue stores into peer ghost layers (NVLink) + barrier" if fused else "NCCL send/recv per axis"),
                    "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % ((2 * V + 2) * nvox * 4 / world / 1e9),
                    "scratch_mb": int(os.environ.get("MVD_SCRATCH_MB", "256")), "batch_streams": int(os.environ.get("MVD_LANES", "3"))},
         "roofline": {"bound": "hbm", "kernel": names[top], "achieved": achieved, "peak": peak, "unit": "GB/s",

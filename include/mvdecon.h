@@ -141,6 +141,29 @@ int mvdProfileStop(mvdContext* ctx, double ms[3], long long launches[3], double 
 /* Device pointer and geometry of a ghosted array: dim = extent, off = index of brick voxel 0. */
 int mvdArrayInfo(mvdContext* ctx, int which, void** devicePtr, int dim[3], int off[3]);
 
+/* Fused ghost exchange.  Instead of exchanging ghost layers between the two steps, a context can
+ * be told where its neighbours' ghosted arrays live; mvdStepQuotient / mvdStepUpdate then store
+ * every output voxel a neighbour needs straight into that neighbour's ghost layers from the
+ * kernel that computes it (peer memory over NVLink), and the "exchange" shrinks to a barrier
+ * between the steps (all bricks finished step n before any starts step n+1).
+ *   mvdExportArrays  64-byte CUDA IPC handles of this context's psi and quotient arrays, to be
+ *                    sent to the processes that own the neighbouring bricks.
+ *   mvdAttachPeer    one neighbour (any brick whose ghost layers overlap this brick): its
+ *                    brickOffset / brickDim as given to its mvdCreate (same globalDim and ghost),
+ *                    and its arrays as MVD_PEER_POINTER (device pointers usable from this
+ *                    context's device: same process, same device or peer access enabled by the
+ *                    library) or MVD_PEER_IPC (the 64-byte handles from mvdExportArrays of another
+ *                    process).  peerDevice is the CUDA device of the neighbour (MVD_PEER_POINTER).
+ *   mvdDetachPeers   back to caller-side exchanges; closes IPC mappings.
+ * The reference has no counterpart (one Java thread per device pulling blocks through host RAM,
+ * MVDeconFFTThreads.java:96-134). */
+#define MVD_PEER_POINTER 0
+#define MVD_PEER_IPC 1
+int mvdExportArrays(mvdContext* ctx, unsigned char psiHandle[64], unsigned char quotientHandle[64]);
+int mvdAttachPeer(mvdContext* ctx, const int peerBrickOffset[3], const int peerBrickDim[3], const void* psi,
+                  const void* quotient, int kind, int peerDevice);
+int mvdDetachPeers(mvdContext* ctx);
+
 /* psi = 0 where no view has data (MVDeconvolution.java:180-187). */
 int mvdMaskNeverUpdated(mvdContext* ctx);
 

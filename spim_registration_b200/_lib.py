@@ -46,6 +46,9 @@ PROTOTYPES = {
     "mvdProfileStart": (C.c_int, [C.c_void_p]),
     "mvdProfileStop": (C.c_int, [C.c_void_p, c_double_p, c_ll_p, c_double_p]),
     "mvdArrayInfo": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), c_int_p, c_int_p]),
+    "mvdExportArrays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mvdAttachPeer": (C.c_int, [C.c_void_p, c_int_p, c_int_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "mvdDetachPeers": (C.c_int, [C.c_void_p]),
     "mvdMaskNeverUpdated": (C.c_int, [C.c_void_p]),
     "mvdConvolve": (C.c_int, [C.c_int, c_float_p, c_int_p, c_float_p, c_int_p, C.c_int, C.c_float, c_float_p]),
     "mvdConvolveDevice": (C.c_int, [C.c_int, C.c_void_p, c_int_p, c_float_p, c_int_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),

@@ -106,6 +106,12 @@ struct mvdContext {
     int stat_capacity = 0;
     double* d_fi_sum = nullptr;
     unsigned long long* d_fi_count = nullptr;
+    // fused ghost exchange (mvdAttachPeer): host copies and device tables of the neighbours
+    int ghost[3] = {0, 0, 0};
+    std::vector<PeerTarget> peers_psi, peers_quot;
+    PeerTarget* d_peers_psi = nullptr;
+    PeerTarget* d_peers_quot = nullptr;
+    std::vector<void*> ipc_mappings;
 
     size_t brick_elems() const { return (size_t)bdim[0] * bdim[1] * bdim[2]; }
     size_t array_elems() const { return (size_t)adim[0] * adim[1] * adim[2]; }
@@ -156,6 +162,8 @@ struct mvdContext {
         ep.lambda = lambda;
         ep.min_value = min_value;
         for (int d = 0; d < 3; ++d) { ep.out_dim[d] = adim[d]; ep.out_off[d] = glo[d]; ep.aux_dim[d] = bdim[d]; }
+        if (out == psi) { ep.peers = d_peers_psi; ep.n_peers = (int)peers_psi.size(); }
+        else if (out == quot) { ep.peers = d_peers_quot; ep.n_peers = (int)peers_quot.size(); }
         return ep;
     }
     ViewPtrs view_ptrs() const {
@@ -168,6 +176,23 @@ struct mvdContext {
 
 static void require(bool ok, const char* msg) {
     if (!ok) throw std::invalid_argument(msg);
+}
+
+// Ghost widths and array extent of a brick: the ghost layers are clipped at the volume border, and
+// in x the low ghost width and the row pitch are rounded up to multiples of 4 so that rows stay
+// float4-aligned (the extra voxels are never consumed; exchanges address the ghost layers through
+// mvdArrayInfo).
+static void ghost_geometry(const int gdim[3], const int boff[3], const int bdim[3], const int ghost[3], int glo[3], int ghi[3], int adim[3]) {
+    for (int d = 0; d < 3; ++d) {
+        glo[d] = std::min(ghost[d], boff[d]);
+        ghi[d] = std::min(ghost[d], gdim[d] - (boff[d] + bdim[d]));
+        if (d == 0) {
+            if (glo[0] > 0) glo[0] = (glo[0] + 3) / 4 * 4;
+            const int rem = (bdim[0] + glo[0] + ghi[0]) % 4;
+            if (rem) ghi[0] += 4 - rem;
+        }
+        adim[d] = bdim[d] + glo[d] + ghi[d];
+    }
 }
 
 // copy between a dense brick-sized array and the interior of a ghosted array
@@ -199,12 +224,10 @@ extern "C" int mvdCreate(mvdContext** out, int device, const int globalDim[3], c
             c->bdim[d] = brickDim ? brickDim[d] : globalDim[d];
             require(c->gdim[d] > 0 && c->bdim[d] > 0 && c->boff[d] >= 0 && c->boff[d] + c->bdim[d] <= c->gdim[d],
                     "mvdCreate: brick outside the volume");
-            const int g = ghost ? ghost[d] : 0;
-            require(g >= 0, "mvdCreate: negative ghost width");
-            c->glo[d] = std::min(g, c->boff[d]);
-            c->ghi[d] = std::min(g, c->gdim[d] - (c->boff[d] + c->bdim[d]));
-            c->adim[d] = c->bdim[d] + c->glo[d] + c->ghi[d];
+            c->ghost[d] = ghost ? ghost[d] : 0;
+            require(c->ghost[d] >= 0, "mvdCreate: negative ghost width");
         }
+        ghost_geometry(c->gdim, c->boff, c->bdim, c->ghost, c->glo, c->ghi, c->adim);
         require((double)c->array_elems() < 2147483647.0 * 4.0, "mvdCreate: brick too large");
         c->lambda = lambda;
         c->min_value = minValue;
@@ -221,6 +244,17 @@ extern "C" int mvdCreate(mvdContext** out, int device, const int globalDim[3], c
     });
 }
 
+static void detach_peers(mvdContext* c) {
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    c->peers_psi.clear();
+    c->peers_quot.clear();
+    if (c->d_peers_psi) cudaFree(c->d_peers_psi);
+    if (c->d_peers_quot) cudaFree(c->d_peers_quot);
+    c->d_peers_psi = c->d_peers_quot = nullptr;
+    for (void* p : c->ipc_mappings) cudaIpcCloseMemHandle(p);
+    c->ipc_mappings.clear();
+}
+
 extern "C" int mvdDestroy(mvdContext* c) {
     if (!c) return 0;
     return guarded([&] {
@@ -233,6 +267,7 @@ extern "C" int mvdDestroy(mvdContext* c) {
         c->views.clear();
         c->plans.clear();
         c->prof.reset();
+        detach_peers(c);
         if (c->psi) cudaFree(c->psi);
         if (c->quot) cudaFree(c->quot);
         if (c->d_sum) cudaFree(c->d_sum);
@@ -467,6 +502,94 @@ extern "C" int mvdArrayInfo(mvdContext* c, int which, void** ptr, int dim[3], in
             if (dim) dim[d] = c->adim[d];
             if (off) off[d] = c->glo[d];
         }
+    });
+}
+
+// ---- fused ghost exchange --------------------------------------------------------------------
+extern "C" int mvdExportArrays(mvdContext* c, unsigned char psiHandle[64], unsigned char quotientHandle[64]) {
+    return guarded([&] {
+        require(c && psiHandle && quotientHandle, "mvdExportArrays: null argument");
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
+        c->activate();
+        cudaIpcMemHandle_t h;
+        MVD_CUDA(cudaIpcGetMemHandle(&h, c->psi));
+        std::memcpy(psiHandle, &h, 64);
+        MVD_CUDA(cudaIpcGetMemHandle(&h, c->quot));
+        std::memcpy(quotientHandle, &h, 64);
+    });
+}
+
+extern "C" int mvdAttachPeer(mvdContext* c, const int peerBrickOffset[3], const int peerBrickDim[3], const void* psi,
+                             const void* quotient, int kind, int peerDevice) {
+    return guarded([&] {
+        require(c && peerBrickOffset && peerBrickDim && psi && quotient, "mvdAttachPeer: null argument");
+        require(kind == MVD_PEER_POINTER || kind == MVD_PEER_IPC, "mvdAttachPeer: bad kind");
+        require((int)c->peers_psi.size() < kMaxPeers, "mvdAttachPeer: too many neighbours");
+        c->activate();
+        int pglo[3], pghi[3], padim[3];
+        for (int d = 0; d < 3; ++d)
+            require(peerBrickDim[d] > 0 && peerBrickOffset[d] >= 0 && peerBrickOffset[d] + peerBrickDim[d] <= c->gdim[d],
+                    "mvdAttachPeer: neighbour brick outside the volume");
+        ghost_geometry(c->gdim, peerBrickOffset, peerBrickDim, c->ghost, pglo, pghi, padim);
+        PeerTarget t;
+        std::memset(&t, 0, sizeof(t));
+        bool any = true;
+        for (int d = 0; d < 3; ++d) {
+            // the neighbour wants my voxels inside its ghosted extent: the true ghost width in y and z, the
+            // whole (4-aligned) array extent in x so that quads stay whole
+            const int want_lo = peerBrickOffset[d] - (d == 0 ? pglo[d] : std::min(c->ghost[d], pglo[d]));
+            const int want_hi = peerBrickOffset[d] + peerBrickDim[d] + (d == 0 ? pghi[d] : std::min(c->ghost[d], pghi[d]));
+            t.dim[d] = padim[d];
+            t.shift[d] = c->boff[d] - (peerBrickOffset[d] - pglo[d]);
+            t.lo[d] = std::max(0, want_lo - c->boff[d]);
+            t.hi[d] = std::min(c->bdim[d], want_hi - c->boff[d]);
+            any = any && t.lo[d] < t.hi[d];
+        }
+        require(any, "mvdAttachPeer: the neighbour's ghost layers do not reach this brick");
+        float* ppsi = nullptr;
+        float* pquot = nullptr;
+        if (kind == MVD_PEER_IPC) {
+            cudaIpcMemHandle_t h;
+            void* m = nullptr;
+            std::memcpy(&h, psi, 64);
+            MVD_CUDA(cudaIpcOpenMemHandle(&m, h, cudaIpcMemLazyEnablePeerAccess));
+            c->ipc_mappings.push_back(m);
+            ppsi = static_cast<float*>(m);
+            std::memcpy(&h, quotient, 64);
+            MVD_CUDA(cudaIpcOpenMemHandle(&m, h, cudaIpcMemLazyEnablePeerAccess));
+            c->ipc_mappings.push_back(m);
+            pquot = static_cast<float*>(m);
+        } else {
+            if (peerDevice >= 0 && peerDevice != c->device) {
+                int can = 0;
+                MVD_CUDA(cudaDeviceCanAccessPeer(&can, c->device, peerDevice));
+                require(can != 0, "mvdAttachPeer: no peer access between the two devices");
+                const cudaError_t e = cudaDeviceEnablePeerAccess(peerDevice, 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+                else MVD_CUDA(e);
+            }
+            ppsi = const_cast<float*>(static_cast<const float*>(psi));
+            pquot = const_cast<float*>(static_cast<const float*>(quotient));
+        }
+        MVD_CUDA(cudaStreamSynchronize(c->stream));
+        t.base = ppsi;
+        c->peers_psi.push_back(t);
+        t.base = pquot;
+        c->peers_quot.push_back(t);
+        if (!c->d_peers_psi) {
+            MVD_CUDA(cudaMalloc(&c->d_peers_psi, kMaxPeers * sizeof(PeerTarget)));
+            MVD_CUDA(cudaMalloc(&c->d_peers_quot, kMaxPeers * sizeof(PeerTarget)));
+        }
+        MVD_CUDA(cudaMemcpy(c->d_peers_psi, c->peers_psi.data(), c->peers_psi.size() * sizeof(PeerTarget), cudaMemcpyHostToDevice));
+        MVD_CUDA(cudaMemcpy(c->d_peers_quot, c->peers_quot.data(), c->peers_quot.size() * sizeof(PeerTarget), cudaMemcpyHostToDevice));
+    });
+}
+
+extern "C" int mvdDetachPeers(mvdContext* c) {
+    return guarded([&] {
+        require(c, "mvdDetachPeers: null context");
+        c->activate();
+        detach_peers(c);
     });
 }
 

@@ -417,7 +417,33 @@ __device__ __forceinline__ float next_psi_value(float last, float integral, floa
     return __fadd_rn(last, __fmul_rn(__fsub_rn(next, last), weight));
 }
 
-template <int BX, int BY, int EPI>
+// ---------------------------------------------------------------------------------------------
+// Fused ghost-layer exchange: a run of N freshly computed output voxels starting at brick
+// coordinate (x0, y, z) is also stored into the ghost layers of every neighbouring brick that
+// needs it (PeerTarget, conv_types.h) -- peer memory over NVLink, written by the same kernel
+// that produced the values.  `pm` is the tile's candidate mask, so interior tiles never get here.
+template <int N>
+__device__ __noinline__ void push_run(const PeerTarget* __restrict__ peers, unsigned pm, int x0, int y, int z, float4 r) {
+    const float rv[4] = {r.x, r.y, r.z, r.w};
+    for (; pm; pm &= pm - 1) {
+        const PeerTarget t = peers[__ffs(pm) - 1];
+        if (y < t.lo[1] || y >= t.hi[1] || z < t.lo[2] || z >= t.hi[2] || x0 + N <= t.lo[0] || x0 >= t.hi[0]) continue;
+        const long long idx = ((long long)(z + t.shift[2]) * t.dim[1] + (y + t.shift[1])) * (long long)t.dim[0] + (x0 + t.shift[0]);
+        float* __restrict__ p = t.base + idx;
+        const bool inside = x0 >= t.lo[0] && x0 + N <= t.hi[0];
+        if (N == 4 && inside && (idx & 3) == 0) {
+            *reinterpret_cast<float4*>(p) = r;
+        } else if (N == 2 && inside && (idx & 1) == 0) {
+            *reinterpret_cast<float2*>(p) = make_float2(r.x, r.y);
+        } else {
+#pragma unroll
+            for (int i = 0; i < N; ++i)
+                if (x0 + i >= t.lo[0] && x0 + i < t.hi[0]) p[i] = rv[i];
+        }
+    }
+}
+
+template <int BX, int BY, int EPI, bool PUSH>
 __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(const float2* __restrict__ scratch, size_t tile_stride,
                                                                            const Tile* __restrict__ tiles, EpilogueArgs ep, int chunks,
                                                                            int n_items, Twiddles tw) {
@@ -430,6 +456,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
     float2* twu = twr + H;
     __shared__ double s_sum[NT / 32];
     __shared__ float s_max[NT / 32];
+    __shared__ unsigned s_pmask;  // PUSH: neighbours whose ghost layers intersect the current tile
 
     const int tid = threadIdx.x;
     if constexpr (BX == 128) {
@@ -459,6 +486,21 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
     if (zfirst >= tile.n[2]) continue;
     const int lx = tile.e[0] - tile.o[0], ly = tile.e[1] - tile.o[1];
     const int n0 = tile.n[0], n1 = tile.n[1];
+    if constexpr (PUSH) {
+        // read by the row phase behind the barrier that ends the column phase; the previous item's
+        // rows are behind the barrier that ended its last plane
+        if (tid < 32) {
+            bool hit = false;
+            if (tid < ep.n_peers) {
+                const PeerTarget& t = ep.peers[tid];
+                hit = true;
+#pragma unroll
+                for (int d = 0; d < 3; ++d) hit = hit && tile.e[d] < t.hi[d] && tile.e[d] + tile.n[d] > t.lo[d];
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (tid == 0) s_pmask = m;
+        }
+    }
     // x pairs owned by this thread: x = 2*(rt + m*TX) - lx, +1; classify once (lx is a multiple of 4)
     unsigned full = 0, part = 0;
 #pragma unroll
@@ -534,6 +576,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                 if (yl >= n1) continue;
                 float2 e[8], f[8];
                 float rsum = 0.f;  // |change| of this thread's <= 32 voxels of the row, added to the double sum once
+                const unsigned pm = PUSH ? s_pmask : 0u;
                 row128_inverse(e, f, plane + (ly + yl) * P, twr, twu, q, wmask);
                 // (e[m].x, e[m].y, f[m].x, f[m].y) = samples x = 16 m + 4 q .. + 3 of the window
                 const size_t rowbase = ((size_t)(zv + ep.out_off[2]) * ep.out_dim[1] + (tile.e[1] + yl + ep.out_off[1])) * (size_t)ep.out_dim[0] +
@@ -589,6 +632,9 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                                     }
                                 }
                                 *reinterpret_cast<float4*>(outp + 16 * m) = make_float4(r[0], r[1], r[2], r[3]);
+                                if constexpr (PUSH) {
+                                    if (pm) push_run<4>(ep.peers, pm, tile.e[0] + xq + 16 * m, tile.e[1] + yl, zv, make_float4(r[0], r[1], r[2], r[3]));
+                                }
                             }
                         }
                     }
@@ -605,18 +651,22 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                             const int x = xq + 16 * m + i;
                             if (x < 0 || x >= n0) continue;
                             const size_t idx = rowbase + x, aidx = auxbase + x;
+                            float nv;
                             if constexpr (EPI == EPI_STORE) {
-                                ep.out[idx] = c[i];
+                                nv = c[i];
                             } else if constexpr (EPI == EPI_QUOTIENT) {
-                                ep.out[idx] = quotient_value(__ldg(ep.img + aidx), c[i]);
+                                nv = quotient_value(__ldg(ep.img + aidx), c[i]);
                             } else {
                                 const float last = ep.out[idx];
                                 const float w = ep.weight ? __ldg(ep.weight + aidx) : ep.weight_const;
-                                const float nv = next_psi_value(last, c[i], w, use_tik, two_lambda, inv_lambda, ep.min_value);
-                                ep.out[idx] = nv;
+                                nv = next_psi_value(last, c[i], w, use_tik, two_lambda, inv_lambda, ep.min_value);
                                 const float ch = fabsf(__fsub_rn(nv, last));
                                 rsum += ch;
                                 lmax = fmaxf(lmax, ch);
+                            }
+                            ep.out[idx] = nv;
+                            if constexpr (PUSH) {
+                                if (pm) push_run<1>(ep.peers, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
                             }
                         }
                     }
@@ -631,6 +681,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
             const unsigned wmask = __ballot_sync(0xffffffffu, yl < n1);
             if (yl >= n1) continue;
             const int row = ly + yl;
+            const unsigned pm = PUSH ? s_pmask : 0u;
             float2* __restrict__ rp = plane + row * P;
             float2 v[8];
 #pragma unroll
@@ -688,6 +739,9 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                             lmax = fmaxf(lmax, fmaxf(ch0, ch1));  // fmaxf drops NaN
                         }
                         *reinterpret_cast<float2*>(outp + 2 * m * TX) = r;
+                        if constexpr (PUSH) {
+                            if (pm) push_run<2>(ep.peers, pm, tile.e[0] + 2 * (rt + m * TX) - lx, tile.e[1] + yl, zv, make_float4(r.x, r.y, 0.f, 0.f));
+                        }
                     }
                 }
             } else {
@@ -705,18 +759,22 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                         const int x = xl + q;
                         if (x < 0 || x >= n0) continue;
                         const size_t idx = rowbase + x, aidx = auxbase + x;
+                        float nv;
                         if constexpr (EPI == EPI_STORE) {
-                            ep.out[idx] = c[q];
+                            nv = c[q];
                         } else if constexpr (EPI == EPI_QUOTIENT) {
-                            ep.out[idx] = quotient_value(__ldg(ep.img + aidx), c[q]);
+                            nv = quotient_value(__ldg(ep.img + aidx), c[q]);
                         } else {
                             const float last = ep.out[idx];
                             const float w = ep.weight ? __ldg(ep.weight + aidx) : ep.weight_const;
-                            const float nv = next_psi_value(last, c[q], w, use_tik, two_lambda, inv_lambda, ep.min_value);
-                            ep.out[idx] = nv;
+                            nv = next_psi_value(last, c[q], w, use_tik, two_lambda, inv_lambda, ep.min_value);
                             const float ch = fabsf(__fsub_rn(nv, last));
                             lsum += (double)ch;
                             lmax = fmaxf(lmax, ch);
+                        }
+                        ep.out[idx] = nv;
+                        if constexpr (PUSH) {
+                            if (pm) push_run<1>(ep.peers, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
                         }
                     }
                 }
@@ -798,9 +856,11 @@ cudaError_t configure_conv_kernels() {
     {                                                                                                                            \
         constexpr int sm = (int)XYCfg<BX, BY>::SMEM_INV;                                                                         \
         if (e == cudaSuccess) e = cudaFuncSetAttribute(fwd_xy_kernel<BX, BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XYCfg<BX, BY>::SMEM_FWD); \
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(inv_xy_kernel<BX, BY, EPI_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm); \
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(inv_xy_kernel<BX, BY, EPI_QUOTIENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm); \
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(inv_xy_kernel<BX, BY, EPI_UPDATE>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm); \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(inv_xy_kernel<BX, BY, EPI_STORE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm); \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(inv_xy_kernel<BX, BY, EPI_QUOTIENT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm); \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(inv_xy_kernel<BX, BY, EPI_UPDATE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm); \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(inv_xy_kernel<BX, BY, EPI_QUOTIENT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm); \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(inv_xy_kernel<BX, BY, EPI_UPDATE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm); \
     }
     CFG_XY(32, 32) CFG_XY(32, 64) CFG_XY(32, 128) CFG_XY(64, 32) CFG_XY(64, 64) CFG_XY(64, 128) CFG_XY(128, 32) CFG_XY(128, 64) CFG_XY(128, 128)
 #undef CFG_XY
@@ -846,6 +906,7 @@ cudaError_t launch_z_pass(int bx, int by, int bz, int mode, float2* scratch, con
 cudaError_t launch_inv_xy(int bx, int by, int bz, int epilogue, const float2* scratch, const Tile* d_tiles, int n_tiles, int max_nz,
                           const EpilogueArgs& ep, const TwiddleTables& tw, cudaStream_t st) {
     if (n_tiles <= 0 || max_nz <= 0) return cudaSuccess;
+    if (ep.n_peers > kMaxPeers) return cudaErrorInvalidValue;
     const size_t stride = tile_scratch_elems(bx, by, bz);
     const int chunks = (max_nz + XY_ZPC - 1) / XY_ZPC;
     const int n_items = chunks * n_tiles;
@@ -853,9 +914,12 @@ cudaError_t launch_inv_xy(int bx, int by, int bz, int epilogue, const float2* sc
 #define F(BX, BY)                                                                                                        \
     {                                                                                                                    \
         constexpr size_t sm = XYCfg<BX, BY>::SMEM_INV;                                                                       \
-        if (epilogue == EPI_STORE) inv_xy_kernel<BX, BY, EPI_STORE><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
-        else if (epilogue == EPI_QUOTIENT) inv_xy_kernel<BX, BY, EPI_QUOTIENT><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
-        else inv_xy_kernel<BX, BY, EPI_UPDATE><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        const bool push = ep.peers != nullptr && ep.n_peers > 0;                                                         \
+        if (epilogue == EPI_STORE) inv_xy_kernel<BX, BY, EPI_STORE, false><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else if (epilogue == EPI_QUOTIENT && !push) inv_xy_kernel<BX, BY, EPI_QUOTIENT, false><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else if (epilogue == EPI_QUOTIENT) inv_xy_kernel<BX, BY, EPI_QUOTIENT, true><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else if (!push) inv_xy_kernel<BX, BY, EPI_UPDATE, false><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else inv_xy_kernel<BX, BY, EPI_UPDATE, true><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
     }
     MVD_XY_DISPATCH(bx, by, F);
 #undef F

@@ -36,6 +36,18 @@ enum Epilogue : int {
     EPI_UPDATE = 2     // psi = update(psi, conv, weight, lambda) (MVDeconvolution.java:582-703)
 };
 
+// Ghost layers of a neighbouring brick that this brick's epilogue fills directly through peer
+// memory (NVLink stores, or plain stores when the neighbour lives on the same device): every
+// output voxel inside [lo, hi) (brick coordinates) is also written to
+// base[((z + shift[2]) * dim[1] + (y + shift[1])) * dim[0] + x + shift[0]].
+struct PeerTarget {
+    float* base;   // the neighbour's ghosted psi / quotient array
+    int dim[3];    // its extent
+    int shift[3];  // brick coordinate -> index in the neighbour's array
+    int lo[3], hi[3];
+};
+constexpr int kMaxPeers = 26;
+
 struct EpilogueArgs {
     float* out;            // EPI_STORE / EPI_QUOTIENT target, EPI_UPDATE: psi (read + write)
     const float* img;      // EPI_QUOTIENT: observed view
@@ -49,6 +61,8 @@ struct EpilogueArgs {
     int out_dim[3];        // extent of the out array (brick plus ghost layers)
     int out_off[3];        // array index of brick voxel 0 inside out
     int aux_dim[3];        // extent of img / weight (brick only, no ghost)
+    const PeerTarget* peers;  // device array of n_peers neighbours whose ghost layers are pushed, or nullptr
+    int n_peers;
 };
 
 }  // namespace mvd

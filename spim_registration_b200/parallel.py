@@ -134,6 +134,48 @@ class ShardedDeconvolution:
             t = torch.as_tensor(_CudaArray(ptr.value, (dim[2], dim[1], dim[0])), device=torch.device("cuda", device))
             self._arrays[which] = (t, (off[2], off[1], off[0]))
         self.slot = 0
+        self.fused = False
+
+    # -- fused ghost exchange ---------------------------------------------------------------------
+    def neighbours(self):
+        """[(rank, offset_xyz, size_xyz)] of the bricks whose ghost layers overlap this brick."""
+        out = []
+        for dz in (-1, 0, 1):
+            for dy in (-1, 0, 1):
+                for dx in (-1, 0, 1):
+                    delta = (dx, dy, dz)
+                    if delta == (0, 0, 0) or any(delta[d] and not self.ghost[d] for d in range(3)):
+                        continue
+                    nc = [self.coords[d] + delta[d] for d in range(3)]
+                    if any(nc[d] < 0 or nc[d] >= self.grid[d] for d in range(3)):
+                        continue
+                    r = rank_of(nc, self.grid)
+                    off, size, _ = brick_of(r, self.grid, self.dim)
+                    out.append((r, off, size))
+        return out
+
+    def attach_peers(self):
+        """Switch to the fused exchange (mvdAttachPeer, include/mvdecon.h): the step kernels store
+        ghost voxels straight into the neighbours' arrays over NVLink; between the steps only a
+        barrier remains.  One process per GPU: the arrays are shared through CUDA IPC handles."""
+        if self.world == 1:
+            return
+        torch, L = self.torch, self.L
+        for d in range(3):
+            assert self.grid[d] == 1 or self.size[d] >= self.ghost[d], "bricks thinner than the ghost layer are not supported"
+        hp, hq = (C.c_ubyte * 64)(), (C.c_ubyte * 64)()
+        L.check(self.lib.mvdExportArrays(self.ctx, hp, hq), "mvdExportArrays")
+        dev = self._arrays[0][0].device
+        mine = torch.tensor(list(bytes(hp) + bytes(hq)), dtype=torch.uint8, device=dev)
+        every = [torch.empty_like(mine) for _ in range(self.world)]
+        self.dist.all_gather(every, mine)
+        for r, off, size in self.neighbours():
+            hb = bytes(every[r].cpu().numpy().tobytes())
+            a, b = C.create_string_buffer(hb[:64], 64), C.create_string_buffer(hb[64:], 64)
+            L.check(self.lib.mvdAttachPeer(self.ctx, L.int3(off), L.int3(size), a, b, 1, -1), "mvdAttachPeer")
+        self._flag = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.fused = True
+        self.dist.barrier()
 
     # -- pieces of the MVDeconvolution constructor ------------------------------------------
     def init_psi_average(self):
@@ -150,6 +192,11 @@ class ShardedDeconvolution:
 
     def _exchange(self, which):
         if self.world == 1:
+            return
+        if self.fused:
+            # the ghost layers were written by the neighbours' step kernels; every brick must have
+            # finished the step before the next one reads them (stream-ordered, no host sync)
+            self.dist.all_reduce(self._flag)
             return
         t, off = self._arrays[which]
         exchange_ghosts(t, off, self.size[::-1], self.ghost, self.coords, self.grid, self.dist)
@@ -198,6 +245,9 @@ class ShardedDeconvolution:
 
     def close(self):
         if self.ctx:
+            if self.fused and self.world > 1 and hasattr(self.dist, "barrier"):
+                self.torch.cuda.synchronize()
+                self.dist.barrier()  # no neighbour may still be writing into arrays that are about to be freed
             self.lib.mvdDestroy(self.ctx)
             self.ctx = None
 
@@ -221,8 +271,20 @@ class LocalBrickGroup:
             d = ShardedDeconvolution.__new__(ShardedDeconvolution)
             _init_brick(d, self.dim, bi, bw, kernel1, kernel2, lam, device, self.grid, r, self.world)
             self.bricks.append(d)
+        self.fused = False
+
+    def attach_peers(self):
+        """Fused exchange between bricks of one device: neighbours are plain device pointers."""
+        for b in self.bricks:
+            for r, off, size in b.neighbours():
+                peer = self.bricks[r]
+                pp, pq = peer._arrays[0][0].data_ptr(), peer._arrays[1][0].data_ptr()
+                b.L.check(b.lib.mvdAttachPeer(b.ctx, b.L.int3(off), b.L.int3(size), C.c_void_p(pp), C.c_void_p(pq), 0, -1), "mvdAttachPeer")
+        self.fused = True
 
     def _exchange(self, which):
+        if self.fused:
+            return  # every brick runs on the same stream: the steps are already ordered
         # axis by axis, full-extent slabs (edges and corners travel through the later axes)
         for axis in (0, 1, 2):
             dimt = 2 - axis

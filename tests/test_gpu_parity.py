@@ -227,14 +227,17 @@ def test_config1_full_size(m, o):
     assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
 
 
-@pytest.mark.parametrize("grid", [(2, 1, 1), (1, 2, 2), (2, 2, 2)])
-def test_bricks_with_ghost_layers_equal_whole_volume(m, o, grid):
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("grid,shape", [((2, 1, 1), (40, 56, 72)), ((1, 2, 2), (40, 56, 72)), ((2, 2, 2), (40, 56, 72)),
+                                        ((2, 2, 2), (41, 54, 70)), ((4, 1, 2), (40, 30, 150))])
+def test_bricks_with_ghost_layers_equal_whole_volume(m, o, grid, shape, fused):
     """The brick / ghost-layer code paths of the library (what every rank of the multi-GPU run
-    executes) on one device: all bricks stepped in lock-step with in-process ghost copies must
-    reproduce the single-context result and the oracle."""
+    executes) on one device: all bricks stepped in lock-step must reproduce the single-context
+    result and the oracle -- with in-process ghost copies between the steps, and with the fused
+    exchange (mvdAttachPeer: the step kernels store into the neighbours' ghost layers)."""
     from spim_registration_b200 import synthetic
     from spim_registration_b200.parallel import LocalBrickGroup
-    shape, V, iters = (40, 56, 72), 2, 2
+    V, iters = 2, 2
     ds = _dataset(o, shape, V, (9, 7, 11), seed=3)
     weights = synthetic.blending_weights(shape, V)
     k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
@@ -243,8 +246,32 @@ def test_bricks_with_ghost_layers_equal_whole_volume(m, o, grid):
     try:
         assert abs(grp.init_psi_average() - avg) <= 1e-9 * abs(avg)
         grp._exchange(0)
+        if fused:
+            grp.attach_peers()
         grp.run_iterations(iters)
         got = grp.get_psi()
     finally:
         grp.close()
     assert rel_l2(got, ref) <= LOOP_TOL
+
+
+def test_fused_ghost_exchange_is_bit_identical_to_copies(m, o):
+    """Pushing ghost voxels from the epilogue changes where values are stored, not the values."""
+    from spim_registration_b200 import synthetic
+    from spim_registration_b200.parallel import LocalBrickGroup
+    shape, V, grid = (37, 50, 150), 2, (2, 2, 2)
+    ds = _dataset(o, shape, V, (9, 7, 11), seed=5)
+    weights = synthetic.blending_weights(shape, V)
+    k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
+    out = []
+    for fused in (False, True):
+        grp = LocalBrickGroup(shape[::-1], grid, ds["imgs"], weights, k1, k2, 0.006)
+        try:
+            grp.init_psi_average()
+            if fused:
+                grp.attach_peers()
+            grp.run_iterations(3)
+            out.append(grp.get_psi())
+        finally:
+            grp.close()
+    np.testing.assert_array_equal(out[0], out[1])
