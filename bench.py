@@ -298,6 +298,17 @@ def run_ours(args, cfg):
                            gbs=(pb[i] / 1e9) / (pms[i] * 1e-3) if pms[i] > 0 else 0.0) for i in range(3)}
     top = max(range(3), key=lambda i: pms[i])
     achieved = kern[names[top]]["gbs"]
+    # DRAM bytes per launch of the dominant kernel: measured once per round with `ncu --set full`
+    # (dram__bytes_read.sum + dram__bytes_write.sum over complete convolutions) as a ratio to the byte
+    # model, profiles/*_dram_traffic.json; applied to this run's algorithmic bytes per launch
+    traffic, traffic_src = None, None
+    tj = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_v5_dram_traffic.json")
+    if os.path.exists(tj) and pl[top] > 0:
+        tk = json.load(open(tj))["kernels"]
+        ratios = [v["traffic_over_model"] for k, v in tk.items() if k.startswith(names[top])]
+        if ratios:
+            traffic = sum(ratios) / len(ratios) * pb[top] / pl[top]
+            traffic_src = "profiles/r01_v5_dram_traffic.json (ncu --set full, dram bytes / byte model = %.3f) x this run's algorithmic bytes per launch" % (sum(ratios) / len(ratios))
     loop_bytes = ALG_BYTES_PER_VOXEL_VIEW[cfg["dense_weights"]] * V * nvox * args.steps / world
     line = {
         "metric": "Gvoxel-iterations/sec (all views)", "value": value, "unit": "Gvoxel-iterations/s", "n_gpus": world,
@@ -309,10 +320,11 @@ def run_ours(args, cfg):
                    "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % ((2 * V + 2) * nvox * 4 / world / 1e9),
                    "scratch_mb": int(os.environ.get("MVD_SCRATCH_MB", "256")), "batch_streams": int(os.environ.get("MVD_LANES", "3"))},
         "roofline": {"bound": "hbm", "kernel": names[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                     "share_of_step": pms[top] / prof_ms, "kernels": kern,
-                     "timing": "CUDA events around every launch, %d serial step(s) after the timed region (%.1f ms/step serial vs %.1f ms/step with %s batch streams)"
-                               % (prof_steps, prof_ms / prof_steps, ms / args.steps, os.environ.get("MVD_LANES", "3")),
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                     "achieved_bytes_per_launch": pb[top] / pl[top] if pl[top] else None, "peak_source": peak_src,
+                     "share_of_step": pms[top] / sum(pms), "kernels": kern,
+                     "timing": "CUDA events around every launch, %d serial step(s) after the timed region: kernels %.1f ms/step, wall %.1f ms/step with the event calls; timed region %.1f ms/step with %s batch streams; share_of_step = kernel / sum of the three kernels"
+                               % (prof_steps, sum(pms) / prof_steps, prof_ms / prof_steps, ms / args.steps, os.environ.get("MVD_LANES", "3")),
                      "loop": {"alg_bytes_per_voxel_view_iteration": ALG_BYTES_PER_VOXEL_VIEW[cfg["dense_weights"]],
                               "achieved": loop_bytes / 1e9 / (ms * 1e-3), "frac": loop_bytes / 1e9 / (ms * 1e-3) / peak,
                               "frac_of_8TBs": loop_bytes / 1e9 / (ms * 1e-3) / 8000.0}},

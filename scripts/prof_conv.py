@@ -37,4 +37,13 @@ torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / reps
 print("volume %dx%dx%d K=%d V=%d: %.3f ms/iteration, %.3f Gvoxel-it/s, %.3f ms per convolution" %
       (X, Y, Z, K, V, ms, X * Y * Z / ms / 1e6, ms / (2 * V)))
+if os.environ.get("MVD_PROF_MODEL", "1") == "1":
+    # byte model of one iteration (2 V convolutions), per kernel: what `roofline.achieved` divides by
+    L.check(lib.mvdProfileStart(dec.ctx), "start")
+    dec.run_iterations(1)
+    torch.cuda.synchronize()
+    pms, pl, pb = (C.c_double * 3)(), (C.c_longlong * 3)(), (C.c_double * 3)()
+    L.check(lib.mvdProfileStop(dec.ctx, pms, pl, pb), "stop")
+    for i, n in enumerate(("fwd_xy", "z_pass", "inv_xy")):
+        print("model %s: %d launches, %.3f ms, %.6f GB algorithmic per iteration (%d convolutions)" % (n, pl[i], pms[i], pb[i] / 1e9, 2 * V))
 dec.close()

@@ -57,6 +57,12 @@ template <int BX> struct PlaneLayout {
     __device__ __forceinline__ static constexpr int slot(int k) { return BX == 128 ? k : k + (k >> 3); }
 };
 
+// identity the optimiser cannot see through (keeps it from sharing address arithmetic across phases)
+__device__ __forceinline__ int opaque(int x) {
+    asm volatile("mov.b32 %0, %0;" : "+r"(x));
+    return x;
+}
+
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // Map a local coordinate through the source's out-of-bounds rule.
@@ -309,52 +315,98 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vol
 // z index); a z line is shared by TZ threads with EPT elements each.  The grid is ordered tile
 // fastest so that concurrently running CTAs read the same part of the kernel spectrum (L2 hits).
 template <int BZ> struct ZCfg {
-    // two passes with ONE exchange each way: 512 = 32 x 16, 256 = 16 x 16, 128 = 16 x 8, 64 = 8 x 8, ...
-    static constexpr int EPT = BZ >= 512 ? 32 : (BZ >= 128 ? 16 : 8);
-    static constexpr int TZ = BZ / EPT;
-#ifndef MVD_Z_PW
-#define MVD_Z_PW 16
+#ifndef MVD_Z_EPT512
+#define MVD_Z_EPT512 16
 #endif
-    static constexpr int PW = MVD_Z_PW;  // 8 (16): 64 (128) contiguous bytes per z index; small CTAs keep more of them in different phases
+    // elements per thread: 512 = 16 x 16 x 2 (two exchanges), 256 = 16 x 16, 128 = 16 x 8, 64 = 8 x 8 (one exchange)
+    static constexpr int EPT = BZ >= 512 ? MVD_Z_EPT512 : (BZ >= 128 ? 16 : 8);
+    static constexpr int TZ = BZ / EPT;
+#ifndef MVD_Z_ASYNC
+#define MVD_Z_ASYNC 0  // measured on B200 (cfg3): 12.5 ms per iteration without, 14.0 - 17.4 ms with
+#endif
+#ifndef MVD_Z_PW
+#define MVD_Z_PW (MVD_Z_ASYNC ? 8 : 16)
+#endif
+    static constexpr int PW = MVD_Z_PW;  // 8 (16): 64 (128) contiguous bytes per z index
     static constexpr int THREADS = PW * TZ;
-    static constexpr size_t SMEM = (size_t)PW * BZ * sizeof(float2) + (size_t)BZ * sizeof(float2);
-    static constexpr int MIN_CTAS = EPT == 32 ? 512 / THREADS : (THREADS >= 256 ? 3 : 4);
+    static constexpr bool ASYNC = MVD_Z_ASYNC != 0;
+    // exchange buffer | twiddles | (ASYNC) staging of the CTA's next item, EPT thread-private slots per thread
+    static constexpr size_t SMEM = (size_t)PW * BZ * sizeof(float2) * (ASYNC ? 2 : 1) + (size_t)BZ * sizeof(float2);
+#ifndef MVD_Z_MINCTAS512
+#define MVD_Z_MINCTAS512 (MVD_Z_ASYNC ? 768 / THREADS : 1024 / THREADS)
+#endif
+    // shorter lines: about 1024 threads per SM at <= 64 registers (at most 16 CTAs)
+    static constexpr int MIN_CTAS_ = BZ >= 512 ? MVD_Z_MINCTAS512 : (1024 / THREADS > 16 ? 16 : 1024 / THREADS);
+    static constexpr int MIN_CTAS = MIN_CTAS_ < 1 ? 1 : MIN_CTAS_;
 };
 
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gmem_src) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// ASYNC (off by default, kept for the measurement in DESIGN.md): the grid is persistent (ZCfg::MIN_CTAS CTAs per SM) and every thread copies the EPT elements
+// of the CTA's NEXT work item into thread-private shared-memory slots with cp.async while the current
+// item is transformed -- the HBM latency of an item is hidden behind the arithmetic of the one before
+// it, without holding registers and without extra barriers (a thread only reads slots it filled itself).
 template <int BZ, int MODE>
 __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_kernel(float2* __restrict__ scratch, size_t tile_stride,
                                                                                      const float2* __restrict__ kspec,
                                                                                      const Tile* __restrict__ tiles, int plane_elems,
                                                                                      float scale, int n_tiles, int n_items, Twiddles tw) {
     using C = ZCfg<BZ>;
-    constexpr int EPT = C::EPT, TZ = C::TZ, PW = C::PW;
+    constexpr int EPT = C::EPT, TZ = C::TZ, PW = C::PW, NTH = C::THREADS;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float2* xch = reinterpret_cast<float2*>(smem_raw);
     float2* twz = xch + (size_t)PW * BZ;
+    float2* stage = twz + BZ + threadIdx.x;  // slot m of this thread: stage[m * NTH]
     const int tid = threadIdx.x;
     const int p = tid % PW, t = tid / PW;
-    const size_t pe = (size_t)plane_elems;
-    for (int i = tid; i < BZ; i += C::THREADS) twz[i] = __ldg(&tw.t[ilog2<BZ>()][i]);
-    // work items = (position block, tile), tile fastest
+    for (int i = tid; i < BZ; i += NTH) twz[i] = __ldg(&tw.t[ilog2<BZ>()][i]);
+
+    // work items = (position block, tile), tile fastest: the CTAs running at the same time read the
+    // same part of the kernel spectrum (L2 hits)
+    auto item_base = [&](int item, bool& valid, int& ti) -> float2* {
+        const int pblk = item / n_tiles;
+        ti = item - pblk * n_tiles;
+        const int pos = pblk * PW + p;
+        valid = pos < plane_elems;
+        return scratch + (size_t)ti * tile_stride + (valid ? pos : 0);
+    };
+    auto prefetch_item = [&](int item) {
+        if (item < n_items) {
+            bool nv;
+            int nti;
+            const float2* nb = item_base(item, nv, nti);
+            const unsigned pl = (unsigned)opaque(plane_elems);
+#pragma unroll
+            for (int m = 0; m < EPT; ++m) cp_async8(stage + m * NTH, nb + (unsigned)(t + m * TZ) * pl);
+        }
+    };
+    if constexpr (C::ASYNC) prefetch_item(blockIdx.x);
+
 #pragma unroll 1
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-    const int pblk = item / n_tiles, ti = item - pblk * n_tiles;
-    const int pos = pblk * PW + p;
-    const bool valid = pos < plane_elems;
-    float2* __restrict__ base = scratch + (size_t)ti * tile_stride + (valid ? pos : 0);
+    bool valid;
+    int ti;
+    float2* __restrict__ base = item_base(item, valid, ti);
+    const int pos = (item / n_tiles) * PW + p;
 
+    // Element offsets are recomputed in every phase from a laundered copy of the plane size: the
+    // loads, the spectrum reads and the stores use the same EPT addresses, and common-subexpression
+    // elimination would otherwise keep all of them (2 registers each) alive across both transforms.
     float2 v[EPT];
+    if constexpr (C::ASYNC) {
+        cp_async_wait_all();
 #pragma unroll
-    for (int m = 0; m < EPT; ++m) v[m] = base[(size_t)(t + m * TZ) * pe];
-    // the kernel spectrum is needed only after the forward transform: pull its lines towards L2
-    // now (no registers held; one lane per 128-byte line), read them then
-    const float2* __restrict__ kb = kspec + (valid ? pos : 0);
-    if constexpr (MODE == 1) {
-        if ((p & 15) == 0) {
+        for (int m = 0; m < EPT; ++m) v[m] = stage[m * NTH];
+    } else {
+        const unsigned pl = (unsigned)plane_elems;
 #pragma unroll
-            for (int m = 0; m < EPT; ++m) prefetch_l2(kb + (size_t)(t + m * TZ) * pe);
-        }
+        for (int m = 0; m < EPT; ++m) v[m] = base[(unsigned)(t + m * TZ) * pl];
     }
+    const float2* __restrict__ kb = kspec + (valid ? pos : 0);
     __syncthreads();  // twiddle table ready; the previous item is done with the exchange buffer
 
     float2* __restrict__ xp = xch + p;
@@ -362,28 +414,47 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
     auto get = [&](int idx) { return xp[idx * PW]; };
     auto sync = [] { __syncthreads(); };
     line_fft<BZ, EPT, false>(v, t, twz, put, get, sync);
+    // the slots were consumed by the transform above (data dependence): refill them with the next item
+    if constexpr (C::ASYNC) prefetch_item(item + gridDim.x);
 
     if constexpr (MODE == 0) {
         if (valid) {
+            const unsigned pl = (unsigned)opaque(plane_elems);
 #pragma unroll
-            for (int m = 0; m < EPT; ++m) base[(size_t)(t + m * TZ) * pe] = make_float2(v[m].x * scale, v[m].y * scale);
+            for (int m = 0; m < EPT; ++m) base[(unsigned)(t + m * TZ) * pl] = make_float2(v[m].x * scale, v[m].y * scale);
         }
     } else {
+        // spectrum values in batches of KB: all EPT at once would need 2 * EPT more registers than the
+        // transform itself and spill (the compiler hoists every load above the first multiplication)
+#ifndef MVD_Z_KB
+#define MVD_Z_KB 4
+#endif
+        constexpr int KB = EPT >= MVD_Z_KB ? MVD_Z_KB : EPT;
 #pragma unroll
-        for (int m = 0; m < EPT; ++m) v[m] = cmul(v[m], __ldg(kb + (size_t)(t + m * TZ) * pe));
+        for (int h = 0; h < EPT; h += KB) {
+            float2 kk[KB];
+            const unsigned pl = (unsigned)opaque(plane_elems);
+#pragma unroll
+            for (int i = 0; i < KB; ++i) kk[i] = __ldg(kb + (unsigned)(t + (h + i) * TZ) * pl);
+#pragma unroll
+            for (int i = 0; i < KB; ++i) v[h + i] = cmul(v[h + i], kk[i]);
+            asm volatile("" ::: "memory");
+        }
         if constexpr (TZ > 1) __syncthreads();
         line_fft<BZ, EPT, true>(v, t, twz, put, get, sync);
         const Tile tile = tiles[ti];
         const int zlo = tile.e[2] - tile.o[2], zhi = zlo + tile.n[2];
         if (valid) {
+            const unsigned pl = (unsigned)opaque(plane_elems);
 #pragma unroll
             for (int m = 0; m < EPT; ++m) {
                 const int z = t + m * TZ;
-                if (z >= zlo && z < zhi) base[(size_t)z * pe] = v[m];
+                if (z >= zlo && z < zhi) base[(unsigned)z * pl] = v[m];
             }
         }
     }
     }  // items
+    if constexpr (C::ASYNC) cp_async_wait_all();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -421,13 +492,23 @@ __device__ __forceinline__ float next_psi_value(float last, float integral, floa
 // Fused ghost-layer exchange: a run of N freshly computed output voxels starting at brick
 // coordinate (x0, y, z) is also stored into the ghost layers of every neighbouring brick that
 // needs it (PeerTarget, conv_types.h) -- peer memory over NVLink, written by the same kernel
-// that produced the values.  `pm` is the tile's candidate mask, so interior tiles never get here.
+// that produced the values.  `peers` is the tile's candidate list in shared memory and `pm` the
+// subset whose y/z range contains the row (push_row_mask), so interior tiles never get here.
+__device__ __forceinline__ unsigned push_row_mask(const PeerTarget* peers, int n, int y, int z) {
+    unsigned m = 0;
+    for (int i = 0; i < n; ++i) {
+        const PeerTarget& t = peers[i];
+        if (y >= t.lo[1] && y < t.hi[1] && z >= t.lo[2] && z < t.hi[2]) m |= 1u << i;
+    }
+    return m;
+}
+
 template <int N>
 __device__ __noinline__ void push_run(const PeerTarget* __restrict__ peers, unsigned pm, int x0, int y, int z, float4 r) {
     const float rv[4] = {r.x, r.y, r.z, r.w};
     for (; pm; pm &= pm - 1) {
-        const PeerTarget t = peers[__ffs(pm) - 1];
-        if (y < t.lo[1] || y >= t.hi[1] || z < t.lo[2] || z >= t.hi[2] || x0 + N <= t.lo[0] || x0 >= t.hi[0]) continue;
+        const PeerTarget& t = peers[__ffs(pm) - 1];
+        if (x0 + N <= t.lo[0] || x0 >= t.hi[0]) continue;
         const long long idx = ((long long)(z + t.shift[2]) * t.dim[1] + (y + t.shift[1])) * (long long)t.dim[0] + (x0 + t.shift[0]);
         float* __restrict__ p = t.base + idx;
         const bool inside = x0 >= t.lo[0] && x0 + N <= t.hi[0];
@@ -443,8 +524,11 @@ __device__ __noinline__ void push_run(const PeerTarget* __restrict__ peers, unsi
     }
 }
 
+#ifndef MVD_INV_MINCTAS
+#define MVD_INV_MINCTAS 2  // 2 x 256 threads at <= 128 registers beat 3 x 256 at 80 with spills (measured)
+#endif
 template <int BX, int BY, int EPI, bool PUSH>
-__global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(const float2* __restrict__ scratch, size_t tile_stride,
+__global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS ? XYCfg<BX, BY>::MIN_CTAS : MVD_INV_MINCTAS)) inv_xy_kernel(const float2* __restrict__ scratch, size_t tile_stride,
                                                                            const Tile* __restrict__ tiles, EpilogueArgs ep, int chunks,
                                                                            int n_items, Twiddles tw) {
     using C = XYCfg<BX, BY>;
@@ -456,7 +540,8 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
     float2* twu = twr + H;
     __shared__ double s_sum[NT / 32];
     __shared__ float s_max[NT / 32];
-    __shared__ unsigned s_pmask;  // PUSH: neighbours whose ghost layers intersect the current tile
+    __shared__ PeerTarget s_peer[PUSH ? kMaxPeers : 1];  // PUSH: neighbours whose ghost layers intersect the current tile
+    __shared__ int s_npeer;
 
     const int tid = threadIdx.x;
     if constexpr (BX == 128) {
@@ -491,14 +576,16 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
         // rows are behind the barrier that ended its last plane
         if (tid < 32) {
             bool hit = false;
+            PeerTarget t;
             if (tid < ep.n_peers) {
-                const PeerTarget& t = ep.peers[tid];
+                t = ep.peers[tid];
                 hit = true;
 #pragma unroll
                 for (int d = 0; d < 3; ++d) hit = hit && tile.e[d] < t.hi[d] && tile.e[d] + tile.n[d] > t.lo[d];
             }
             const unsigned m = __ballot_sync(0xffffffffu, hit);
-            if (tid == 0) s_pmask = m;
+            if (hit) s_peer[__popc(m & ((1u << tid) - 1u))] = t;
+            if (tid == 0) s_npeer = __popc(m);
         }
     }
     // x pairs owned by this thread: x = 2*(rt + m*TX) - lx, +1; classify once (lx is a multiple of 4)
@@ -576,9 +663,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                 if (yl >= n1) continue;
                 float2 e[8], f[8];
                 float rsum = 0.f;  // |change| of this thread's <= 32 voxels of the row, added to the double sum once
-                const unsigned pm = PUSH ? s_pmask : 0u;
-                row128_inverse(e, f, plane + (ly + yl) * P, twr, twu, q, wmask);
-                // (e[m].x, e[m].y, f[m].x, f[m].y) = samples x = 16 m + 4 q .. + 3 of the window
+                const unsigned pm = PUSH && s_npeer ? push_row_mask(s_peer, s_npeer, tile.e[1] + yl, zv) : 0u;
                 const size_t rowbase = ((size_t)(zv + ep.out_off[2]) * ep.out_dim[1] + (tile.e[1] + yl + ep.out_off[1])) * (size_t)ep.out_dim[0] +
                                        tile.e[0] + ep.out_off[0];
                 const size_t auxbase = ((size_t)zv * ep.aux_dim[1] + (tile.e[1] + yl)) * (size_t)ep.aux_dim[0] + tile.e[0];
@@ -595,49 +680,59 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                 float* __restrict__ outp = ep.out + rowbase + xq;
                 const float* __restrict__ imgp = ep.img + auxbase + xq;
                 const float* __restrict__ wp = ep.weight + auxbase + xq;
-                if (vec) {
+                // epilogue operands of quads h .. h+3 (the first half is requested before the row transform,
+                // the second half before the first half is consumed: two batches of loads in flight)
+                auto load_half = [&](int h, float4 (&a)[4], float4 (&b)[4]) {
 #pragma unroll
-                    for (int h = 0; h < 8; h += 4) {  // two halves: 4 quads of loads in flight, registers stay below the cap
-                        float4 a[4], b[4];
-#pragma unroll
-                        for (int i4 = 0; i4 < 4; ++i4) {  // issue the loads before the first use
-                            const int m = h + i4;
-                            a[i4] = make_float4(0.f, 0.f, 0.f, 0.f);
-                            b[i4] = make_float4(ep.weight_const, ep.weight_const, ep.weight_const, ep.weight_const);
-                            if (full4 >> m & 1) {
-                                if constexpr (EPI == EPI_QUOTIENT) a[i4] = __ldg(reinterpret_cast<const float4*>(imgp + 16 * m));
-                                if constexpr (EPI == EPI_UPDATE) {
-                                    a[i4] = *reinterpret_cast<const float4*>(outp + 16 * m);
-                                    if (ep.weight) b[i4] = __ldg(reinterpret_cast<const float4*>(wp + 16 * m));
-                                }
-                            }
-                        }
-#pragma unroll
-                        for (int i4 = 0; i4 < 4; ++i4) {
-                            const int m = h + i4;
-                            if (full4 >> m & 1) {
-                                const float c[4] = {e[m].x + ep.add_const, e[m].y + ep.add_const, f[m].x + ep.add_const, f[m].y + ep.add_const};
-                                const float av[4] = {a[i4].x, a[i4].y, a[i4].z, a[i4].w};
-                                const float bv[4] = {b[i4].x, b[i4].y, b[i4].z, b[i4].w};
-                                float r[4];
-#pragma unroll
-                                for (int i = 0; i < 4; ++i) {
-                                    if constexpr (EPI == EPI_STORE) r[i] = c[i];
-                                    else if constexpr (EPI == EPI_QUOTIENT) r[i] = quotient_value(av[i], c[i]);
-                                    else {
-                                        r[i] = next_psi_value(av[i], c[i], bv[i], use_tik, two_lambda, inv_lambda, ep.min_value);
-                                        const float ch = fabsf(__fsub_rn(r[i], av[i]));
-                                        rsum += ch;
-                                        lmax = fmaxf(lmax, ch);  // fmaxf drops NaN
-                                    }
-                                }
-                                *reinterpret_cast<float4*>(outp + 16 * m) = make_float4(r[0], r[1], r[2], r[3]);
-                                if constexpr (PUSH) {
-                                    if (pm) push_run<4>(ep.peers, pm, tile.e[0] + xq + 16 * m, tile.e[1] + yl, zv, make_float4(r[0], r[1], r[2], r[3]));
-                                }
+                    for (int i4 = 0; i4 < 4; ++i4) {
+                        const int m = h + i4;
+                        a[i4] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        b[i4] = make_float4(ep.weight_const, ep.weight_const, ep.weight_const, ep.weight_const);
+                        if (vec && (full4 >> m & 1)) {
+                            if constexpr (EPI == EPI_QUOTIENT) a[i4] = __ldg(reinterpret_cast<const float4*>(imgp + 16 * m));
+                            if constexpr (EPI == EPI_UPDATE) {
+                                a[i4] = *reinterpret_cast<const float4*>(outp + 16 * m);
+                                if (ep.weight) b[i4] = __ldg(reinterpret_cast<const float4*>(wp + 16 * m));
                             }
                         }
                     }
+                };
+                auto finish_half = [&](int h, const float4 (&a)[4], const float4 (&b)[4]) {
+#pragma unroll
+                    for (int i4 = 0; i4 < 4; ++i4) {
+                        const int m = h + i4;
+                        if (full4 >> m & 1) {
+                            const float c[4] = {e[m].x + ep.add_const, e[m].y + ep.add_const, f[m].x + ep.add_const, f[m].y + ep.add_const};
+                            const float av[4] = {a[i4].x, a[i4].y, a[i4].z, a[i4].w};
+                            const float bv[4] = {b[i4].x, b[i4].y, b[i4].z, b[i4].w};
+                            float r[4];
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                if constexpr (EPI == EPI_STORE) r[i] = c[i];
+                                else if constexpr (EPI == EPI_QUOTIENT) r[i] = quotient_value(av[i], c[i]);
+                                else {
+                                    r[i] = next_psi_value(av[i], c[i], bv[i], use_tik, two_lambda, inv_lambda, ep.min_value);
+                                    const float ch = fabsf(__fsub_rn(r[i], av[i]));
+                                    rsum += ch;
+                                    lmax = fmaxf(lmax, ch);  // fmaxf drops NaN
+                                }
+                            }
+                            *reinterpret_cast<float4*>(outp + 16 * m) = make_float4(r[0], r[1], r[2], r[3]);
+                            if constexpr (PUSH) {
+                                if (pm) push_run<4>(s_peer, pm, tile.e[0] + xq + 16 * m, tile.e[1] + yl, zv, make_float4(r[0], r[1], r[2], r[3]));
+                            }
+                        }
+                    }
+                };
+                float4 a0[4], b0[4];
+                load_half(0, a0, b0);
+                row128_inverse(e, f, plane + (ly + yl) * P, twr, twu, q, wmask);
+                // (e[m].x, e[m].y, f[m].x, f[m].y) = samples x = 16 m + 4 q .. + 3 of the window
+                if (vec) {
+                    float4 a1[4], b1[4];
+                    load_half(4, a1, b1);
+                    finish_half(0, a0, b0);
+                    finish_half(4, a1, b1);
                 } else {
                     part4 |= full4;
                 }
@@ -666,7 +761,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                             }
                             ep.out[idx] = nv;
                             if constexpr (PUSH) {
-                                if (pm) push_run<1>(ep.peers, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
+                                if (pm) push_run<1>(s_peer, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
                             }
                         }
                     }
@@ -681,7 +776,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
             const unsigned wmask = __ballot_sync(0xffffffffu, yl < n1);
             if (yl >= n1) continue;
             const int row = ly + yl;
-            const unsigned pm = PUSH ? s_pmask : 0u;
+            const unsigned pm = PUSH && s_npeer ? push_row_mask(s_peer, s_npeer, tile.e[1] + yl, zv) : 0u;
             float2* __restrict__ rp = plane + row * P;
             float2 v[8];
 #pragma unroll
@@ -740,7 +835,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                         }
                         *reinterpret_cast<float2*>(outp + 2 * m * TX) = r;
                         if constexpr (PUSH) {
-                            if (pm) push_run<2>(ep.peers, pm, tile.e[0] + 2 * (rt + m * TX) - lx, tile.e[1] + yl, zv, make_float4(r.x, r.y, 0.f, 0.f));
+                            if (pm) push_run<2>(s_peer, pm, tile.e[0] + 2 * (rt + m * TX) - lx, tile.e[1] + yl, zv, make_float4(r.x, r.y, 0.f, 0.f));
                         }
                     }
                 }
@@ -774,7 +869,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
                         }
                         ep.out[idx] = nv;
                         if constexpr (PUSH) {
-                            if (pm) push_run<1>(ep.peers, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
+                            if (pm) push_run<1>(s_peer, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
                         }
                     }
                 }
@@ -809,6 +904,7 @@ __global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) inv_xy_kernel(con
 // grids of a fraction of the SMs' capacity, so CTAs of different kernels share an SM
 int g_xy_grid_cap = 0;
 int g_z_grid_cap = 0;
+int g_num_sms = 148;  // set by configure_conv_kernels
 void set_grid_caps(int xy_cap, int z_cap) { g_xy_grid_cap = xy_cap; g_z_grid_cap = z_cap; }
 
 bool xy_size_supported(int b) { return b == 32 || b == 64 || b == 128; }
@@ -842,6 +938,11 @@ static inline Twiddles to_dev(const TwiddleTables& t) {
 
 cudaError_t configure_conv_kernels() {
     cudaError_t e = cudaSuccess;
+    {
+        int dev = 0, sms = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0)
+            g_num_sms = sms;
+    }
     // column twiddles in the constant bank
     {
         float2 h[128];
@@ -894,7 +995,8 @@ cudaError_t launch_z_pass(int bx, int by, int bz, int mode, float2* scratch, con
 #define F(BZ)                                                                                                          \
     {                                                                                                                  \
         const int n_items = n_tiles * ((pe + ZCfg<BZ>::PW - 1) / ZCfg<BZ>::PW);                                        \
-        const int grid = g_z_grid_cap > 0 ? std::min(n_items, g_z_grid_cap) : n_items;                                 \
+        const int cap = g_z_grid_cap > 0 ? g_z_grid_cap : (ZCfg<BZ>::ASYNC ? g_num_sms * ZCfg<BZ>::MIN_CTAS : 0);       \
+        const int grid = cap > 0 ? std::min(n_items, cap) : n_items;                                                   \
         if (mode == 0) z_pass_kernel<BZ, 0><<<grid, ZCfg<BZ>::THREADS, ZCfg<BZ>::SMEM, st>>>(scratch, stride, kspec, d_tiles, pe, scale, n_tiles, n_items, to_dev(tw)); \
         else z_pass_kernel<BZ, 1><<<grid, ZCfg<BZ>::THREADS, ZCfg<BZ>::SMEM, st>>>(scratch, stride, kspec, d_tiles, pe, scale, n_tiles, n_items, to_dev(tw)); \
     }
