@@ -335,8 +335,10 @@ template <int BZ> struct ZCfg {
 #ifndef MVD_Z_MINCTAS512
 #define MVD_Z_MINCTAS512 (MVD_Z_ASYNC ? 768 / THREADS : 1024 / THREADS)
 #endif
-    // shorter lines: about 1024 threads per SM at <= 64 registers (at most 16 CTAs)
-    static constexpr int MIN_CTAS_ = BZ >= 512 ? MVD_Z_MINCTAS512 : (1024 / THREADS > 16 ? 16 : 1024 / THREADS);
+    // shorter lines: 3 x 256 threads at <= 85 registers (measured faster than 4 x 256 at 64); the persistent ASYNC
+    // grid wants about 1024 threads per SM instead
+    static constexpr int MIN_CTAS_ = BZ >= 512 ? MVD_Z_MINCTAS512
+                                               : (ASYNC ? (1024 / THREADS > 16 ? 16 : 1024 / THREADS) : (THREADS >= 256 ? 3 : 4));
     static constexpr int MIN_CTAS = MIN_CTAS_ < 1 ? 1 : MIN_CTAS_;
 };
 
@@ -429,7 +431,11 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
 #ifndef MVD_Z_KB
 #define MVD_Z_KB 4
 #endif
-        constexpr int KB = EPT >= MVD_Z_KB ? MVD_Z_KB : EPT;
+#ifndef MVD_Z_KB_SHORT
+#define MVD_Z_KB_SHORT 16  // shorter lines run at <= 85 registers: no batching needed (measured)
+#endif
+        constexpr int KB_ = BZ >= 512 ? MVD_Z_KB : MVD_Z_KB_SHORT;
+        constexpr int KB = EPT >= KB_ ? KB_ : EPT;
 #pragma unroll
         for (int h = 0; h < EPT; h += KB) {
             float2 kk[KB];
