@@ -500,11 +500,18 @@ __device__ __forceinline__ float next_psi_value(float last, float integral, floa
 // needs it (PeerTarget, conv_types.h) -- peer memory over NVLink, written by the same kernel
 // that produced the values.  `peers` is the tile's candidate list in shared memory and `pm` the
 // subset whose y/z range contains the row (push_row_mask), so interior tiles never get here.
-__device__ __forceinline__ unsigned push_row_mask(const PeerTarget* peers, int n, int y, int z) {
+// also returns the x range [xlo, xhi) covered by the matching neighbours, so that runs outside it skip the call
+__device__ __forceinline__ unsigned push_row_mask(const PeerTarget* peers, int n, int y, int z, int& xlo, int& xhi) {
     unsigned m = 0;
+    xlo = 0x7fffffff;
+    xhi = -0x7fffffff;
     for (int i = 0; i < n; ++i) {
         const PeerTarget& t = peers[i];
-        if (y >= t.lo[1] && y < t.hi[1] && z >= t.lo[2] && z < t.hi[2]) m |= 1u << i;
+        if (y >= t.lo[1] && y < t.hi[1] && z >= t.lo[2] && z < t.hi[2]) {
+            m |= 1u << i;
+            xlo = min(xlo, t.lo[0]);
+            xhi = max(xhi, t.hi[0]);
+        }
     }
     return m;
 }
@@ -669,7 +676,8 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
                 if (yl >= n1) continue;
                 float2 e[8], f[8];
                 float rsum = 0.f;  // |change| of this thread's <= 32 voxels of the row, added to the double sum once
-                const unsigned pm = PUSH && s_npeer ? push_row_mask(s_peer, s_npeer, tile.e[1] + yl, zv) : 0u;
+                int pxlo = 0, pxhi = 0;  // brick x range any neighbour wants from this row
+                const unsigned pm = PUSH && s_npeer ? push_row_mask(s_peer, s_npeer, tile.e[1] + yl, zv, pxlo, pxhi) : 0u;
                 const size_t rowbase = ((size_t)(zv + ep.out_off[2]) * ep.out_dim[1] + (tile.e[1] + yl + ep.out_off[1])) * (size_t)ep.out_dim[0] +
                                        tile.e[0] + ep.out_off[0];
                 const size_t auxbase = ((size_t)zv * ep.aux_dim[1] + (tile.e[1] + yl)) * (size_t)ep.aux_dim[0] + tile.e[0];
@@ -725,7 +733,8 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
                             }
                             *reinterpret_cast<float4*>(outp + 16 * m) = make_float4(r[0], r[1], r[2], r[3]);
                             if constexpr (PUSH) {
-                                if (pm) push_run<4>(s_peer, pm, tile.e[0] + xq + 16 * m, tile.e[1] + yl, zv, make_float4(r[0], r[1], r[2], r[3]));
+                                const int px = tile.e[0] + xq + 16 * m;
+                                if (pm && px + 4 > pxlo && px < pxhi) push_run<4>(s_peer, pm, px, tile.e[1] + yl, zv, make_float4(r[0], r[1], r[2], r[3]));
                             }
                         }
                     }
@@ -767,7 +776,7 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
                             }
                             ep.out[idx] = nv;
                             if constexpr (PUSH) {
-                                if (pm) push_run<1>(s_peer, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
+                                if (pm && tile.e[0] + x >= pxlo && tile.e[0] + x < pxhi) push_run<1>(s_peer, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
                             }
                         }
                     }
@@ -782,7 +791,8 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
             const unsigned wmask = __ballot_sync(0xffffffffu, yl < n1);
             if (yl >= n1) continue;
             const int row = ly + yl;
-            const unsigned pm = PUSH && s_npeer ? push_row_mask(s_peer, s_npeer, tile.e[1] + yl, zv) : 0u;
+            int pxlo = 0, pxhi = 0;
+            const unsigned pm = PUSH && s_npeer ? push_row_mask(s_peer, s_npeer, tile.e[1] + yl, zv, pxlo, pxhi) : 0u;
             float2* __restrict__ rp = plane + row * P;
             float2 v[8];
 #pragma unroll
@@ -841,7 +851,8 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
                         }
                         *reinterpret_cast<float2*>(outp + 2 * m * TX) = r;
                         if constexpr (PUSH) {
-                            if (pm) push_run<2>(s_peer, pm, tile.e[0] + 2 * (rt + m * TX) - lx, tile.e[1] + yl, zv, make_float4(r.x, r.y, 0.f, 0.f));
+                            const int px = tile.e[0] + 2 * (rt + m * TX) - lx;
+                            if (pm && px + 2 > pxlo && px < pxhi) push_run<2>(s_peer, pm, px, tile.e[1] + yl, zv, make_float4(r.x, r.y, 0.f, 0.f));
                         }
                     }
                 }
@@ -875,7 +886,7 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
                         }
                         ep.out[idx] = nv;
                         if constexpr (PUSH) {
-                            if (pm) push_run<1>(s_peer, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
+                            if (pm && tile.e[0] + x >= pxlo && tile.e[0] + x < pxhi) push_run<1>(s_peer, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
                         }
                     }
                 }
