@@ -49,6 +49,25 @@ long long getFreeMemDeviceCUDA(int devCUDA);
  * the error is latched (mvdGetLastError). */
 void convolution3DfftCUDAInPlace(float* im, int* imDim, float* kernel, int* kernelDim, int devCUDA);
 
+/* spim.process.cuda.CUDASeparableConvolution (CUDASeparableConvolution.java:13-17), the reference's
+ * second native hook (Gaussian blurs of the Difference-of-Gaussian detection,
+ * CUDASeparableConvolutionFunctions.java:127-199): in-place separable convolution with one kernel of
+ * diameter N per axis, image x fastest.  outofbounds 0 = zero, 1 = outofboundsvalue, 2 = extend the
+ * last pixel.  Java `boolean` arguments and results are C ints (JNA).  Returns 1 on success, 0 on
+ * failure (mvdGetLastError).  N <= 31 runs the direct separable kernels, 63 the FFT engine axis by
+ * axis, 127 is refused (wider than the largest xy window).  The interface's convolutionCPU is not
+ * exported: this library has no CPU path. */
+int convolve_7(float* image, float* kernelX, float* kernelY, float* kernelZ, int imageW, int imageH, int imageD, int convolveX,
+               int convolveY, int convolveZ, int outofbounds, float outofboundsvalue, int devCUDA);
+int convolve_15(float* image, float* kernelX, float* kernelY, float* kernelZ, int imageW, int imageH, int imageD, int convolveX,
+                int convolveY, int convolveZ, int outofbounds, float outofboundsvalue, int devCUDA);
+int convolve_31(float* image, float* kernelX, float* kernelY, float* kernelZ, int imageW, int imageH, int imageD, int convolveX,
+                int convolveY, int convolveZ, int outofbounds, float outofboundsvalue, int devCUDA);
+int convolve_63(float* image, float* kernelX, float* kernelY, float* kernelZ, int imageW, int imageH, int imageD, int convolveX,
+                int convolveY, int convolveZ, int outofbounds, float outofboundsvalue, int devCUDA);
+int convolve_127(float* image, float* kernelX, float* kernelY, float* kernelZ, int imageW, int imageH, int imageD, int convolveX,
+                 int convolveY, int convolveZ, int outofbounds, float outofboundsvalue, int devCUDA);
+
 /* CUDAFourierConvolution.java:9 -- declared by the reference, never called.  Returns a
  * malloc()ed array with the result (caller frees) or NULL on failure. */
 float* convolution3DfftCUDA(float* im, int* imDim, float* kernel, int* kernelDim, int devCUDA);
@@ -140,6 +159,15 @@ int mvdProfileStop(mvdContext* ctx, double ms[3], long long launches[3], double 
 #define MVD_ARRAY_QUOTIENT 1
 /* Device pointer and geometry of a ghosted array: dim = extent, off = index of brick voxel 0. */
 int mvdArrayInfo(mvdContext* ctx, int which, void** devicePtr, int dim[3], int off[3]);
+
+/* Direct path for small separable kernels.  mvdAddView tests every kernel for rank-1 separability
+ * (sum |K - a(z) b(y) c(x)| <= 1e-6 sum |K|, each extent <= 31); such convolutions run as direct
+ * separable passes with the same fused epilogues instead of through the FFT engine (Gaussian PSFs
+ * and the compound kernels built from them qualify, extracted bead PSFs do not).  Enabled by
+ * default; contexts with attached peers use the FFT engine.  mvdViewUsesDirectPath reports the tap
+ * count class (0 = FFT, else 7 / 15 / 31) chosen for conv1 and conv2 of a view. */
+int mvdSetDirectPath(mvdContext* ctx, int enable);
+int mvdViewUsesDirectPath(mvdContext* ctx, int view, int* conv1, int* conv2);
 
 /* Fused ghost exchange.  Instead of exchanging ghost layers between the two steps, a context can
  * be told where its neighbours' ghosted arrays live; mvdStepQuotient / mvdStepUpdate then store

@@ -160,6 +160,70 @@ def convolve_direct(f, kernel, mode, value=0.0):
 # kernel preparation, MVDeconFFT.init (MVDeconFFT.java:162-303) driven by MVDeconInput.init
 # (MVDeconInput.java:43-49): views are initialised IN ORDER, so while view v is prepared the
 # kernel1 of views w < v is already normalised and that of views w > v is not yet.
+def separable_convolve(f, kx, ky, kz, mode, value=0.0):
+    """The reference's second native hook (CUDASeparableConvolution.java:13-17; implementation in the
+    external SeparableConvolutionCUDALib, not in the reference tree -- parity unpinned): three
+    in-place 1-D passes x, y, z, each seeing the image extended by `mode` ("zero", "const" = value,
+    "clamp" = extend last pixel); out(p) = sum_j k[j] f(p - j + K // 2).  None skips an axis.
+    f is [z, y, x]; double accumulation, float32 between the passes like an in-place float image."""
+    a = np.asarray(f, dtype=np.float32)
+    for axis, k in ((2, kx), (1, ky), (0, kz)):
+        if k is None:
+            continue
+        k = np.asarray(k, dtype=np.float64)
+        K = len(k)
+        lo, hi = K - 1 - K // 2, K // 2
+        pad = [(0, 0)] * 3
+        pad[axis] = (lo, hi)
+        if mode == "zero":
+            e = np.pad(a.astype(np.float64), pad, mode="constant", constant_values=0.0)
+        elif mode == "const":
+            e = np.pad(a.astype(np.float64), pad, mode="constant", constant_values=float(value))
+        elif mode == "clamp":
+            e = np.pad(a.astype(np.float64), pad, mode="edge")
+        else:
+            raise ValueError(mode)
+        n = a.shape[axis]
+        out = np.zeros(a.shape, np.float64)
+        for j in range(K):
+            start = lo - j + K // 2  # index of f(p - j + K//2) for p = 0 in the padded array
+            sl = [slice(None)] * 3
+            sl[axis] = slice(start, start + n)
+            out += k[j] * e[tuple(sl)]
+        a = out.astype(np.float32)
+    return a
+
+
+def gaussian_kernel_1d(sigma, normalize=True):
+    """mpicbg.imglib.util.Util.createGaussianKernel1DDouble (imglib1 2.0.0-beta, outside the reference
+    tree; called at CUDASeparableConvolutionFunctions.java:208)."""
+    if sigma <= 0:
+        return np.array([0.0, 1.0, 0.0])
+    size = max(3, 2 * int(3 * sigma + 0.5) + 1)
+    k = np.zeros(size)
+    for x in range(size // 2, -1, -1):
+        v = np.exp(-(x * x) / (2.0 * sigma * sigma))
+        k[size // 2 - x] = v
+        k[size // 2 + x] = v
+    return k / k.sum() if normalize else k
+
+
+def cuda_kernels(sigma, supported=(7, 15, 31, 63, 127)):
+    """CUDASeparableConvolutionFunctions.getCUDAKernels / getFloatKernelPadded (:199-245)."""
+    ks = [gaussian_kernel_1d(s) for s in sigma]
+    longest = max(len(k) for k in ks)
+    size = min([s for s in supported if longest <= s], default=None)
+    if size is None:
+        return None
+    out = []
+    for k in ks:
+        p = np.zeros(size, np.float32)
+        s0 = (size - len(k)) // 2
+        p[s0:s0 + len(k)] = k
+        out.append(p)
+    return out
+
+
 def _conv_zero_same(inp, kernel):
     # new FFTConvolution(Views.extendZero(input), input, Views.extendZero(kernel), kernel, output)
     return convolve_extended(inp, kernel, "zero")

@@ -5,8 +5,9 @@ cuda (mirror of spim.process.cuda), deconvolution (mirror of spim.process.fusion
 """
 from . import _lib
 from ._lib import MVDeconError, load
-from .cuda import Block, BlockGeneratorFixedSizePrecise, CUDADevice, CUDAFourierConvolution, CUDATools, convolve, plan_tiles
+from .cuda import (Block, BlockGeneratorFixedSizePrecise, CUDADevice, CUDAFourierConvolution, CUDASeparableConvolution,
+                   CUDASeparableConvolutionFunctions, CUDATools, convolve, plan_tiles)
 from .deconvolution import AdjustInput, Mirror, MVDeconFFT, MVDeconInput, MVDeconvolution, PSFTYPE
 
-__all__ = ["MVDeconError", "load", "Block", "BlockGeneratorFixedSizePrecise", "CUDADevice", "CUDAFourierConvolution", "CUDATools",
+__all__ = ["MVDeconError", "load", "Block", "BlockGeneratorFixedSizePrecise", "CUDADevice", "CUDAFourierConvolution", "CUDASeparableConvolution", "CUDASeparableConvolutionFunctions", "CUDATools",
            "convolve", "plan_tiles", "AdjustInput", "Mirror", "MVDeconFFT", "MVDeconInput", "MVDeconvolution", "PSFTYPE"]

@@ -18,6 +18,11 @@ c_ll_p = C.POINTER(C.c_longlong)
 
 # name -> (restype, argtypes); every symbol declared in include/mvdecon.h
 PROTOTYPES = {
+    "convolve_7": (C.c_int, [c_float_p, c_float_p, c_float_p, c_float_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int]),
+    "convolve_15": (C.c_int, [c_float_p, c_float_p, c_float_p, c_float_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int]),
+    "convolve_31": (C.c_int, [c_float_p, c_float_p, c_float_p, c_float_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int]),
+    "convolve_63": (C.c_int, [c_float_p, c_float_p, c_float_p, c_float_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int]),
+    "convolve_127": (C.c_int, [c_float_p, c_float_p, c_float_p, c_float_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int]),
     "getCUDAcomputeCapabilityMinorVersion": (C.c_int, [C.c_int]),
     "getCUDAcomputeCapabilityMajorVersion": (C.c_int, [C.c_int]),
     "getNumDevicesCUDA": (C.c_int, []),
@@ -46,6 +51,8 @@ PROTOTYPES = {
     "mvdProfileStart": (C.c_int, [C.c_void_p]),
     "mvdProfileStop": (C.c_int, [C.c_void_p, c_double_p, c_ll_p, c_double_p]),
     "mvdArrayInfo": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), c_int_p, c_int_p]),
+    "mvdSetDirectPath": (C.c_int, [C.c_void_p, C.c_int]),
+    "mvdViewUsesDirectPath": (C.c_int, [C.c_void_p, C.c_int, c_int_p, c_int_p]),
     "mvdExportArrays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "mvdAttachPeer": (C.c_int, [C.c_void_p, c_int_p, c_int_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "mvdDetachPeers": (C.c_int, [C.c_void_p]),

@@ -10,6 +10,7 @@
 
 #include "../../include/mvdecon.h"
 #include "engine.h"
+#include "sep_kernels.h"
 #include "volume_kernels.h"
 
 using namespace mvd;
@@ -84,7 +85,41 @@ struct ViewData {
     float weight_const = 1.f;
     int plan1 = -1, plan2 = -1;
     std::unique_ptr<KernelSpectra> spec1, spec2;
+    // direct path: kernel i is rank-1 separable and at most 31 wide (sep_kernels.cu)
+    int sep_kmax1 = 0, sep_kmax2 = 0;  // 0 = not separable
+    SepTaps taps1, taps2;
 };
+
+// K[z][y][x] ~ a[z] b[y] c[x]?  The factors are the marginal sums (they average the rounding noise of
+// kernels that were themselves computed by convolutions); accepted when sum |K - a b c| <= 1e-6 sum |K|.
+static int separate_kernel(const float* k, const int kd[3], SepTaps& taps) {
+    const int kmax = sep_kmax_for(kd[0], kd[1], kd[2]);
+    if (kmax == 0) return 0;
+    std::vector<double> mx(kd[0], 0.0), my(kd[1], 0.0), mz(kd[2], 0.0);
+    double S = 0.0, A = 0.0;
+    for (int z = 0; z < kd[2]; ++z)
+        for (int y = 0; y < kd[1]; ++y)
+            for (int x = 0; x < kd[0]; ++x) {
+                const double v = k[((size_t)z * kd[1] + y) * kd[0] + x];
+                mx[x] += v; my[y] += v; mz[z] += v; S += v; A += std::fabs(v);
+            }
+    if (!(std::fabs(S) > 1e-30) || !std::isfinite(S)) return 0;
+    double err = 0.0;
+    for (int z = 0; z < kd[2]; ++z)
+        for (int y = 0; y < kd[1]; ++y)
+            for (int x = 0; x < kd[0]; ++x)
+                err += std::fabs((double)k[((size_t)z * kd[1] + y) * kd[0] + x] - mx[x] * my[y] * mz[z] / (S * S));
+    if (!(err <= 1e-6 * A)) return 0;
+    std::vector<float> fx(kd[0]), fy(kd[1]), fz(kd[2]);
+    for (int x = 0; x < kd[0]; ++x) fx[x] = (float)(mx[x] / S);
+    for (int y = 0; y < kd[1]; ++y) fy[y] = (float)(my[y] / S);
+    for (int z = 0; z < kd[2]; ++z) fz[z] = (float)mz[z];
+    std::memset(&taps, 0, sizeof(taps));
+    make_window_taps(fx.data(), kd[0], kmax, taps.x);
+    make_window_taps(fy.data(), kd[1], kmax, taps.y);
+    make_window_taps(fz.data(), kd[2], kmax, taps.z);
+    return kmax;
+}
 
 struct mvdContext {
     int device = 0;
@@ -112,6 +147,23 @@ struct mvdContext {
     PeerTarget* d_peers_psi = nullptr;
     PeerTarget* d_peers_quot = nullptr;
     std::vector<void*> ipc_mappings;
+    // direct separable path
+    bool direct_enabled = true;
+    float* sep_tmp = nullptr;
+    size_t sep_tmp_cap = 0;
+    bool direct_ok() const { return direct_enabled && peers_psi.empty(); }  // the direct kernels do not push ghost layers
+    float* sep_scratch(const Volume& src) {
+        const size_t n = sep_tmp_elems(src, bdim);
+        if (n > sep_tmp_cap) {
+            MVD_CUDA(cudaStreamSynchronize(stream));
+            if (sep_tmp) cudaFree(sep_tmp);
+            sep_tmp = nullptr;
+            sep_tmp_cap = 0;
+            MVD_CUDA(cudaMalloc(&sep_tmp, n * sizeof(float)));
+            sep_tmp_cap = n;
+        }
+        return sep_tmp;
+    }
 
     size_t brick_elems() const { return (size_t)bdim[0] * bdim[1] * bdim[2]; }
     size_t array_elems() const { return (size_t)adim[0] * adim[1] * adim[2]; }
@@ -268,6 +320,7 @@ extern "C" int mvdDestroy(mvdContext* c) {
         c->plans.clear();
         c->prof.reset();
         detach_peers(c);
+        if (c->sep_tmp) cudaFree(c->sep_tmp);
         if (c->psi) cudaFree(c->psi);
         if (c->quot) cudaFree(c->quot);
         if (c->d_sum) cudaFree(c->d_sum);
@@ -327,6 +380,8 @@ extern "C" int mvdAddView(mvdContext* c, const float* img, const float* weight, 
         v.plan2 = c->plan_for(k2);
         v.spec1 = build_spectra(*c->dev, *c->plans[v.plan1], kernel1, c->stream);
         v.spec2 = build_spectra(*c->dev, *c->plans[v.plan2], kernel2, c->stream);
+        v.sep_kmax1 = separate_kernel(kernel1, k1, v.taps1);
+        v.sep_kmax2 = separate_kernel(kernel2, k2, v.taps2);
         MVD_CUDA(cudaStreamSynchronize(c->stream));  // caller buffers may go away after return
         c->views.push_back(std::move(v));
         if (viewIndex) *viewIndex = (int)c->views.size() - 1;
@@ -399,6 +454,11 @@ static void step_quotient(mvdContext* c, int v) {
     const Volume src = c->ghosted_volume(c->psi, EXT_MIRROR_SINGLE, 0.f);
     EpilogueArgs ep = c->epilogue_base(c->quot);
     ep.img = vd.img;
+    if (vd.sep_kmax1 && c->direct_ok()) {
+        MVD_CUDA(launch_separable(src, c->bdim, vd.taps1, vd.sep_kmax1, EPI_QUOTIENT, ep, c->sep_scratch(src), c->stream));
+        g_kernel_launches += 2;
+        return;
+    }
     run_convolution(*c->dev, *c->plans[vd.plan1], *vd.spec1, src, EPI_QUOTIENT, ep, c->scratch, c->stream, c->prof.get());
 }
 
@@ -414,6 +474,11 @@ static void step_update(mvdContext* c, int v, int slot) {
     ep.weight_const = vd.weight_const;
     ep.sum_change = c->d_sum + slot;
     ep.max_change_bits = c->d_max + slot;
+    if (vd.sep_kmax2 && c->direct_ok()) {
+        MVD_CUDA(launch_separable(src, c->bdim, vd.taps2, vd.sep_kmax2, EPI_UPDATE, ep, c->sep_scratch(src), c->stream));
+        g_kernel_launches += 2;
+        return;
+    }
     run_convolution(*c->dev, *c->plans[vd.plan2], *vd.spec2, src, EPI_UPDATE, ep, c->scratch, c->stream, c->prof.get());
 }
 
@@ -504,6 +569,105 @@ extern "C" int mvdArrayInfo(mvdContext* c, int which, void** ptr, int dim[3], in
         }
     });
 }
+
+static void convolve_device(Device& dev, const float* d_src, const int dim[3], const float* kernel, const int k[3], int ext,
+                            float ext_value, float* d_out, cudaStream_t st);
+
+// ---- direct separable path -------------------------------------------------------------------
+extern "C" int mvdSetDirectPath(mvdContext* c, int enable) {
+    return guarded([&] {
+        require(c, "mvdSetDirectPath: null context");
+        c->direct_enabled = enable != 0;
+    });
+}
+
+extern "C" int mvdViewUsesDirectPath(mvdContext* c, int view, int* conv1, int* conv2) {
+    return guarded([&] {
+        require(c && view >= 0 && view < (int)c->views.size(), "mvdViewUsesDirectPath: bad view");
+        if (conv1) *conv1 = c->views[view].sep_kmax1 && c->direct_ok() ? c->views[view].sep_kmax1 : 0;
+        if (conv2) *conv2 = c->views[view].sep_kmax2 && c->direct_ok() ? c->views[view].sep_kmax2 : 0;
+    });
+}
+
+// The reference's second native hook: in-place separable convolution of a whole image or block with
+// one kernel of diameter N per axis (CUDASeparableConvolution.java:13-17, called by
+// CUDASeparableConvolutionFunctions.gauss, :127-199).  N <= 31 runs the direct kernels, 63 the FFT
+// engine axis by axis; 127 exceeds the largest xy window and is refused.
+static int separable_hook(int N, float* image, const float* kx, const float* ky, const float* kz, int w, int h, int d, int cx, int cy,
+                          int cz, int oob, float oobv, int dev_id) {
+    const int rc = guarded([&] {
+        require(image && w > 0 && h > 0 && d > 0, "convolve_N: bad image");
+        require(oob >= 0 && oob <= 2, "convolve_N: outofbounds must be 0 (zero), 1 (value) or 2 (extend last pixel)");
+        require((!cx || kx) && (!cy || ky) && (!cz || kz), "convolve_N: null kernel for an enabled axis");
+        int n_dev = 0;
+        MVD_CUDA(cudaGetDeviceCount(&n_dev));
+        require(dev_id >= 0 && dev_id < n_dev, "convolve_N: no such CUDA device (this library has no CPU path)");
+        MVD_CUDA(cudaSetDevice(dev_id));
+        Device& dev = Device::get(dev_id);
+        const size_t n = (size_t)w * h * d;
+        struct Bufs {
+            float *a = nullptr, *b = nullptr, *t = nullptr;
+            cudaStream_t st = nullptr;
+            ~Bufs() { if (a) cudaFree(a); if (b) cudaFree(b); if (t) cudaFree(t); if (st) cudaStreamDestroy(st); }
+        } B;
+        MVD_CUDA(cudaStreamCreateWithFlags(&B.st, cudaStreamNonBlocking));
+        MVD_CUDA(cudaMalloc(&B.a, n * sizeof(float)));
+        MVD_CUDA(cudaMalloc(&B.b, n * sizeof(float)));
+        MVD_CUDA(cudaMemcpyAsync(B.a, image, n * sizeof(float), cudaMemcpyHostToDevice, B.st));
+        const int dim[3] = {w, h, d};
+        const int ext = oob == 0 ? EXT_ZERO : (oob == 1 ? EXT_CONST : EXT_CLAMP);
+        const float one = 1.f;
+        if (N <= kSepMaxTaps) {
+            Volume v;
+            v.data = B.a;
+            for (int i = 0; i < 3; ++i) { v.dim[i] = dim[i]; v.off[i] = 0; v.gmin[i] = 0; v.gdim[i] = dim[i]; }
+            v.ext = ext;
+            v.ext_value = oobv;
+            SepTaps taps;
+            std::memset(&taps, 0, sizeof(taps));
+            const int kmax = sep_kmax_for(N, N, N);
+            make_window_taps(cx ? kx : &one, cx ? N : 1, kmax, taps.x);
+            make_window_taps(cy ? ky : &one, cy ? N : 1, kmax, taps.y);
+            make_window_taps(cz ? kz : &one, cz ? N : 1, kmax, taps.z);
+            taps.per_pass_fill = 1;
+            EpilogueArgs ep;
+            std::memset(&ep, 0, sizeof(ep));
+            ep.out = B.b;
+            for (int i = 0; i < 3; ++i) { ep.out_dim[i] = dim[i]; ep.aux_dim[i] = dim[i]; }
+            MVD_CUDA(cudaMalloc(&B.t, sep_tmp_elems(v, dim) * sizeof(float)));
+            MVD_CUDA(launch_separable(v, dim, taps, kmax, EPI_STORE, ep, B.t, B.st));
+            g_kernel_launches += 2;
+            MVD_CUDA(cudaMemcpyAsync(image, B.b, n * sizeof(float), cudaMemcpyDeviceToHost, B.st));
+        } else {
+            float* srcp = B.a;
+            float* dstp = B.b;
+            const float* ks[3] = {cx ? kx : nullptr, cy ? ky : nullptr, cz ? kz : nullptr};
+            for (int ax = 0; ax < 3; ++ax) {
+                if (!ks[ax]) continue;
+                int kd[3] = {1, 1, 1};
+                kd[ax] = N;
+                convolve_device(dev, srcp, dim, ks[ax], kd, ext, oobv, dstp, B.st);
+                std::swap(srcp, dstp);
+            }
+            MVD_CUDA(cudaMemcpyAsync(image, srcp, n * sizeof(float), cudaMemcpyDeviceToHost, B.st));
+        }
+        MVD_CUDA(cudaStreamSynchronize(B.st));
+    });
+    return rc == 0 ? 1 : 0;  // Java boolean
+}
+
+#define MVD_SEP_HOOK(N)                                                                                                          \
+    extern "C" int convolve_##N(float* image, float* kernelX, float* kernelY, float* kernelZ, int imageW, int imageH, int imageD,   \
+                                int convolveX, int convolveY, int convolveZ, int outofbounds, float outofboundsvalue, int devCUDA) { \
+        return separable_hook(N, image, kernelX, kernelY, kernelZ, imageW, imageH, imageD, convolveX, convolveY, convolveZ,       \
+                              outofbounds, outofboundsvalue, devCUDA);                                                            \
+    }
+MVD_SEP_HOOK(7)
+MVD_SEP_HOOK(15)
+MVD_SEP_HOOK(31)
+MVD_SEP_HOOK(63)
+MVD_SEP_HOOK(127)
+#undef MVD_SEP_HOOK
 
 // ---- fused ghost exchange --------------------------------------------------------------------
 extern "C" int mvdExportArrays(mvdContext* c, unsigned char psiHandle[64], unsigned char quotientHandle[64]) {

@@ -5,13 +5,14 @@
 
 namespace mvd {
 
-enum ExtMode : int { EXT_ZERO = 0, EXT_CONST = 1, EXT_MIRROR_SINGLE = 2 };
+enum ExtMode : int { EXT_ZERO = 0, EXT_CONST = 1, EXT_MIRROR_SINGLE = 2, EXT_CLAMP = 3 };
 
 // Out-of-bounds rule of the *source* of a convolution.  The reference feeds
 // conv1 with Views.extendMirrorSingle(psi) (MVDeconFFTThreads.java:23,57) and
 // conv2 with Views.extendValue(quotient, 1.0f) (MVDeconFFTThreads.java:42,82;
 // MVDeconFFT.java:490).  Zero extension serves the drop-in block symbol and
-// the kernel preparation (Views.extendZero, MVDeconFFT.java:201-227).
+// the kernel preparation (Views.extendZero, MVDeconFFT.java:201-227).  EXT_CLAMP repeats the last
+// pixel ("extendlastpixel" of the separable-convolution hook, CUDASeparableConvolution.java:12).
 struct Volume {
     const float* data;   // x fastest, index = x + dim[0]*(y + dim[1]*z), local array
     int dim[3];          // array extent (brick plus ghost layers)

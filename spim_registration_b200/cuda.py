@@ -118,6 +118,100 @@ class CUDAFourierConvolution:
             raise _lib.MVDeconError("convolution3DfftCUDAInPlace: " + msg)
 
 
+class CUDASeparableConvolution:
+    """Proxy of the JNA interface J/spim/process/cuda/CUDASeparableConvolution.java:9-22 (the
+    reference's second native hook: Gaussian blurs of the Difference-of-Gaussian detection)."""
+
+    SIZES = (7, 15, 31, 63, 127)  # CUDASeparableConvolutionFunctions.java:14
+
+    def __init__(self, path=None):
+        self._lib = _lib.load(path)
+
+    def convolve(self, size, image, kernelX, kernelY, kernelZ, imageW, imageH, imageD, convolveX, convolveY, convolveZ,
+                 outofbounds, outofboundsvalue, devCUDA):
+        """convolve_<size>: in-place; image float32 [d,h,w] contiguous; outofbounds 0 zero, 1 value, 2 extend last pixel.
+        Returns the native boolean."""
+        assert size in self.SIZES and image.dtype == np.float32 and image.flags.c_contiguous
+
+        def ptr(k, on):
+            if not on:
+                return None
+            assert k is not None and k.dtype == np.float32 and k.size == size
+            return k.ctypes.data_as(_lib.c_float_p)
+        fn = getattr(self._lib, "convolve_%d" % size)
+        ok = fn(image.ctypes.data_as(_lib.c_float_p), ptr(kernelX, convolveX), ptr(kernelY, convolveY), ptr(kernelZ, convolveZ),
+                int(imageW), int(imageH), int(imageD), int(bool(convolveX)), int(bool(convolveY)), int(bool(convolveZ)),
+                int(outofbounds), float(outofboundsvalue), int(devCUDA))
+        if not ok:
+            _lib.last_error()  # read (and clear) the latch; the reference only sees the boolean
+        return bool(ok)
+
+    def convolve_7(self, *a):
+        return self.convolve(7, *a)
+
+    def convolve_15(self, *a):
+        return self.convolve(15, *a)
+
+    def convolve_31(self, *a):
+        return self.convolve(31, *a)
+
+    def convolve_63(self, *a):
+        return self.convolve(63, *a)
+
+    def convolve_127(self, *a):
+        return self.convolve(127, *a)
+
+
+class CUDASeparableConvolutionFunctions:
+    """Host side of the hook, J/spim/process/cuda/CUDASeparableConvolutionFunctions.java."""
+
+    ZERO, VALUE, EXTEND_BORDER_PIXELS = 0, 1, 2  # enum OutOfBounds (:13), passed as its ordinal (:178)
+
+    @staticmethod
+    def createGaussianKernel1DDouble(sigma, normalize=True):
+        """mpicbg.imglib.util.Util.createGaussianKernel1DDouble (imglib1, a dependency outside the
+        reference tree): size = max(3, 2 * round(3 sigma + 0.5) + 1), exp(-x^2 / (2 sigma^2)), sum 1."""
+        if sigma <= 0:
+            return np.ones(3, np.float64) * np.array([0.0, 1.0, 0.0])
+        size = max(3, 2 * int(3 * sigma + 0.5) + 1)
+        x = np.arange(size, dtype=np.float64) - size // 2
+        k = np.exp(-(x * x) / (2.0 * sigma * sigma))
+        return k / k.sum() if normalize else k
+
+    @classmethod
+    def getCUDAKernels(cls, sigma, supported=CUDASeparableConvolution.SIZES):
+        """:199-229 -- one padded float kernel per dimension, all of the smallest supported size that holds them."""
+        ks = [cls.createGaussianKernel1DDouble(s, True) for s in sigma]
+        longest = max(len(k) for k in ks)
+        sizes = [s for s in supported if longest <= s]
+        if not sizes:
+            return None
+        size = min(sizes)
+        out = []
+        for k in ks:  # getFloatKernelPadded, :231-245
+            p = np.zeros(size, np.float32)
+            s0 = (size - len(k)) // 2
+            p[s0:s0 + len(k)] = k.astype(np.float32)
+            out.append(p)
+        return out
+
+    @classmethod
+    def gauss(cls, img, sigma, oobs=2, oobsValue=0.0, cuda=None, cudaDeviceId=0):
+        """:127-197 -- in-place Gaussian blur of img (float32 [z,y,x] / [y,x] / [x]); sigma per dimension in (x,y,z) order."""
+        if img is None or sigma is None or len(sigma) != img.ndim or img.ndim > 3 or img.ndim == 0:
+            return False
+        if cudaDeviceId < 0:
+            raise _lib.MVDeconError("gauss: CPU computation (device -1) is not provided, no CPU path")
+        ks = cls.getCUDAKernels(sigma)
+        if ks is None:
+            return False
+        cuda = cuda or CUDASeparableConvolution()
+        dims = list(img.shape[::-1]) + [1] * (3 - img.ndim)
+        k3 = ks + [None] * (3 - len(ks))
+        return cuda.convolve(len(ks[0]), img, k3[0], k3[1], k3[2], dims[0], dims[1], dims[2], k3[0] is not None, k3[1] is not None,
+                             k3[2] is not None, oobs, oobsValue, cudaDeviceId)
+
+
 def convolve(src, kernel, ext_mode="zero", ext_value=0.0, device=0):
     """Resident-engine convolution of a whole volume (mvdConvolve)."""
     lib = _lib.load()

@@ -181,7 +181,7 @@ class MVDeconvolution:
     minValue = F32(0.0001)  # MVDeconvolution.java:49
 
     def __init__(self, views, iterationType, numIterations, lam, osemspeedup=1.0, osemspeedupindex=0, name="",
-                 initialImage=None, device=None, numThreads=8, prepared=False):
+                 initialImage=None, device=None, numThreads=8, prepared=False, directPath=True):
         lib = _lib.load()
         self.views, self.name, self.lam = views, name, float(lam)
         self.data = views.getViews()
@@ -201,6 +201,13 @@ class MVDeconvolution:
                 _lib.check(lib.mvdAddView(self._ctx, v.getImage().ctypes.data_as(C.c_void_p), wp, wc,
                                           k1.ctypes.data_as(_lib.c_float_p), _lib.int3(k1.shape[::-1]),
                                           k2.ctypes.data_as(_lib.c_float_p), _lib.int3(k2.shape[::-1]), 0, None), "mvdAddView")
+            # which convolutions take the direct separable path (kernel class 7 / 15 / 31, 0 = FFT engine)
+            _lib.check(lib.mvdSetDirectPath(self._ctx, int(bool(directPath))), "mvdSetDirectPath")
+            self.directPath = []
+            for i in range(self.numViews):
+                a, b = C.c_int(), C.c_int()
+                _lib.check(lib.mvdViewUsesDirectPath(self._ctx, i, C.byref(a), C.byref(b)), "mvdViewUsesDirectPath")
+                self.directPath.append((a.value, b.value))
             if initialImage is not None:
                 init = np.ascontiguousarray(initialImage, dtype=F32)
                 _lib.check(lib.mvdSetPsi(self._ctx, init.ctypes.data_as(C.c_void_p), 0), "mvdSetPsi")

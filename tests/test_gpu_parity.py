@@ -267,6 +267,8 @@ def test_fused_ghost_exchange_is_bit_identical_to_copies(m, o):
     for fused in (False, True):
         grp = LocalBrickGroup(shape[::-1], grid, ds["imgs"], weights, k1, k2, 0.006)
         try:
+            for b in grp.bricks:  # contexts with peers use the FFT engine: compare like with like
+                b.L.check(b.lib.mvdSetDirectPath(b.ctx, 0), "mvdSetDirectPath")
             grp.init_psi_average()
             if fused:
                 grp.attach_peers()
@@ -275,3 +277,90 @@ def test_fused_ghost_exchange_is_bit_identical_to_copies(m, o):
         finally:
             grp.close()
     np.testing.assert_array_equal(out[0], out[1])
+
+
+# ---- direct separable path and the separable-convolution hook -------------------------------------
+@pytest.mark.parametrize("size,shape", [(7, (20, 33, 150)), (15, (40, 70, 260)), (31, (35, 66, 140)), (63, (70, 80, 90))])
+@pytest.mark.parametrize("oob", [0, 1, 2])
+def test_separable_hook_matches_oracle(m, o, size, shape, oob):
+    """convolve_N (CUDASeparableConvolution.java:13-17): N <= 31 direct kernels, 63 through the FFT engine."""
+    rng = np.random.default_rng(size + oob)
+    f = rng.random(shape, dtype=np.float32) + np.float32(0.1)
+    ks = [np.zeros(size, np.float32) for _ in range(3)]
+    for i, n in enumerate((size, max(3, size - 4), max(3, size // 2 | 1))):  # kernels shorter than N are centred (getFloatKernelPadded)
+        k = rng.random(n).astype(np.float32)
+        k /= k.sum()
+        ks[i][(size - n) // 2:(size - n) // 2 + n] = k
+    ref = o.separable_convolve(f, ks[0], ks[1], ks[2], ("zero", "const", "clamp")[oob], 0.6)
+    got = f.copy()
+    cuda = m.CUDASeparableConvolution()
+    assert cuda.convolve(size, got, ks[0], ks[1], ks[2], shape[2], shape[1], shape[0], True, True, True, oob, 0.6, 0)
+    assert rel_l2(got, ref) <= CONV_TOL
+
+
+def test_separable_hook_partial_axes_gauss_and_refusals(m, o):
+    F = m.CUDASeparableConvolutionFunctions
+    rng = np.random.default_rng(9)
+    f = rng.random((30, 40, 50), dtype=np.float32)
+    k = o.cuda_kernels([2.0])[0]
+    cuda = m.CUDASeparableConvolution()
+    got = f.copy()
+    assert cuda.convolve(len(k), got, None, k, None, 50, 40, 30, False, True, False, 2, 0.0, 0)  # y only
+    assert rel_l2(got, o.separable_convolve(f, None, k, None, "clamp")) <= CONV_TOL
+    # gauss(): kernels from sigma, extend-border rule (CUDASeparableConvolutionFunctions.java:33-58, 127-197)
+    got = f.copy()
+    assert F.gauss(got, [1.8, 1.8, 2.5])
+    ks = o.cuda_kernels([1.8, 1.8, 2.5])
+    assert rel_l2(got, o.separable_convolve(f, ks[0], ks[1], ks[2], "clamp")) <= CONV_TOL
+    img2 = rng.random((64, 72), dtype=np.float32)  # 2-d image: z kernel null, d = 1
+    got2 = img2.copy()
+    assert F.gauss(got2, [3.0, 1.2])
+    k2 = o.cuda_kernels([3.0, 1.2])
+    assert rel_l2(got2, o.separable_convolve(img2[None], k2[0], k2[1], None, "clamp")[0]) <= CONV_TOL
+    # refusals leave the image untouched and return false
+    before = f.copy()
+    big = np.full(127, 1 / 127, np.float32)
+    assert not cuda.convolve(127, f, big, big, big, 50, 40, 30, True, True, True, 2, 0.0, 0)
+    assert not cuda.convolve(7, f, k[:7].copy(), None, None, 50, 40, 30, True, False, False, 5, 0.0, 0)  # bad out-of-bounds code
+    assert not cuda.convolve(7, f, k[:7].copy(), None, None, 50, 40, 30, True, False, False, 0, 0.0, 99)  # bad device
+    np.testing.assert_array_equal(f, before)
+
+
+@pytest.mark.parametrize("psftype,ksize", [("EFFICIENT_BAYESIAN", (9, 9, 9)), ("OPTIMIZATION_I", (15, 11, 7)), ("INDEPENDENT", (5, 7, 9))])
+def test_direct_path_for_gaussian_psfs_matches_oracle_and_fft_path(m, o, psftype, ksize):
+    """Gaussian PSFs are rank-1: conv1 (and the compound kernels of conv2 when they stay within 31 taps)
+    run as direct separable passes -- same result as the oracle and as the FFT engine."""
+    from spim_registration_b200 import synthetic
+    shape, V, iters = (40, 52, 140), 3, 4
+
+    def g(n, sigma):
+        x = np.arange(n, dtype=np.float64) - n // 2
+        return np.exp(-x * x / (2 * sigma * sigma))
+    psfs = [(g(ksize[0], 1.0 + 0.4 * v)[:, None, None] * g(ksize[1], 1.6 - 0.3 * v)[None, :, None] *
+             g(ksize[2], 1.2 + 0.2 * v)[None, None, :]).astype(np.float32) for v in range(V)]  # axis-aligned: rank 1
+    truth = synthetic.make_truth(shape, "blob", synthetic.SEED0 + 7)
+    imgs = [synthetic.degrade(o.convolve_extended(truth, (p / p.sum()).astype(np.float32), "mirror"), v, V, synthetic.SEED0 + 7)
+            for v, p in enumerate(psfs)]
+    ds = dict(psfs=psfs, imgs=imgs)
+    weights = synthetic.blending_weights(shape, V)
+    k1, k2 = o.init_kernels(ds["psfs"], psftype, 8)
+    ref, stats, _ = o.run_deconvolution(ds["imgs"], weights, k1, k2, iters, 0.006)
+    res = {}
+    for direct in (True, False):
+        dec = m.MVDeconvolution(_views(m, ds["imgs"], weights, ds["psfs"]), psftype, iters, 0.006, directPath=direct)
+        res[direct] = dec
+        assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
+    assert all(a > 0 for a, _ in res[True].directPath), res[True].directPath   # every conv1 is direct
+    assert all(a == 0 and b == 0 for a, b in res[False].directPath)
+    assert rel_l2(res[True].getPsi(), res[False].getPsi()) <= LOOP_TOL
+    rs = np.array([[s for s, _ in row] for row in stats])
+    np.testing.assert_allclose(res[True].sumChange, rs, rtol=2e-3)
+
+
+def test_extracted_psfs_stay_on_the_fft_engine(m, o):
+    """Bead-extracted PSFs (noise, rotation) are not rank 1: every convolution goes through the FFT engine."""
+    from spim_registration_b200 import synthetic
+    psfs = synthetic.make_psfs(2, (9, 9, 9), extracted=True)
+    imgs = [_rand((24, 28, 32), 20 + v) for v in range(2)]
+    dec = m.MVDeconvolution(_views(m, imgs, [0.5, 0.5], psfs), "EFFICIENT_BAYESIAN", 1, 0.006)
+    assert all(a == 0 and b == 0 for a, b in dec.directPath), dec.directPath

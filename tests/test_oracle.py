@@ -225,3 +225,48 @@ def test_golden_fixture_reproduced_by_oracle():
                                           int(g["iterations"]), float(g["lam"]))
     assert avg == pytest.approx(float(g["avg"]), rel=1e-12)
     assert rel_l2(psi, g["psi"]) < 1e-6
+
+
+# ---- the separable-convolution hook (CUDASeparableConvolution.java:13-17) -------------------------
+@pytest.mark.parametrize("mode,nd_mode", [("zero", "constant"), ("clamp", "nearest"), ("const", "constant")])
+def test_separable_convolve_against_scipy(mode, nd_mode):
+    """Per-axis in-place passes, centre K // 2 also for even kernels, each pass with its own extension."""
+    from scipy import ndimage
+    rng = np.random.default_rng(3)
+    f = rng.random((9, 11, 13), dtype=np.float32)
+    ks = {2: rng.random(7), 1: rng.random(4), 0: rng.random(5)}
+    got = o.separable_convolve(f, ks[2], ks[1], ks[0], mode, 0.75)
+    ref = f
+    for ax in (2, 1, 0):
+        ref = ndimage.convolve1d(ref.astype(np.float64), ks[ax], axis=ax, mode=nd_mode, cval=0.75 if mode == "const" else 0.0).astype(np.float32)
+    np.testing.assert_allclose(got, ref, rtol=0, atol=2e-6)
+    # skipping an axis == convolving it with a delta
+    a = o.separable_convolve(f, ks[2], None, ks[0], mode, 0.75)
+    b = o.separable_convolve(f, ks[2], np.array([0.0, 1.0, 0.0]), ks[0], mode, 0.75)
+    np.testing.assert_array_equal(a, b)
+
+
+def test_separable_equals_full_3d_convolution_for_rank1_kernels():
+    """A rank-1 kernel through the three 1-D passes == the 3-D convolution of the loop's oracle (zero extension)."""
+    rng = np.random.default_rng(4)
+    f = rng.random((10, 12, 14), dtype=np.float32)
+    kx, ky, kz = rng.random(5), rng.random(3), rng.random(7)
+    k3 = (kz[:, None, None] * ky[None, :, None] * kx[None, None, :]).astype(np.float32)
+    a = o.separable_convolve(f, kx, ky, kz, "zero")
+    b = o.convolve_extended(f, k3, "zero")
+    assert rel_l2(a, b) <= 2e-6
+
+
+def test_gaussian_kernels_of_the_hook():
+    """Util.createGaussianKernel1DDouble + getCUDAKernels: size rule, symmetry, normalisation, centred padding."""
+    k = o.gaussian_kernel_1d(1.8)
+    assert len(k) == 2 * int(3 * 1.8 + 0.5) + 1 == 11 and abs(k.sum() - 1) < 1e-12 and np.allclose(k, k[::-1])
+    assert list(o.gaussian_kernel_1d(0.0)) == [0.0, 1.0, 0.0] and len(o.gaussian_kernel_1d(0.2)) == 3
+    ks = o.cuda_kernels([1.8, 1.8, 2.5])
+    assert [len(x) for x in ks] == [31, 31, 31]  # 17 taps for sigma 2.5 -> next supported size
+    assert ks[0][:10].sum() == 0 and ks[0][21:].sum() == 0 and abs(ks[0].sum() - 1) < 1e-6
+    assert o.cuda_kernels([30.0]) is None or len(o.cuda_kernels([30.0])[0]) == 127
+    assert o.cuda_kernels([50.0]) is None  # 301 taps: "Kernel bigger than maximally supported size"
+    import spim_registration_b200 as m
+    for a, b in zip(m.CUDASeparableConvolutionFunctions.getCUDAKernels([1.8, 1.8, 2.5]), ks):
+        np.testing.assert_array_equal(a, b)
