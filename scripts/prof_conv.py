@@ -18,7 +18,14 @@ X, Y, Z, K, reps = (a + [480, 480, 452, 31, 2][len(a):])[:5]
 lib = m.load()
 torch.cuda.set_device(0)
 V = 2
-psfs = synthetic.make_psfs(V, (K, K, K))
+if os.environ.get("MVD_PROF_SEP", "0") == "1":  # axis-aligned Gaussians: rank-1 kernels, direct separable path
+    def _g(n, sigma):
+        x = np.arange(n, dtype=np.float64) - n // 2
+        return np.exp(-x * x / (2 * sigma * sigma))
+    psfs = [(_g(K, K / 7.0 + 0.3 * v)[:, None, None] * _g(K, K / 8.0)[None, :, None] * _g(K, K / 9.0 + 0.2 * v)[None, None, :]).astype(np.float32)
+            for v in range(V)]
+else:
+    psfs = synthetic.make_psfs(V, (K, K, K))
 k1 = [(p / p.sum()).astype(np.float32) for p in psfs]
 k2 = [np.ascontiguousarray(k[::-1, ::-1, ::-1]) for k in k1]
 g = torch.Generator(device="cuda")
@@ -26,6 +33,10 @@ g.manual_seed(1)
 imgs = [torch.rand((Z, Y, X), generator=g, device="cuda") * 0.9 + 0.05 for _ in range(V)]
 w = [torch.full((Z, Y, X), 1.0 / V, device="cuda") for _ in range(V)]
 dec = ShardedDeconvolution((X, Y, Z), imgs, w, k1, k2, 0.006, None, 0)
+L.check(lib.mvdSetDirectPath(dec.ctx, int(os.environ.get("MVD_PROF_DIRECT", "1"))), "mvdSetDirectPath")
+a_, b_ = C.c_int(), C.c_int()
+L.check(lib.mvdViewUsesDirectPath(dec.ctx, 0, C.byref(a_), C.byref(b_)), "mvdViewUsesDirectPath")
+print("view 0 direct-path classes (conv1, conv2):", a_.value, b_.value)
 dec.init_psi_average()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 dec.run_iterations(1)

@@ -13,7 +13,8 @@
 //
 // Traffic per output voxel and convolution: read source (x halo overlap), write + read one float
 // intermediate, epilogue operands -- about 22 B against about 50 B for the FFT path, and about
-// 7 K instructions per voxel instead of 250.  The same kernels serve the reference's second native
+// 5 K instructions per voxel instead of 250.  Both kernels march SEP_U rows / planes per step so that
+// several loads are in flight and the register window shifts once per SEP_U outputs.  The same kernels serve the reference's second native
 // hook (in-place separable Gaussian convolution, CUDASeparableConvolution.java:13-17).
 //
 // Convention (same as the FFT path): out(p) = sum_j k[j] f(p - j + K/2) per axis.
@@ -31,53 +32,88 @@ constexpr int SEP_NT = 128;   // threads per CTA = columns per CTA
 constexpr int SEP_CHY = 64;   // rows per CTA in the xy kernel
 constexpr int SEP_CHZ = 128;  // planes per CTA in the z kernel
 
+constexpr int SEP_R = 16;    // rows per marching step of the xy kernel
+constexpr int SEP_WP = 164;  // pitch of the input strip: >= 128 + 31 - 1, multiple of 4, = 4 (mod 32) -> conflict-free LDS.128 across 8 rows
+constexpr int SEP_XP = 132;  // pitch of the x-convolved strip, same rule
+constexpr int SEP_U = 4;     // planes per marching step of the z kernel
+
 template <int KMAX>
 __global__ void __launch_bounds__(SEP_NT) sep_xy_kernel(Volume src, SepTaps taps, float* __restrict__ tmp, int bx, int by) {
     // tmp: [src.dim[2]][by][bx] -- every resident plane of the source (brick and ghost planes)
-    constexpr int H = KMAX / 2;
-    __shared__ float row[SEP_NT + KMAX - 1];
-    __shared__ int xmap[SEP_NT + KMAX - 1];
+    constexpr int H = KMAX / 2, R = SEP_R, W = SEP_NT + KMAX - 1;
+    constexpr int NIN = (16 + KMAX - 1 + 3) / 4;  // float4 loads feeding 16 adjacent outputs
+    static_assert(W <= SEP_WP && 4 * NIN + 16 * 7 <= SEP_WP, "input strip too narrow");
+    __shared__ __align__(16) float in[R][SEP_WP];
+    __shared__ __align__(16) float xs[R][SEP_XP];
+    __shared__ int xmap[W];
+    __shared__ int ymap[R];
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * SEP_NT, y0 = blockIdx.y * SEP_CHY, za = blockIdx.z;
     const float fillv = src.ext == EXT_CONST ? src.ext_value : 0.f;
-    for (int i = tid; i < SEP_NT + KMAX - 1; i += SEP_NT)
-        xmap[i] = map_coord(x0 - H + i, src.dim[0], src.off[0], src.gmin[0], src.gdim[0], src.ext);
+    for (int i = tid; i < W; i += SEP_NT) xmap[i] = map_coord(x0 - H + i, src.dim[0], src.off[0], src.gmin[0], src.gdim[0], src.ext);
+    for (int i = tid; i < R * SEP_WP; i += SEP_NT) (&in[0][0])[i] = 0.f;  // the pad columns are read (times zero taps): keep them finite
     float sx = 0.f;  // x convolution of a constant row = fill * sum of the x taps
 #pragma unroll
     for (int i = 0; i < KMAX; ++i) sx += taps.x[i];
+    const float fill_row = taps.per_pass_fill ? fillv : fillv * sx;
     const float* __restrict__ zbase = src.data + (size_t)za * src.dim[1] * (size_t)src.dim[0];
-    float ring[KMAX];
+    // win[j] = x-convolved row (r0 - (KMAX - 1) + j) of this thread's column; output row y = r0 + u - H reads win[u .. u + KMAX - 1]
+    float win[KMAX - 1 + R];
 #pragma unroll
-    for (int i = 0; i < KMAX; ++i) ring[i] = 0.f;
+    for (int i = 0; i < KMAX - 1 + R; ++i) win[i] = 0.f;
     const int yend = min(y0 + SEP_CHY, by);
-    __syncthreads();
+    // x pass mapping: 8 consecutive threads take 8 different rows (conflict-free float4 reads), a thread makes 16 adjacent outputs
+    const int xr = (tid & 7) + 8 * ((tid >> 3) & 1), xseg = (tid >> 4) * 16;
 #pragma unroll 1
-    for (int r = y0 - H; r < yend + H; ++r) {
-        const int yl = map_coord(r, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
-        float xc;
-        if (yl < 0) {
-            xc = yl == -1 ? (taps.per_pass_fill ? fillv : fillv * sx) : 0.f;
-        } else {
-            const float* __restrict__ rp = zbase + (size_t)yl * src.dim[0];
-            for (int i = tid; i < SEP_NT + KMAX - 1; i += SEP_NT) {
+    for (int r0 = y0 - H; r0 < yend + H; r0 += R) {
+        __syncthreads();  // the previous step's column reads are done (first step: xmap and the cleared strip are ready)
+        if (tid < R) ymap[tid] = map_coord(r0 + tid, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
+        __syncthreads();
+        for (int idx = tid; idx < R * W; idx += SEP_NT) {
+            const int r = idx / W, i = idx - r * W;
+            const int yl = ymap[r];
+            if (yl >= 0) {
                 const int xi = xmap[i];
-                row[i] = xi >= 0 ? __ldg(rp + xi) : (xi == -1 ? fillv : 0.f);
+                in[r][i] = xi >= 0 ? __ldg(zbase + (size_t)yl * src.dim[0] + xi) : (xi == -1 ? fillv : 0.f);
             }
-            __syncthreads();
-            xc = 0.f;
-#pragma unroll
-            for (int i = 0; i < KMAX; ++i) xc = fmaf(taps.x[i], row[tid + i], xc);
-            __syncthreads();  // the row buffer is rewritten by the next iteration
         }
+        __syncthreads();
+        if (ymap[xr] >= 0) {
+            float v[4 * NIN];
 #pragma unroll
-        for (int i = 0; i + 1 < KMAX; ++i) ring[i] = ring[i + 1];
-        ring[KMAX - 1] = xc;
-        const int y = r - H;  // the ring now holds rows y - H .. y + H
-        if (y >= y0 && x0 + tid < bx) {
-            float acc = 0.f;
+            for (int j = 0; j < NIN; ++j) {
+                const float4 q = *reinterpret_cast<const float4*>(&in[xr][xseg + 4 * j]);
+                v[4 * j] = q.x; v[4 * j + 1] = q.y; v[4 * j + 2] = q.z; v[4 * j + 3] = q.w;
+            }
 #pragma unroll
-            for (int i = 0; i < KMAX; ++i) acc = fmaf(taps.y[i], ring[i], acc);
-            tmp[((size_t)za * by + y) * bx + x0 + tid] = acc;
+            for (int o4 = 0; o4 < 4; ++o4) {
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int i = 0; i < KMAX; ++i) {
+#pragma unroll
+                    for (int o = 0; o < 4; ++o) acc[o] = fmaf(taps.x[i], v[4 * o4 + o + i], acc[o]);
+                }
+                *reinterpret_cast<float4*>(&xs[xr][xseg + 4 * o4]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < KMAX - 1; ++i) win[i] = win[i + R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int yl = ymap[r];
+            win[KMAX - 1 + r] = yl >= 0 ? xs[r][tid] : (yl == -1 ? fill_row : 0.f);
+        }
+        float* __restrict__ op = tmp + ((size_t)za * by + (r0 - H)) * bx + x0 + tid;
+#pragma unroll
+        for (int u = 0; u < R; ++u) {
+            const int y = r0 + u - H;
+            if (y >= y0 && y < yend && x0 + tid < bx) {
+                float acc = 0.f;
+#pragma unroll
+                for (int i = 0; i < KMAX; ++i) acc = fmaf(taps.y[i], win[u + i], acc);
+                op[(size_t)u * bx] = acc;
+            }
         }
     }
 }
@@ -85,7 +121,7 @@ __global__ void __launch_bounds__(SEP_NT) sep_xy_kernel(Volume src, SepTaps taps
 template <int KMAX, int EPI>
 __global__ void __launch_bounds__(SEP_NT) sep_z_kernel(const float* __restrict__ tmp, Volume src, SepTaps taps, EpilogueArgs ep, int bx,
                                                        int by, int bz) {
-    constexpr int H = KMAX / 2;
+    constexpr int H = KMAX / 2, U = SEP_U;
     __shared__ double s_sum[SEP_NT / 32];
     __shared__ float s_max[SEP_NT / 32];
     const int tid = threadIdx.x;
@@ -100,37 +136,58 @@ __global__ void __launch_bounds__(SEP_NT) sep_z_kernel(const float* __restrict__
     const double two_lambda = 2.0 * ep.lambda, inv_lambda = use_tik ? 1.0 / ep.lambda : 0.0;
     double lsum = 0.0;
     float lmax = 0.f;
-    float ring[KMAX];
+    float win[KMAX - 1 + U];  // win[j] = plane (r0 - (KMAX - 1) + j) of tmp at this thread's (x, y)
 #pragma unroll
-    for (int i = 0; i < KMAX; ++i) ring[i] = 0.f;
+    for (int i = 0; i < KMAX - 1 + U; ++i) win[i] = 0.f;
     const int zend = min(z0 + SEP_CHZ, bz);
-    const size_t col = (size_t)y * bx + (live ? x : 0);
     const size_t plane = (size_t)by * bx;
-#pragma unroll 4
-    for (int r = z0 - H; r < zend + H; ++r) {
-        const int zl = map_coord(r, src.dim[2], src.off[2], src.gmin[2], src.gdim[2], src.ext);
-        const float v = zl >= 0 ? __ldg(tmp + (size_t)zl * plane + col) : (zl == -1 ? fill_t : 0.f);
+    const float* __restrict__ tcol = tmp + (size_t)y * bx + (live ? x : 0);
+    const size_t oplane = (size_t)ep.out_dim[1] * ep.out_dim[0], aplane = (size_t)ep.aux_dim[1] * ep.aux_dim[0];
+    // pointers of output plane z = r0 - H, advanced by U planes per step
+    float* optr = ep.out + ((size_t)(z0 - 2 * H + ep.out_off[2]) * ep.out_dim[1] + (y + ep.out_off[1])) * (size_t)ep.out_dim[0] + ep.out_off[0] + (live ? x : 0);
+    const float* iptr = ep.img + ((size_t)(z0 - 2 * H) * ep.aux_dim[1] + y) * (size_t)ep.aux_dim[0] + (live ? x : 0);
+    const float* wptr = ep.weight + ((size_t)(z0 - 2 * H) * ep.aux_dim[1] + y) * (size_t)ep.aux_dim[0] + (live ? x : 0);
+#pragma unroll 1
+    for (int r0 = z0 - H; r0 < zend + H; r0 += U, optr += U * oplane, iptr += U * aplane, wptr += U * aplane) {
 #pragma unroll
-        for (int i = 0; i + 1 < KMAX; ++i) ring[i] = ring[i + 1];
-        ring[KMAX - 1] = v;
-        const int z = r - H;
-        if (z >= z0 && live) {
+        for (int i = 0; i < KMAX - 1; ++i) win[i] = win[i + U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int zl = map_coord(r0 + u, src.dim[2], src.off[2], src.gmin[2], src.gdim[2], src.ext);
+            win[KMAX - 1 + u] = zl >= 0 ? __ldg(tcol + (size_t)zl * plane) : (zl == -1 ? fill_t : 0.f);
+        }
+        // epilogue operands of the U outputs of this step, requested before the arithmetic
+        bool on[U];
+        float a[U], b[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int z = r0 + u - H;
+            on[u] = z >= z0 && z < zend && live;
+            a[u] = 0.f;
+            b[u] = ep.weight_const;
+            if (on[u]) {
+                if constexpr (EPI == EPI_QUOTIENT) a[u] = __ldg(iptr + u * aplane);
+                if constexpr (EPI == EPI_UPDATE) {
+                    a[u] = optr[u * oplane];
+                    if (ep.weight) b[u] = __ldg(wptr + u * aplane);
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (!on[u]) continue;
             float acc = 0.f;
 #pragma unroll
-            for (int i = 0; i < KMAX; ++i) acc = fmaf(taps.z[i], ring[i], acc);
+            for (int i = 0; i < KMAX; ++i) acc = fmaf(taps.z[i], win[u + i], acc);
             acc += ep.add_const;
-            const size_t idx = ((size_t)(z + ep.out_off[2]) * ep.out_dim[1] + (y + ep.out_off[1])) * (size_t)ep.out_dim[0] + x + ep.out_off[0];
-            const size_t aidx = ((size_t)z * ep.aux_dim[1] + y) * (size_t)ep.aux_dim[0] + x;
             if constexpr (EPI == EPI_STORE) {
-                ep.out[idx] = acc;
+                optr[u * oplane] = acc;
             } else if constexpr (EPI == EPI_QUOTIENT) {
-                ep.out[idx] = quotient_value(__ldg(ep.img + aidx), acc);
+                optr[u * oplane] = quotient_value(a[u], acc);
             } else {
-                const float last = ep.out[idx];
-                const float w = ep.weight ? __ldg(ep.weight + aidx) : ep.weight_const;
-                const float nv = next_psi_value(last, acc, w, use_tik, two_lambda, inv_lambda, ep.min_value);
-                ep.out[idx] = nv;
-                const float ch = fabsf(__fsub_rn(nv, last));
+                const float nv = next_psi_value(a[u], acc, b[u], use_tik, two_lambda, inv_lambda, ep.min_value);
+                optr[u * oplane] = nv;
+                const float ch = fabsf(__fsub_rn(nv, a[u]));
                 lsum += (double)ch;
                 lmax = fmaxf(lmax, ch);
             }
