@@ -272,15 +272,23 @@ def run_ours(args, cfg):
     barrier()
     t0 = time.perf_counter()
     dec = ShardedDeconvolution(dim_xyz, np_imgs, np_w, k1, k2, LAMBDA, dz, dev_index, grid=grid)  # H2D of every view
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
     dec.init_psi_average()
     if fused:
         dec.attach_peers()
     elif world > 1:
         dec._exchange(0)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
     dec.run_iterations(args.steps)
+    torch.cuda.synchronize()
+    t3 = time.perf_counter()
     dec.mask_never_updated()
     dec.get_psi_brick(h_psi.numpy())  # D2H of the result
     barrier()
+    t4 = time.perf_counter()
+    e2e_phases = {"create_context_h2d_views_spectra": t1 - t0, "psi_init": t2 - t1, "iterations": t3 - t2, "mask_d2h": t4 - t3}
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
@@ -318,18 +326,18 @@ def run_ours(args, cfg):
                    "lambda": LAMBDA, "step": "one iteration over all views", "brick_grid_xyz": list(grid),
                    "halo": "none" if world == 1 else ("fused: epilogue stores into peer ghost layers (NVLink) + barrier" if fused else "NCCL send/recv per axis"),
                    "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % ((2 * V + 2) * nvox * 4 / world / 1e9),
-                   "scratch_mb": int(os.environ.get("MVD_SCRATCH_MB", "256")), "batch_streams": int(os.environ.get("MVD_LANES", "3"))},
+                   "scratch_mb": int(os.environ.get("MVD_SCRATCH_MB", "4096")), "batch_streams": int(os.environ.get("MVD_LANES", "1"))},
         "roofline": {"bound": "hbm", "kernel": names[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "achieved_bytes_per_launch": pb[top] / pl[top] if pl[top] else None, "peak_source": peak_src,
                      "share_of_step": pms[top] / sum(pms), "kernels": kern,
                      "timing": "CUDA events around every launch, %d serial step(s) after the timed region: kernels %.1f ms/step, wall %.1f ms/step with the event calls; timed region %.1f ms/step with %s batch streams; share_of_step = kernel / sum of the three kernels"
-                               % (prof_steps, sum(pms) / prof_steps, prof_ms / prof_steps, ms / args.steps, os.environ.get("MVD_LANES", "3")),
+                               % (prof_steps, sum(pms) / prof_steps, prof_ms / prof_steps, ms / args.steps, os.environ.get("MVD_LANES", "1")),
                      "loop": {"alg_bytes_per_voxel_view_iteration": ALG_BYTES_PER_VOXEL_VIEW[cfg["dense_weights"]],
                               "achieved": loop_bytes / 1e9 / (ms * 1e-3), "frac": loop_bytes / 1e9 / (ms * 1e-3) / peak,
                               "frac_of_8TBs": loop_bytes / 1e9 / (ms * 1e-3) / 8000.0}},
         "e2e": {"value": e2e_value, "unit": "Gvoxel-iterations/s", "h2d_bytes_per_step": h2d / args.steps,
-                "d2h_bytes_per_step": d2h / args.steps, "seconds": e2e_s,
+                "d2h_bytes_per_step": d2h / args.steps, "seconds": e2e_s, "phase_seconds_rank0": e2e_phases,
                 "includes": "context creation, H2D of all views and weights (pinned), kernel spectra, psi init, %d iterations, mask, D2H of psi" % args.steps},
         "gpu_launches": int(launches), "clocks": clocks,
     }

@@ -33,7 +33,7 @@ g.manual_seed(1)
 imgs = [torch.rand((Z, Y, X), generator=g, device="cuda") * 0.9 + 0.05 for _ in range(V)]
 w = [torch.full((Z, Y, X), 1.0 / V, device="cuda") for _ in range(V)]
 dec = ShardedDeconvolution((X, Y, Z), imgs, w, k1, k2, 0.006, None, 0)
-L.check(lib.mvdSetDirectPath(dec.ctx, int(os.environ.get("MVD_PROF_DIRECT", "1"))), "mvdSetDirectPath")
+L.check(lib.mvdSetDirectPath(dec.ctx, int(os.environ.get("MVD_PROF_DIRECT", os.environ.get("MVD_PROF_SEP", "0")))), "mvdSetDirectPath")
 a_, b_ = C.c_int(), C.c_int()
 L.check(lib.mvdViewUsesDirectPath(dec.ctx, 0, C.byref(a_), C.byref(b_)), "mvdViewUsesDirectPath")
 print("view 0 direct-path classes (conv1, conv2):", a_.value, b_.value)
