@@ -326,13 +326,13 @@ def run_ours(args, cfg):
                    "lambda": LAMBDA, "step": "one iteration over all views", "brick_grid_xyz": list(grid),
                    "halo": "none" if world == 1 else ("fused: epilogue stores into peer ghost layers (NVLink) + barrier" if fused else "NCCL send/recv per axis"),
                    "l2": "inputs larger than L2 (%.1f GB resident per GPU)" % ((2 * V + 2) * nvox * 4 / world / 1e9),
-                   "scratch_mb": int(os.environ.get("MVD_SCRATCH_MB", "4096")), "batch_streams": int(os.environ.get("MVD_LANES", "1"))},
+                   "scratch_mb": int(os.environ.get("MVD_SCRATCH_MB", "4096")), "batch_streams": "1 + %d side lanes for sub-wave tile batches" % (int(os.environ.get("MVD_LANES", "4")) - 1)},
         "roofline": {"bound": "hbm", "kernel": names[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "achieved_bytes_per_launch": pb[top] / pl[top] if pl[top] else None, "peak_source": peak_src,
                      "share_of_step": pms[top] / sum(pms), "kernels": kern,
-                     "timing": "CUDA events around every launch, %d serial step(s) after the timed region: kernels %.1f ms/step, wall %.1f ms/step with the event calls; timed region %.1f ms/step with %s batch streams; share_of_step = kernel / sum of the three kernels"
-                               % (prof_steps, sum(pms) / prof_steps, prof_ms / prof_steps, ms / args.steps, os.environ.get("MVD_LANES", "1")),
+                     "timing": "CUDA events around every launch, %d serial step(s) after the timed region: kernels %.1f ms/step, wall %.1f ms/step with the event calls; timed region %.1f ms/step (MVD_LANES=%s); share_of_step = kernel / sum of the three kernels"
+                               % (prof_steps, sum(pms) / prof_steps, prof_ms / prof_steps, ms / args.steps, os.environ.get("MVD_LANES", "4")),
                      "loop": {"alg_bytes_per_voxel_view_iteration": ALG_BYTES_PER_VOXEL_VIEW[cfg["dense_weights"]],
                               "achieved": loop_bytes / 1e9 / (ms * 1e-3), "frac": loop_bytes / 1e9 / (ms * 1e-3) / peak,
                               "frac_of_8TBs": loop_bytes / 1e9 / (ms * 1e-3) / 8000.0}},

@@ -181,7 +181,8 @@ Device::Device(int id) : id_(id) {
         if (v > 0) mb = (size_t)v;
     }
     scratch_budget_ = mb << 20;
-    lanes_ = 1;
+    sm_count_ = prop.multiProcessorCount;
+    lanes_ = 4;  // the caller's stream + three side lanes for small batches (run_convolution)
     if (const char* s = std::getenv("MVD_LANES")) {
         const int v = std::atoi(s);
         if (v > 0) lanes_ = std::min(v, (int)Scratch::kMaxLanes);
@@ -301,10 +302,14 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
                      const EpilogueArgs& ep, Scratch& scratch, cudaStream_t st, Profiler* prof) {
     const double epi_bytes = epilogue == EPI_STORE ? 4.0 : (epilogue == EPI_QUOTIENT ? 8.0 : (ep.weight ? 12.0 : 8.0));
     scratch.init(dev.lanes());
-    // per-kernel event timing needs the launches back to back on one stream
+    // Lane 0 is the caller's stream: batches that fill the GPU run there back to back.  Batches whose
+    // grids are smaller than about two waves (the 64-wide windows at the end of an axis, bricks of a
+    // multi-GPU run) are dealt to the side lanes so that they overlap each other instead of each
+    // paying its own launch latency and tail.  Per-kernel event timing needs everything on one stream.
     const int lanes = prof ? 1 : scratch.lanes;
-    int used = 0, next = 0;
-    if (lanes > 1) MVD_CUDA(cudaEventRecord(scratch.fork, st));
+    const int small_grid = 2 * 3 * dev.sm_count();
+    int used = 0, next = 1;
+    bool forked = false;
     for (size_t ci = 0; ci < plan.classes.size(); ++ci) {
         const TileClass& c = plan.classes[ci];
         const int bx = c.b[0], by = c.b[1], bz = c.b[2];
@@ -313,13 +318,20 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
         const int n = (int)c.tiles.size();
         int batch = (int)std::max<size_t>(1, dev.scratch_budget_bytes() / (te * sizeof(float2)));
         batch = std::min(batch, n);
-        if (lanes > 1) batch = std::min(batch, std::max(1, (n + lanes - 1) / lanes));  // give every lane something to do
         for (int s = 0; s < n; s += batch) {
             const int cnt = std::min(batch, n - s);
-            const int li = lanes > 1 ? next : 0;
-            next = (next + 1) % lanes;
-            cudaStream_t ls = lanes > 1 ? scratch.lane[li] : st;
-            if (lanes > 1 && !(used >> li & 1)) {
+            const bool small = lanes > 1 && (long long)cnt * ((bz + 1) / 2) < small_grid;
+            int li = 0;
+            if (small) {
+                li = next;
+                next = next + 1 < lanes ? next + 1 : 1;
+            }
+            cudaStream_t ls = li ? scratch.lane[li] : st;
+            if (li && !(used >> li & 1)) {
+                if (!forked) {
+                    MVD_CUDA(cudaEventRecord(scratch.fork, st));
+                    forked = true;
+                }
                 MVD_CUDA(cudaStreamWaitEvent(ls, scratch.fork, 0));
                 used |= 1 << li;
             }
@@ -342,7 +354,7 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
         }
     }
     if (lanes > 1)
-        for (int li = 0; li < lanes; ++li)
+        for (int li = 1; li < lanes; ++li)
             if (used >> li & 1) {
                 MVD_CUDA(cudaEventRecord(scratch.join[li], scratch.lane[li]));
                 MVD_CUDA(cudaStreamWaitEvent(st, scratch.join[li], 0));

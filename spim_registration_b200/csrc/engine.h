@@ -72,6 +72,7 @@ public:
     const TwiddleTables& twiddles() const { return tw_; }
     size_t scratch_budget_bytes() const { return scratch_budget_; }
     int lanes() const { return lanes_; }
+    int sm_count() const { return sm_count_; }
     std::mutex legacy_mutex;  // serialises the drop-in symbol per device
 
 private:
@@ -80,12 +81,12 @@ private:
     TwiddleTables tw_{};
     size_t scratch_budget_;
     int lanes_ = 1;
+    int sm_count_ = 148;
 };
 
-// Scratch for the tile batches of one convolution stream.  Tile batches are independent, so they
-// are dealt round-robin to `lanes` auxiliary streams (each with its own scratch buffer): while one
-// batch sits in its latency-bound z pass another one runs its shared-memory-bound xy pass on the
-// same SMs.  The lanes fork from / join into the caller's stream with events.
+// Scratch for the tile batches of one convolution stream.  Lane 0 is the caller's stream; batches too
+// small to fill the GPU are dealt round-robin to the side lanes 1 .. lanes-1 (each with its own
+// scratch buffer), which fork from / join into the caller's stream with events.
 struct Scratch {
     static constexpr int kMaxLanes = 4;
     float2* data[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
