@@ -192,6 +192,26 @@ int mvdAttachPeer(mvdContext* ctx, const int peerBrickOffset[3], const int peerB
                   const void* quotient, int kind, int peerDevice);
 int mvdDetachPeers(mvdContext* ctx);
 
+/* Inputs of the loop produced on the device (the step before the loop).
+ * mvdTransformView = TransformInputAndWeights (TransformInputAndWeights.java:56-114) for one view:
+ *   src / srcDim      the view's image stack (x,y,z)
+ *   inverse           row-major 3x4 matrix world -> view coordinates, i.e. the inverse of the view's
+ *                     registration (AffineTransform3D.applyInverse, :100); world = output voxel + outOffset
+ *   outOffset, outDim bounding box of the deconvolved volume (ProcessForDeconvolution.java:198)
+ *   blendBorder/Range Blending parameters (ProcessForDeconvolution.java:545-559); used when outWeight != NULL
+ *   outImg            max(minValue, n-linear interpolation over the mirror-single extended view) inside
+ *                     the view, 0 outside (0 = no data); outWeight the cosine blending weight
+ *                     (BlendingRealRandomAccess.java:71-101), may be NULL (TransformInput.java:50-95).
+ * mvdNormalizeWeights = WeightNormalizer with directly applied normalisation (WeightNormalizer.java:
+ * 133-181: every weight divided by the sum over the views, 0/0 stays NaN as in the reference) followed by
+ * adjustForOSEM (ProcessForDeconvolution.java:351-362: w = min(1, w * osemSpeedup), skipped for 1.0);
+ * returns the minimal and the average number of views with weight > 0 per voxel (:97-101). */
+int mvdTransformView(int device, const float* src, const int srcDim[3], const double inverse[12], const int outOffset[3],
+                     const int outDim[3], const float blendBorder[3], const float blendRange[3], float minValue, float* outImg,
+                     float* outWeight, int srcMemKind, int outMemKind);
+int mvdNormalizeWeights(int device, float* const* weights, int numViews, long long numVoxels, double osemSpeedup,
+                        int* minOverlappingViews, double* avgOverlappingViews, int memKind);
+
 /* psi = 0 where no view has data (MVDeconvolution.java:180-187). */
 int mvdMaskNeverUpdated(mvdContext* ctx);
 

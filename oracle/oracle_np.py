@@ -224,6 +224,104 @@ def cuda_kernels(sigma, supported=(7, 15, 31, 63, 127)):
     return out
 
 
+# ---- inputs of the loop -------------------------------------------------
+def blending_lookup():
+    """BlendingRealRandomAccess.java:25-36: lookUp[round(d * 1000)] = (cos((1 - d) pi) + 1) / 2 for the
+    accumulated d = 0, 0.001, ... <= 1.0001."""
+    lut = np.zeros(1001, np.float64)
+    d = 0.0
+    while d <= 1.0001:
+        i = int(np.floor(d * 1000.0 + 0.5))
+        if 0 <= i <= 1000:
+            lut[i] = (np.cos((1 - d) * np.pi) + 1) / 2
+        d = d + 0.001
+    return lut
+
+
+def blending_weight(t, src_dim_xyz, border, blending, lut=None):
+    """BlendingRealRandomAccess.computeWeight (:71-101), float arithmetic as in the Java code.
+    t: float32 array [..., 3] of (x, y, z) positions in the view; the interval starts at 0."""
+    lut = blending_lookup() if lut is None else lut
+    t = np.asarray(t, dtype=F32)
+    out = np.ones(t.shape[:-1], F32)
+    zero = np.zeros(t.shape[:-1], bool)
+    for d in range(3):
+        l = t[..., d]
+        a = (l - F32(border[d])).astype(F32)
+        b = ((F32(src_dim_xyz[d] - 1) - l).astype(F32) - F32(border[d])).astype(F32)
+        dist = np.maximum(F32(0), np.minimum(a, b)).astype(F32)
+        zero |= dist == 0
+        rel = (dist / F32(blending[d])).astype(F32)
+        idx = np.floor(rel.astype(np.float64) * 1000.0 + 0.5).astype(np.int64)
+        fac = lut[np.clip(idx, 0, 1000)]
+        out = np.where(rel < 1, (out.astype(np.float64) * fac).astype(F32), out)
+    out[zero] = 0
+    return out
+
+
+def _mirror_single_index(i, n):
+    if n == 1:
+        return np.zeros_like(i)
+    p = 2 * n - 2
+    i = np.mod(i, p)
+    return np.where(i < n, i, p - i)
+
+
+def transform_input_and_weights(img, inverse, offset_xyz, out_dim_xyz, border=None, blending=None, min_value=MIN_VALUE):
+    """TransformInputAndWeights.loop (TransformInputAndWeights.java:81-114) for a whole bounding box.
+    img [z,y,x]; inverse: 3x4 float64 world -> view; returns (transformed [z,y,x], weights or None).
+    The n-linear interpolation (imglib2 NLinearInterpolator over Views.extendMirrorSingle, a dependency
+    outside the reference tree) is restated in double with one final rounding -- parity unpinned in the
+    last bit."""
+    inv = np.asarray(inverse, dtype=np.float64).reshape(3, 4)
+    X, Y, Z = out_dim_xyz
+    sz, sy, sx = img.shape
+    zz, yy, xx = np.meshgrid(np.arange(Z), np.arange(Y), np.arange(X), indexing="ij")
+    s = [(xx + offset_xyz[0]).astype(F32).astype(np.float64), (yy + offset_xyz[1]).astype(F32).astype(np.float64),
+         (zz + offset_xyz[2]).astype(F32).astype(np.float64)]
+    t = np.stack([(inv[d, 0] * s[0] + inv[d, 1] * s[1] + inv[d, 2] * s[2] + inv[d, 3]).astype(F32) for d in range(3)], axis=-1)
+    inside = ((t[..., 0] >= 0) & (t[..., 1] >= 0) & (t[..., 2] >= 0) & (t[..., 0] < F32(sx)) & (t[..., 1] < F32(sy)) & (t[..., 2] < F32(sz)))
+    td = t.astype(np.float64)
+    f = np.floor(td)
+    w = td - f
+    i0 = [_mirror_single_index(f[..., d].astype(np.int64), n) for d, n in enumerate((sx, sy, sz))]
+    i1 = [_mirror_single_index(f[..., d].astype(np.int64) + 1, n) for d, n in enumerate((sx, sy, sz))]
+    a = img.astype(np.float64)
+
+    def at(ix, iy, iz):
+        return a[iz, iy, ix]
+    c00 = at(i0[0], i0[1], i0[2]) * (1 - w[..., 0]) + at(i1[0], i0[1], i0[2]) * w[..., 0]
+    c10 = at(i0[0], i1[1], i0[2]) * (1 - w[..., 0]) + at(i1[0], i1[1], i0[2]) * w[..., 0]
+    c01 = at(i0[0], i0[1], i1[2]) * (1 - w[..., 0]) + at(i1[0], i0[1], i1[2]) * w[..., 0]
+    c11 = at(i0[0], i1[1], i1[2]) * (1 - w[..., 0]) + at(i1[0], i1[1], i1[2]) * w[..., 0]
+    c0 = c00 * (1 - w[..., 1]) + c10 * w[..., 1]
+    c1 = c01 * (1 - w[..., 1]) + c11 * w[..., 1]
+    val = (c0 * (1 - w[..., 2]) + c1 * w[..., 2]).astype(F32)
+    out = np.where(inside, np.maximum(F32(min_value), val), F32(0)).astype(F32)
+    weights = None if border is None else blending_weight(t, (sx, sy, sz), border, blending)
+    return out, weights
+
+
+def normalize_weights(weights):
+    """WeightNormalizer.ApplyDirectly (WeightNormalizer.java:133-181): w_v = (float)(w_v / sum_v w_v) with a
+    double sum -- always applied (the "sumW > 1" test is commented out there), so voxels without any
+    weight become NaN; returns (weights, min overlapping views, average overlapping views)."""
+    stack = np.stack([np.asarray(w, dtype=F32) for w in weights])
+    s = stack.astype(np.float64).sum(axis=0)
+    cnt = (stack > 0).sum(axis=0)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        out = [(w.astype(np.float64) / s).astype(F32) for w in stack]
+    return out, int(cnt.min()), float(cnt.mean())
+
+
+def adjust_for_osem(w, osemspeedup):
+    """ProcessForDeconvolution.adjustForOSEM (:351-362): min(1, w * (float)osemspeedup); Math.min keeps NaN."""
+    if osemspeedup == 1.0:
+        return w
+    v = (np.asarray(w, dtype=F32) * F32(osemspeedup)).astype(F32)
+    return np.where(np.isnan(v), v, np.minimum(F32(1), v)).astype(F32)
+
+
 def _conv_zero_same(inp, kernel):
     # new FFTConvolution(Views.extendZero(input), input, Views.extendZero(kernel), kernel, output)
     return convolve_extended(inp, kernel, "zero")

@@ -34,6 +34,15 @@ def main():
     dec = ShardedDeconvolution.__new__(ShardedDeconvolution)
     _init_brick(dec, dim, imgs, weights, k1, k2, bench.LAMBDA, 0, grid, rank, world)
     dec.lib.mvdFillPsi(dec.ctx, 1.0)
+    if os.environ.get("MVD_FAKE_PEERS", "0") == "1":
+        # the push code path without a second GPU: every neighbour's arrays are dummies on this device
+        dummies = []
+        for r, noff, nsize in dec.neighbours():
+            n = (nsize[0] + 32) * (nsize[1] + 30) * (nsize[2] + 30)
+            a, b = torch.empty(n, device="cuda"), torch.empty(n, device="cuda")
+            dummies.append((a, b))
+            L.check(lib.mvdAttachPeer(dec.ctx, L.int3(noff), L.int3(nsize), C.c_void_p(a.data_ptr()), C.c_void_p(b.data_ptr()), 0, -1), "mvdAttachPeer")
+        print("attached %d fake peers" % len(dummies))
     V = dec.V
 
     def run(n):

@@ -51,6 +51,9 @@ PROTOTYPES = {
     "mvdProfileStart": (C.c_int, [C.c_void_p]),
     "mvdProfileStop": (C.c_int, [C.c_void_p, c_double_p, c_ll_p, c_double_p]),
     "mvdArrayInfo": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), c_int_p, c_int_p]),
+    "mvdTransformView": (C.c_int, [C.c_int, C.c_void_p, c_int_p, c_double_p, c_int_p, c_int_p, c_float_p, c_float_p, C.c_float, C.c_void_p,
+                                   C.c_void_p, C.c_int, C.c_int]),
+    "mvdNormalizeWeights": (C.c_int, [C.c_int, C.POINTER(C.c_void_p), C.c_int, C.c_longlong, C.c_double, c_int_p, c_double_p, C.c_int]),
     "mvdSetDirectPath": (C.c_int, [C.c_void_p, C.c_int]),
     "mvdViewUsesDirectPath": (C.c_int, [C.c_void_p, C.c_int, c_int_p, c_int_p]),
     "mvdExportArrays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -5,11 +5,13 @@
 #include <cstring>
 #include <limits>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
 #include "../../include/mvdecon.h"
 #include "engine.h"
+#include "input_kernels.h"
 #include "sep_kernels.h"
 #include "volume_kernels.h"
 
@@ -764,6 +766,131 @@ extern "C" int mvdMaskNeverUpdated(mvdContext* c) {
         MVD_CUDA(launch_mask_never_updated(c->view_ptrs(), c->bdim, c->psi, c->adim, c->glo, c->stream));
         ++g_kernel_launches;
         MVD_CUDA(cudaStreamSynchronize(c->stream));
+    });
+}
+
+// ---- inputs of the loop, produced on the device ----------------------------------------------
+namespace {
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    void alloc(size_t bytes) { MVD_CUDA(cudaMalloc(&p, bytes)); }
+};
+struct StreamGuard {
+    cudaStream_t st = nullptr;
+    StreamGuard() { MVD_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)); }
+    ~StreamGuard() { if (st) cudaStreamDestroy(st); }
+};
+void use_device(int device) {
+    int n_dev = 0;
+    MVD_CUDA(cudaGetDeviceCount(&n_dev));
+    require(device >= 0 && device < n_dev, "no such CUDA device (this library has no CPU path)");
+    MVD_CUDA(cudaSetDevice(device));
+    Device::get(device);  // checks the architecture, uploads the tables
+    static std::mutex m;
+    static std::vector<char> done;
+    std::lock_guard<std::mutex> lock(m);
+    if ((int)done.size() < n_dev) done.resize(n_dev, 0);
+    if (!done[device]) {
+        MVD_CUDA(upload_blend_table());
+        done[device] = 1;
+    }
+}
+}  // namespace
+
+extern "C" int mvdTransformView(int device, const float* src, const int srcDim[3], const double inverse[12], const int outOffset[3],
+                                const int outDim[3], const float blendBorder[3], const float blendRange[3], float minValue, float* outImg,
+                                float* outWeight, int srcMemKind, int outMemKind) {
+    return guarded([&] {
+        require(src && srcDim && inverse && outOffset && outDim && outImg, "mvdTransformView: null argument");
+        require(!outWeight || (blendBorder && blendRange), "mvdTransformView: weights need blendBorder and blendRange");
+        use_device(device);
+        TransformArgs a;
+        std::memset(&a, 0, sizeof(a));
+        for (int i = 0; i < 12; ++i) a.inv[i] = inverse[i];
+        for (int d = 0; d < 3; ++d) {
+            require(srcDim[d] > 0 && outDim[d] > 0, "mvdTransformView: empty image");
+            a.src_dim[d] = srcDim[d];
+            a.out_dim[d] = outDim[d];
+            a.offset[d] = outOffset[d];
+            a.border[d] = blendBorder ? blendBorder[d] : 0.f;
+            a.blending[d] = blendRange ? blendRange[d] : 1.f;
+        }
+        a.min_value = minValue;
+        const size_t ns = (size_t)srcDim[0] * srcDim[1] * srcDim[2], no = (size_t)outDim[0] * outDim[1] * outDim[2];
+        StreamGuard sg;
+        DevBuf dsrc, dimg, dw;
+        const float* s = src;
+        if (srcMemKind != MVD_MEM_DEVICE) {
+            dsrc.alloc(ns * sizeof(float));
+            MVD_CUDA(cudaMemcpyAsync(dsrc.p, src, ns * sizeof(float), cudaMemcpyHostToDevice, sg.st));
+            s = static_cast<const float*>(dsrc.p);
+        }
+        float* oi = outImg;
+        float* ow = outWeight;
+        if (outMemKind != MVD_MEM_DEVICE) {
+            dimg.alloc(no * sizeof(float));
+            oi = static_cast<float*>(dimg.p);
+            if (outWeight) {
+                dw.alloc(no * sizeof(float));
+                ow = static_cast<float*>(dw.p);
+            }
+        }
+        MVD_CUDA(launch_transform_view(s, a, oi, ow, sg.st));
+        ++g_kernel_launches;
+        if (outMemKind != MVD_MEM_DEVICE) {
+            MVD_CUDA(cudaMemcpyAsync(outImg, oi, no * sizeof(float), cudaMemcpyDeviceToHost, sg.st));
+            if (outWeight) MVD_CUDA(cudaMemcpyAsync(outWeight, ow, no * sizeof(float), cudaMemcpyDeviceToHost, sg.st));
+        }
+        MVD_CUDA(cudaStreamSynchronize(sg.st));
+    });
+}
+
+extern "C" int mvdNormalizeWeights(int device, float* const* weights, int numViews, long long numVoxels, double osemSpeedup,
+                                   int* minOverlappingViews, double* avgOverlappingViews, int memKind) {
+    return guarded([&] {
+        require(weights && numViews > 0 && numViews <= kMaxViews && numVoxels > 0, "mvdNormalizeWeights: bad argument");
+        use_device(device);
+        const size_t n = (size_t)numVoxels;
+        StreamGuard sg;
+        std::vector<DevBuf> bufs(memKind == MVD_MEM_DEVICE ? 0 : numViews);
+        WeightPtrs wp;
+        wp.n = numViews;
+        for (int v = 0; v < numViews; ++v) {
+            require(weights[v], "mvdNormalizeWeights: null weight image");
+            if (memKind == MVD_MEM_DEVICE) {
+                wp.w[v] = weights[v];
+            } else {
+                bufs[v].alloc(n * sizeof(float));
+                MVD_CUDA(cudaMemcpyAsync(bufs[v].p, weights[v], n * sizeof(float), cudaMemcpyHostToDevice, sg.st));
+                wp.w[v] = static_cast<float*>(bufs[v].p);
+            }
+        }
+        DevBuf stats;
+        stats.alloc(16);
+        unsigned long long* d_count = static_cast<unsigned long long*>(stats.p);
+        int* d_min = reinterpret_cast<int*>(d_count + 1);
+        const unsigned long long zero = 0;
+        const int big = numViews;
+        MVD_CUDA(cudaMemcpyAsync(d_count, &zero, sizeof(zero), cudaMemcpyHostToDevice, sg.st));
+        MVD_CUDA(cudaMemcpyAsync(d_min, &big, sizeof(big), cudaMemcpyHostToDevice, sg.st));
+        MVD_CUDA(launch_normalize_weights(wp, n, d_count, d_min, sg.st));
+        ++g_kernel_launches;
+        if (osemSpeedup != 1.0 && osemSpeedup > 0.0)
+            for (int v = 0; v < numViews; ++v) {
+                MVD_CUDA(launch_osem(wp.w[v], n, (float)osemSpeedup, sg.st));
+                ++g_kernel_launches;
+            }
+        unsigned long long cnt = 0;
+        int mn = 0;
+        MVD_CUDA(cudaMemcpyAsync(&cnt, d_count, sizeof(cnt), cudaMemcpyDeviceToHost, sg.st));
+        MVD_CUDA(cudaMemcpyAsync(&mn, d_min, sizeof(mn), cudaMemcpyDeviceToHost, sg.st));
+        if (memKind != MVD_MEM_DEVICE)
+            for (int v = 0; v < numViews; ++v)
+                MVD_CUDA(cudaMemcpyAsync(weights[v], wp.w[v], n * sizeof(float), cudaMemcpyDeviceToHost, sg.st));
+        MVD_CUDA(cudaStreamSynchronize(sg.st));
+        if (minOverlappingViews) *minOverlappingViews = mn;
+        if (avgOverlappingViews) *avgOverlappingViews = (double)cnt / (double)n;
     });
 }
 

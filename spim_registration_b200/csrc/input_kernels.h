@@ -1,0 +1,29 @@
+// Device-side preparation of the loop's inputs (see input_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "volume_kernels.h"
+
+namespace mvd {
+
+struct TransformArgs {
+    double inv[12];     // row-major 3x4: world (output voxel + offset) -> view voxel coordinates
+    int offset[3];      // bounding-box minimum (ProcessForDeconvolution.java:198)
+    int out_dim[3];
+    int src_dim[3];
+    float border[3];    // Blending: pixels skipped before the blending starts
+    float blending[3];  // Blending: width of the cosine ramp
+    float min_value;    // MVDeconvolution.minValue (1e-4f)
+};
+
+struct WeightPtrs {
+    float* w[kMaxViews];
+    int n;
+};
+
+cudaError_t upload_blend_table();
+cudaError_t launch_transform_view(const float* src, const TransformArgs& a, float* out_img, float* out_w, cudaStream_t st);
+cudaError_t launch_normalize_weights(const WeightPtrs& w, size_t n, unsigned long long* d_count, int* d_min, cudaStream_t st);
+cudaError_t launch_osem(float* w, size_t n, float speedup, cudaStream_t st);
+
+}  // namespace mvd

@@ -364,3 +364,68 @@ def test_extracted_psfs_stay_on_the_fft_engine(m, o):
     imgs = [_rand((24, 28, 32), 20 + v) for v in range(2)]
     dec = m.MVDeconvolution(_views(m, imgs, [0.5, 0.5], psfs), "EFFICIENT_BAYESIAN", 1, 0.006)
     assert all(a == 0 and b == 0 for a, b in dec.directPath), dec.directPath
+
+
+# ---- inputs of the loop produced on the device ---------------------------------
+def _registration(angle_deg, scale_z, shift):
+    a = np.deg2rad(angle_deg)
+    m = np.eye(4)
+    m[:3, :3] = np.array([[np.cos(a), 0, np.sin(a)], [0, 1, 0], [-np.sin(a), 0, np.cos(a)]]) @ np.diag([1.0, 1.0, scale_z])
+    m[:3, 3] = shift
+    return m
+
+
+@pytest.mark.parametrize("angle,border,blend", [(0.0, (0, 0, 0), (8, 8, 4)), (35.0, (3, 2, 1), (10, 12, 6)), (90.0, (-2, 0, 0), (5, 5, 5))])
+def test_transform_view_and_weights_match_oracle(m, o, angle, border, blend):
+    """mvdTransformView == TransformInputAndWeights restated by the oracle: resampled view bit-close, weights exact."""
+    rng = np.random.default_rng(11)
+    img = rng.random((30, 44, 52), dtype=np.float32) * np.float32(0.9)
+    reg = _registration(angle, 2.5, (20.0, 5.0, 30.0))
+    offset, dims = (-10, -4, -8), (120, 60, 110)
+    got_t, got_w = m.transformInputAndWeights(img, reg, offset, dims, border, blend)
+    inv = np.linalg.inv(reg)[:3, :4]
+    ref_t, ref_w = o.transform_input_and_weights(img, inv, offset, dims, border, blend)
+    assert (ref_t > 0).mean() > 0.05                       # the view really lies inside the box
+    np.testing.assert_array_equal(got_t == 0, ref_t == 0)  # same "no data" set
+    np.testing.assert_allclose(got_t, ref_t, rtol=0, atol=2e-7)
+    np.testing.assert_allclose(got_w, ref_w, rtol=0, atol=1e-7)
+    only_t, none_w = m.transformInputAndWeights(img, reg, offset, dims)  # TransformInput: no weights
+    assert none_w is None
+    np.testing.assert_array_equal(only_t, got_t)
+
+
+def test_weight_normalizer_matches_oracle(m, o):
+    rng = np.random.default_rng(12)
+    ws = [np.where(rng.random((20, 30, 40)) < 0.3, 0, rng.random((20, 30, 40))).astype(np.float32) for _ in range(4)]
+    ref, mn, avg = o.normalize_weights(ws)
+    for speed in (1.0, 2.0):
+        wn = m.WeightNormalizer([w.copy() for w in ws])
+        assert wn.process(speed)
+        assert wn.getMinOverlappingViews() == mn and abs(wn.getAvgOverlappingViews() - avg) < 1e-9
+        for a, b in zip(wn.weights, ref):
+            np.testing.assert_array_equal(a, o.adjust_for_osem(b, speed))  # NaN == NaN position-wise, values bit-exact
+
+
+def test_device_prepared_inputs_drive_the_loop(m, o):
+    """Views resampled and weighted on the device, then deconvolved: same result as the oracle fed with the oracle's inputs."""
+    from spim_registration_b200 import synthetic
+    rng = np.random.default_rng(13)
+    dims, offset, V = (64, 48, 40), (0, 0, 0), 3
+    truth = synthetic.make_truth(dims[::-1], "blob", 5)
+    imgs_d, ws_d, imgs_o, ws_o = [], [], [], []
+    for v in range(V):
+        reg = _registration(0.0, 1.0, (3.0 * v, -2.0 * v, 1.5 * v))
+        raw = (truth + np.float32(0.02) * rng.random(truth.shape, dtype=np.float32)).astype(np.float32)
+        t, w = m.transformInputAndWeights(raw, reg, offset, dims, (0, 0, 0), (6, 6, 6))
+        to, wo = o.transform_input_and_weights(raw, np.linalg.inv(reg)[:3, :4], offset, dims, (0, 0, 0), (6, 6, 6))
+        imgs_d.append(t); ws_d.append(w); imgs_o.append(to); ws_o.append(wo)
+    wn = m.WeightNormalizer(ws_d)
+    wn.process(1.0)
+    ws_o, _, _ = o.normalize_weights(ws_o)
+    ws_dn = [np.nan_to_num(w, nan=0.0) for w in wn.weights]   # voxels outside every view: no data, weight irrelevant
+    ws_on = [np.nan_to_num(w, nan=0.0) for w in ws_o]
+    psfs = synthetic.make_psfs(V, (7, 7, 7), extracted=True)
+    k1, k2 = o.init_kernels(psfs, "EFFICIENT_BAYESIAN", 8)
+    ref, _, _ = o.run_deconvolution(imgs_o, ws_on, k1, k2, 3, 0.006)
+    dec = m.MVDeconvolution(_views(m, imgs_d, ws_dn, psfs), "EFFICIENT_BAYESIAN", 3, 0.006)
+    assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL

@@ -270,3 +270,51 @@ def test_gaussian_kernels_of_the_hook():
     import spim_registration_b200 as m
     for a, b in zip(m.CUDASeparableConvolutionFunctions.getCUDAKernels([1.8, 1.8, 2.5]), ks):
         np.testing.assert_array_equal(a, b)
+
+
+# ---- inputs of the loop: resampling, blending weights, weight normalisation ------
+def test_blending_weight_known_values():
+    """BlendingRealRandomAccess.computeWeight: 0 on and outside the border, cosine ramp of `blending`
+    pixels, 1 in the interior, product over the dimensions; the lookup table quantises the ramp to 1/1000."""
+    lut = o.blending_lookup()
+    assert lut[0] == 0 and abs(lut[500] - 0.5) < 1e-12 and lut[1000] == 1 and np.all(np.diff(lut) >= 0)
+    dim, border, blend = (101, 81, 61), (5.0, 0.0, 0.0), (10.0, 20.0, 12.0)
+    t = np.array([[50, 40, 30], [5, 40, 30], [4, 40, 30], [10, 40, 30], [50, 0, 30], [50, 10, 30], [95, 40, 30], [50, 40, 60], [7.5, 5, 30]], np.float32)
+    w = o.blending_weight(t, dim, border, blend)
+    ramp = lambda d: (np.cos((1 - d) * np.pi) + 1) / 2
+    assert w[0] == 1 and w[1] == 0 and w[2] == 0 and w[4] == 0 and w[7] == 0
+    assert abs(w[3] - ramp(0.5)) < 2e-3 and abs(w[5] - ramp(0.5)) < 2e-3 and abs(w[6] - ramp(0.0)) < 1e-6  # x = 95 = 100 - 5: on the border
+    assert abs(w[8] - ramp(0.25) * ramp(0.25)) < 4e-3
+
+
+def test_transform_identity_translation_and_outside():
+    rng = np.random.default_rng(5)
+    img = rng.random((6, 7, 8), dtype=np.float32) + np.float32(0.01)
+    ident = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, 0]], float)
+    t, w = o.transform_input_and_weights(img, ident, (0, 0, 0), (8, 7, 6))
+    np.testing.assert_array_equal(t, img)           # integer positions: interpolation reproduces the samples
+    assert w is None
+    # the bounding box starts at (-2, 1, 0): voxel x of the box is view x - 2 ... and half-voxel shifts average neighbours
+    t2, _ = o.transform_input_and_weights(img, ident, (-2, 1, 0), (8, 7, 6))
+    np.testing.assert_array_equal(t2[:, :-1, 2:], img[:, 1:, :-2])
+    assert (t2[:, :, :2] == 0).all() and (t2[:, -1, :] == 0).all()   # outside the view: 0 = no data
+    half = ident.copy()
+    half[0, 3] = 0.5
+    t3, _ = o.transform_input_and_weights(img, half, (0, 0, 0), (8, 7, 6))
+    np.testing.assert_allclose(t3[:, :, :-1], (img[:, :, :-1].astype(np.float64) + img[:, :, 1:]) / 2, rtol=1e-6)
+    np.testing.assert_allclose(t3[:, :, -1], (img[:, :, -1].astype(np.float64) + img[:, :, -2]) / 2, rtol=1e-6)  # mirror-single beyond the last sample
+    dark = np.zeros((3, 3, 3), np.float32)
+    t4, _ = o.transform_input_and_weights(dark, ident, (0, 0, 0), (3, 3, 3))
+    assert (t4 == o.MIN_VALUE).all()                # inside the view the value never drops to the "no data" marker
+
+
+def test_weight_normalisation_and_osem():
+    w = [np.array([0.5, 0.2, 0.0, 0.0], np.float32), np.array([1.0, 0.2, 0.3, 0.0], np.float32)]
+    n, mn, avg = o.normalize_weights(w)
+    np.testing.assert_allclose(n[0][:3], [1 / 3, 0.5, 0.0], rtol=1e-6)
+    np.testing.assert_allclose(n[1][:3], [2 / 3, 0.5, 1.0], rtol=1e-6)
+    assert np.isnan(n[0][3]) and np.isnan(n[1][3])  # 0 / 0, exactly what WeightNormalizer.java:171 does
+    assert mn == 0 and abs(avg - 5 / 4) < 1e-12
+    a = o.adjust_for_osem(n[1], 2.0)
+    np.testing.assert_allclose(a[:3], [1.0, 1.0, 1.0])
+    assert np.isnan(a[3]) and o.adjust_for_osem(n[1], 1.0) is n[1]
