@@ -55,12 +55,13 @@ __device__ __forceinline__ float blend_weight(const float t[3], const int dim_mi
 
 __global__ void __launch_bounds__(256) transform_view_kernel(const float* __restrict__ src, TransformArgs a, float* __restrict__ out_img,
                                                              float* __restrict__ out_w) {
-    const size_t n = (size_t)a.out_dim[0] * a.out_dim[1] * a.out_dim[2];
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const int x = (int)(i % a.out_dim[0]);
-        const size_t r = i / a.out_dim[0];
+    // grid: x = chunks of a row, y = rows (y + Y * z) in a grid-stride loop
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const long long rows = (long long)a.out_dim[1] * a.out_dim[2];
+    if (x >= a.out_dim[0]) return;
+    for (long long r = blockIdx.y; r < rows; r += gridDim.y) {
         const int y = (int)(r % a.out_dim[1]), z = (int)(r / a.out_dim[1]);
+        const size_t i = (size_t)r * a.out_dim[0] + x;
         // s = voxel + offset as floats, t = inverse * s evaluated in double and stored as float (applyInverse(float[], float[]))
         const double s0 = (double)(float)(x + a.offset[0]), s1 = (double)(float)(y + a.offset[1]), s2 = (double)(float)(z + a.offset[2]);
         float t[3];
@@ -160,7 +161,9 @@ cudaError_t upload_blend_table() {
 cudaError_t launch_transform_view(const float* src, const TransformArgs& a, float* out_img, float* out_w, cudaStream_t st) {
     const size_t n = (size_t)a.out_dim[0] * a.out_dim[1] * a.out_dim[2];
     if (n == 0) return cudaSuccess;
-    transform_view_kernel<<<grid_for(n), 256, 0, st>>>(src, a, out_img, out_w);
+    const long long rows = (long long)a.out_dim[1] * a.out_dim[2];
+    const dim3 grid((a.out_dim[0] + 255) / 256, (unsigned)(rows < 65535 ? rows : 65535));
+    transform_view_kernel<<<grid, 256, 0, st>>>(src, a, out_img, out_w);
     return cudaGetLastError();
 }
 
