@@ -179,6 +179,7 @@ struct mvdContext {
         for (size_t i = 0; i < plans.size(); ++i)
             if (same_plan(*plans[i], bdim, k)) return (int)i;
         plans.push_back(make_plan(bdim, k));
+        if (!peers_psi.empty()) partition_for_peers(*plans.back(), peers_psi.data(), (int)peers_psi.size());
         return (int)plans.size() - 1;
     }
     void ensure_stats(int n) {
@@ -302,6 +303,7 @@ static void detach_peers(mvdContext* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->peers_psi.clear();
     c->peers_quot.clear();
+    for (auto& plan : c->plans) partition_for_peers(*plan, nullptr, 0);
     if (c->d_peers_psi) cudaFree(c->d_peers_psi);
     if (c->d_peers_quot) cudaFree(c->d_peers_quot);
     c->d_peers_psi = c->d_peers_quot = nullptr;
@@ -748,6 +750,7 @@ extern "C" int mvdAttachPeer(mvdContext* c, const int peerBrickOffset[3], const 
         }
         MVD_CUDA(cudaMemcpy(c->d_peers_psi, c->peers_psi.data(), c->peers_psi.size() * sizeof(PeerTarget), cudaMemcpyHostToDevice));
         MVD_CUDA(cudaMemcpy(c->d_peers_quot, c->peers_quot.data(), c->peers_quot.size() * sizeof(PeerTarget), cudaMemcpyHostToDevice));
+        for (auto& plan : c->plans) partition_for_peers(*plan, c->peers_psi.data(), (int)c->peers_psi.size());
     });
 }
 

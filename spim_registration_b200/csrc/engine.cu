@@ -297,6 +297,23 @@ Profiler::~Profiler() {
     for (auto& r : recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
 }
 
+void partition_for_peers(ConvPlan& plan, const PeerTarget* peers, int n) {
+    for (TileClass& c : plan.classes) {
+        auto interior = [&](const Tile& t) {
+            for (int p = 0; p < n; ++p) {
+                bool hit = true;
+                for (int d = 0; d < 3; ++d) hit = hit && t.e[d] < peers[p].hi[d] && t.e[d] + t.n[d] > peers[p].lo[d];
+                if (hit) return false;
+            }
+            return true;
+        };
+        const auto mid = std::stable_partition(c.tiles.begin(), c.tiles.end(), interior);
+        c.n_interior = n > 0 ? (int)(mid - c.tiles.begin()) : -1;
+        if (c.d_tiles && !c.tiles.empty())
+            MVD_CUDA(cudaMemcpy(c.d_tiles, c.tiles.data(), c.tiles.size() * sizeof(Tile), cudaMemcpyHostToDevice));
+    }
+}
+
 // ---- convolution -----------------------------------------------------------------------
 void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spec, const Volume& src, int epilogue,
                      const EpilogueArgs& ep, Scratch& scratch, cudaStream_t st, Profiler* prof) {
@@ -348,9 +365,27 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
             if (prof) { prof->end(ls); prof->begin(1, cnt * pe * bz * 8.0 + pe * bz * 8.0 + nz_sum * pe * 8.0, ls); }
             MVD_CUDA(launch_z_pass(bx, by, bz, 1, buf, spec.per_class[ci], c.d_tiles + s, cnt, 1.f, dev.twiddles(), ls));
             if (prof) { prof->end(ls); prof->begin(2, nz_sum * pe * 8.0 + out_vox * epi_bytes, ls); }
-            MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, buf, c.d_tiles + s, cnt, c.max_nz, ep, dev.twiddles(), ls));
+            if (ep.n_peers > 0 && c.n_interior >= 0) {
+                // interior tiles with the plain epilogue, tiles at the brick faces with the one that also
+                // stores into the neighbours' ghost layers
+                const int a = std::max(0, std::min(cnt, c.n_interior - s));
+                EpilogueArgs plain = ep;
+                plain.peers = nullptr;
+                plain.n_peers = 0;
+                if (a > 0) {
+                    MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, buf, c.d_tiles + s, a, c.max_nz, plain, dev.twiddles(), ls));
+                    ++g_kernel_launches;
+                }
+                if (cnt - a > 0) {
+                    MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, buf + (size_t)a * te, c.d_tiles + s + a, cnt - a, c.max_nz, ep, dev.twiddles(), ls));
+                    ++g_kernel_launches;
+                }
+                g_kernel_launches += 2;
+            } else {
+                MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, buf, c.d_tiles + s, cnt, c.max_nz, ep, dev.twiddles(), ls));
+                g_kernel_launches += 3;
+            }
             if (prof) prof->end(ls);
-            g_kernel_launches += 3;
         }
     }
     if (lanes > 1)

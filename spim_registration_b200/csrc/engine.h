@@ -38,6 +38,9 @@ struct TileClass {
     std::vector<Tile> tiles;
     Tile* d_tiles = nullptr;  // device copy
     int max_nz = 0;
+    // fused ghost exchange: tiles [0, n_interior) touch no neighbour's ghost layers and run the plain
+    // epilogue, the rest runs the PUSH epilogue (partition_for_peers); -1 = not partitioned
+    int n_interior = -1;
 };
 
 struct ConvPlan {
@@ -53,6 +56,9 @@ struct ConvPlan {
 // Builds the plan and uploads the tile lists to the current device.
 std::unique_ptr<ConvPlan> make_plan(const int dim[3], const int k[3]);
 bool same_plan(const ConvPlan& p, const int dim[3], const int k[3]);
+// Orders the tiles of every class interior first (stable) with respect to the neighbours' boxes and
+// uploads them again; n = 0 removes the partition.  No kernel using the plan may be in flight.
+void partition_for_peers(ConvPlan& plan, const PeerTarget* peers, int n);
 
 // Spectra of one kernel for every tile class of a plan (resident in HBM).
 struct KernelSpectra {
