@@ -241,7 +241,7 @@ static void ghost_geometry(const int gdim[3], const int boff[3], const int bdim[
     for (int d = 0; d < 3; ++d) {
         glo[d] = std::min(ghost[d], boff[d]);
         ghi[d] = std::min(ghost[d], gdim[d] - (boff[d] + bdim[d]));
-        if (d == 0) {
+        if (d == 0 && ghost[0] > 0) {  // only bricks with x neighbours are padded: a whole volume keeps its own extent
             if (glo[0] > 0) glo[0] = (glo[0] + 3) / 4 * 4;
             const int rem = (bdim[0] + glo[0] + ghi[0]) % 4;
             if (rem) ghi[0] += 4 - rem;

@@ -429,3 +429,40 @@ def test_device_prepared_inputs_drive_the_loop(m, o):
     ref, _, _ = o.run_deconvolution(imgs_o, ws_on, k1, k2, 3, 0.006)
     dec = m.MVDeconvolution(_views(m, imgs_d, ws_dn, psfs), "EFFICIENT_BAYESIAN", 3, 0.006)
     assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
+
+
+# ---- edge cases of the loop ------------------------------------------------------------------------
+@pytest.mark.parametrize("shape,ksize", [
+    ((1, 40, 44), (1, 7, 7)),        # a single plane: 2-d deconvolution
+    ((9, 10, 11), (15, 15, 15)),     # kernel larger than the volume: repeated reflection in conv1, mostly "outside = 1" in conv2
+    ((33, 37, 41), (5, 6, 8)),       # odd sizes, even kernel extents (centre K // 2, Mirror's even-size quirk in kernel2)
+    ((20, 24, 131), (3, 3, 31)),     # widest kernel the 128-wide window supports, in x only
+])
+def test_loop_edge_shapes_match_oracle(m, o, shape, ksize):
+    rng = np.random.default_rng(21)
+    V, iters = 2, 3
+    psfs = [(rng.random(ksize, dtype=np.float32) + np.float32(0.05)) for _ in range(V)]
+    imgs = [rng.random(shape, dtype=np.float32) + np.float32(0.05) for _ in range(V)]
+    imgs[1][..., : shape[2] // 3] = 0                                  # a slab without data in one view
+    weights = [np.float32(0.5)] * V
+    k1, k2 = o.init_kernels(psfs, "OPTIMIZATION_I", 8)
+    ref, _, _ = o.run_deconvolution(imgs, weights, k1, k2, iters, 0.006)
+    dec = m.MVDeconvolution(_views(m, imgs, [0.5, 0.5], psfs), "OPTIMIZATION_I", iters, 0.006)
+    assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
+
+
+def test_view_without_any_data_and_never_updated_voxels(m, o):
+    """One view is empty (all zeros = no data): its quotient is 1 everywhere and it must not disturb the result;
+    voxels no view covers end as 0 (MVDeconvolution.java:180-187)."""
+    rng = np.random.default_rng(22)
+    shape = (24, 28, 36)
+    psfs = [(rng.random((5, 5, 5), dtype=np.float32) + np.float32(0.05)) for _ in range(3)]
+    imgs = [rng.random(shape, dtype=np.float32) + np.float32(0.05) for _ in range(3)]
+    imgs[2][:] = 0
+    imgs[0][:, :, 30:] = 0
+    imgs[1][:, :, 30:] = 0
+    k1, k2 = o.init_kernels(psfs, "EFFICIENT_BAYESIAN", 8)
+    ref, _, _ = o.run_deconvolution(imgs, [np.float32(1 / 3)] * 3, k1, k2, 3, 0.006)
+    dec = m.MVDeconvolution(_views(m, imgs, [1 / 3] * 3, psfs), "EFFICIENT_BAYESIAN", 3, 0.006)
+    assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
+    assert (dec.getPsi()[:, :, 30:] == 0).all() and (dec.getPsi()[:, :, :30] > 0).all()
