@@ -212,6 +212,19 @@ int mvdTransformView(int device, const float* src, const int srcDim[3], const do
 int mvdNormalizeWeights(int device, float* const* weights, int numViews, long long numVoxels, double osemSpeedup,
                         int* minOverlappingViews, double* avgOverlappingViews, int memKind);
 
+/* PSF extraction (ExtractPSF.java).
+ * mvdExtractPSF = extractPSFLocal (:353-394): psf(v) = sum over the bead locations (x,y,z triples, view
+ *   coordinates) of the view sampled n-linearly with periodic extension at v - psfSize/2 + location, float
+ *   accumulation in the order given; normalize != 0 applies ExtractPSF.normalize (:277-295, min-max to [0,1]).
+ * mvdTransformedPSFSize / mvdTransformPSF = transformPSF (:304-346) + transform (:396-437): the PSF resampled
+ *   (zero outside) through the view's model (row-major 3x4, view -> world) into an odd-sized image whose
+ *   centre is the transformed centre voxel; newDim comes from mvdTransformedPSFSize (host only).
+ * psf / out are host arrays (PSFs are small). */
+int mvdExtractPSF(int device, const float* img, const int imgDim[3], const double* locations, int numLocations,
+                  const int psfSize[3], int normalize, float* psf, int imgMemKind);
+int mvdTransformedPSFSize(const int psfDim[3], const double model[12], int newDim[3]);
+int mvdTransformPSF(int device, const float* psf, const int psfDim[3], const double model[12], const int newDim[3], float* out);
+
 /* psi = 0 where no view has data (MVDeconvolution.java:180-187). */
 int mvdMaskNeverUpdated(mvdContext* ctx);
 

@@ -322,6 +322,97 @@ def adjust_for_osem(w, osemspeedup):
     return np.where(np.isnan(v), v, np.minimum(F32(1), v)).astype(F32)
 
 
+# ---- PSF extraction (ExtractPSF.java) -----------------------------------------
+def _sample_linear(img, px, py, pz, mode):
+    """n-linear interpolation of img [z,y,x] at double positions (arrays); mode "zero" (Views.extendZero)
+    or "periodic" (Views.extendPeriodic).  imglib2's interpolator is outside the reference tree: restated
+    in double, one final rounding by the caller (parity unpinned in the last bit)."""
+    sz, sy, sx = img.shape
+    a = img.astype(np.float64)
+    idx, w, ok = [], [], []
+    for p, n in ((px, sx), (py, sy), (pz, sz)):
+        f = np.floor(p)
+        w.append(p - f)
+        i0, i1 = f.astype(np.int64), f.astype(np.int64) + 1
+        if mode == "periodic":
+            idx.append((np.mod(i0, n), np.mod(i1, n)))
+            ok.append((np.ones(i0.shape, bool), np.ones(i0.shape, bool)))
+        else:
+            ok.append(((i0 >= 0) & (i0 < n), (i1 >= 0) & (i1 < n)))
+            idx.append((np.clip(i0, 0, n - 1), np.clip(i1, 0, n - 1)))
+
+    def at(bx, by, bz):
+        v = a[idx[2][bz], idx[1][by], idx[0][bx]]
+        return np.where(ok[0][bx] & ok[1][by] & ok[2][bz], v, 0.0)
+    c00 = at(0, 0, 0) * (1 - w[0]) + at(1, 0, 0) * w[0]
+    c10 = at(0, 1, 0) * (1 - w[0]) + at(1, 1, 0) * w[0]
+    c01 = at(0, 0, 1) * (1 - w[0]) + at(1, 0, 1) * w[0]
+    c11 = at(0, 1, 1) * (1 - w[0]) + at(1, 1, 1) * w[0]
+    c0 = c00 * (1 - w[1]) + c10 * w[1]
+    c1 = c01 * (1 - w[1]) + c11 * w[1]
+    return c0 * (1 - w[2]) + c1 * w[2]
+
+
+def extract_psf_local(img, locations, size_xyz):
+    """ExtractPSF.extractPSFLocal (:353-394): float accumulation over the bead locations (x,y,z) in order."""
+    X, Y, Z = size_xyz
+    zz, yy, xx = np.meshgrid(np.arange(Z), np.arange(Y), np.arange(X), indexing="ij")
+    psf = np.zeros((Z, Y, X), F32)
+    for loc in locations:
+        v = _sample_linear(img, xx - X // 2 + float(loc[0]), yy - Y // 2 + float(loc[1]), zz - Z // 2 + float(loc[2]), "periodic")
+        psf = (psf + v.astype(F32)).astype(F32)
+    return psf
+
+
+def normalize_psf(psf):
+    """ExtractPSF.normalize (:277-295)."""
+    a = psf.astype(np.float64)
+    return ((a - a.min()) / (a.max() - a.min())).astype(F32)
+
+
+def transformed_psf_geometry(dim_xyz, model):
+    """ExtractPSF.transformPSF (:304-346): (new size, offset) from the bounds of the transformed interval."""
+    m = np.asarray(model, dtype=np.float64).reshape(3, 4)
+    corners = np.array([[(c >> d & 1) * (dim_xyz[d] - 1.0) for d in range(3)] for c in range(8)])
+    t = corners @ m[:, :3].T + m[:, 3]
+    size = t.max(axis=0) - t.min(axis=0)
+    new = [int(s) + 1 for s in size]
+    new = [n + 1 if n % 2 == 0 else n for n in new]
+    centre = np.array([float(d // 2) for d in dim_xyz])
+    tc = m[:, :3] @ centre + m[:, 3]
+    return new, [tc[d] - (new[d] // 2) for d in range(3)]
+
+
+def transform_psf(psf, model):
+    """ExtractPSF.transformPSF + transform (:396-437): resample through the view's model, zero outside."""
+    m = np.eye(4)
+    m[:3, :4] = np.asarray(model, dtype=np.float64).reshape(3, 4)
+    inv = np.linalg.inv(m)
+    new, off = transformed_psf_geometry(psf.shape[::-1], model)
+    zz, yy, xx = np.meshgrid(np.arange(new[2]), np.arange(new[1]), np.arange(new[0]), indexing="ij")
+    t = [xx + off[0], yy + off[1], zz + off[2]]
+    p = [inv[d, 0] * t[0] + inv[d, 1] * t[1] + inv[d, 2] * t[2] + inv[d, 3] for d in range(3)]
+    return _sample_linear(psf, p[0], p[1], p[2], "zero").astype(F32)
+
+
+def average_transformed_psf(psfs):
+    """ExtractPSF.computeAverageTransformedPSF (:173-215): the PSFs are *added* point-mirrored about their centres
+    into an image of the maximal size (loc = psfCentre - loc + avgCentre), zero outside."""
+    size = [max(p.shape[2 - d] for p in psfs) for d in range(3)]  # x, y, z
+    avg = np.zeros(size[::-1], F32)
+    ac = [s // 2 for s in size]
+    for p in psfs:
+        pz, py, px = p.shape
+        pc = (px // 2, py // 2, pz // 2)
+        for z in range(pz):
+            for y in range(py):
+                for x in range(px):
+                    lx, ly, lz = pc[0] - x + ac[0], pc[1] - y + ac[1], pc[2] - z + ac[2]
+                    if 0 <= lx < size[0] and 0 <= ly < size[1] and 0 <= lz < size[2]:
+                        avg[lz, ly, lx] += p[z, y, x]
+    return avg
+
+
 def _conv_zero_same(inp, kernel):
     # new FFTConvolution(Views.extendZero(input), input, Views.extendZero(kernel), kernel, output)
     return convolve_extended(inp, kernel, "zero")

@@ -897,6 +897,115 @@ extern "C" int mvdNormalizeWeights(int device, float* const* weights, int numVie
     });
 }
 
+// ---- PSF extraction (ExtractPSF.java) --------------------------------------------------------------
+static void invert_affine(const double m[12], double inv[12]) {
+    // AffineTransform3D.inverse(): adjugate of the 3x3 part over its determinant, translation -R^-1 t
+    const double a = m[0], b = m[1], c = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+    const double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+    require(det != 0.0 && std::isfinite(det), "singular affine transformation");
+    const double r[9] = {(e * i - f * h) / det, (c * h - b * i) / det, (b * f - c * e) / det,
+                         (f * g - d * i) / det, (a * i - c * g) / det, (c * d - a * f) / det,
+                         (d * h - e * g) / det, (b * g - a * h) / det, (a * e - b * d) / det};
+    for (int row = 0; row < 3; ++row) {
+        for (int col = 0; col < 3; ++col) inv[4 * row + col] = r[3 * row + col];
+        inv[4 * row + 3] = -(r[3 * row] * m[3] + r[3 * row + 1] * m[7] + r[3 * row + 2] * m[11]);
+    }
+}
+
+// ExtractPSF.transformPSF (:304-346): odd size from the bounds of the transformed interval [0, dim-1],
+// offset such that the transformed centre voxel (dim / 2) is the centre of the result
+static void transformed_psf_geometry(const int dim[3], const double model[12], int new_dim[3], double offset[3]) {
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (int corner = 0; corner < 8; ++corner) {
+        const double p[3] = {(corner & 1) ? dim[0] - 1.0 : 0.0, (corner & 2) ? dim[1] - 1.0 : 0.0, (corner & 4) ? dim[2] - 1.0 : 0.0};
+        for (int d = 0; d < 3; ++d) {
+            const double v = model[4 * d] * p[0] + model[4 * d + 1] * p[1] + model[4 * d + 2] * p[2] + model[4 * d + 3];
+            lo[d] = std::min(lo[d], v);
+            hi[d] = std::max(hi[d], v);
+        }
+    }
+    const double centre[3] = {(double)(dim[0] / 2), (double)(dim[1] / 2), (double)(dim[2] / 2)};
+    for (int d = 0; d < 3; ++d) {
+        new_dim[d] = (int)(hi[d] - lo[d]) + 1;
+        if (new_dim[d] % 2 == 0) ++new_dim[d];
+        const double t = model[4 * d] * centre[0] + model[4 * d + 1] * centre[1] + model[4 * d + 2] * centre[2] + model[4 * d + 3];
+        offset[d] = t - (double)(new_dim[d] / 2);
+    }
+}
+
+extern "C" int mvdExtractPSF(int device, const float* img, const int imgDim[3], const double* locations, int numLocations,
+                             const int psfSize[3], int normalize, float* psf, int imgMemKind) {
+    return guarded([&] {
+        require(img && imgDim && psfSize && psf && (locations || numLocations == 0) && numLocations >= 0, "mvdExtractPSF: bad argument");
+        use_device(device);
+        PsfArgs a;
+        std::memset(&a, 0, sizeof(a));
+        for (int d = 0; d < 3; ++d) {
+            require(imgDim[d] > 0 && psfSize[d] > 0, "mvdExtractPSF: empty image or PSF");
+            a.dim[d] = imgDim[d];
+            a.size[d] = psfSize[d];
+        }
+        const size_t ni = (size_t)imgDim[0] * imgDim[1] * imgDim[2], np = (size_t)psfSize[0] * psfSize[1] * psfSize[2];
+        require(np < (1u << 30), "mvdExtractPSF: PSF too large");
+        StreamGuard sg;
+        DevBuf dimg, dloc, dpsf;
+        const float* s = img;
+        if (imgMemKind != MVD_MEM_DEVICE) {
+            dimg.alloc(ni * sizeof(float));
+            MVD_CUDA(cudaMemcpyAsync(dimg.p, img, ni * sizeof(float), cudaMemcpyHostToDevice, sg.st));
+            s = static_cast<const float*>(dimg.p);
+        }
+        dloc.alloc(std::max<size_t>(1, (size_t)numLocations * 3) * sizeof(double));
+        if (numLocations) MVD_CUDA(cudaMemcpyAsync(dloc.p, locations, (size_t)numLocations * 3 * sizeof(double), cudaMemcpyHostToDevice, sg.st));
+        dpsf.alloc(np * sizeof(float));
+        MVD_CUDA(launch_extract_psf(s, a, static_cast<const double*>(dloc.p), numLocations, static_cast<float*>(dpsf.p), sg.st));
+        ++g_kernel_launches;
+        MVD_CUDA(cudaMemcpyAsync(psf, dpsf.p, np * sizeof(float), cudaMemcpyDeviceToHost, sg.st));
+        MVD_CUDA(cudaStreamSynchronize(sg.st));
+        if (normalize) {  // ExtractPSF.normalize (:277-295): (v - min) / (max - min) in double
+            double mn = std::numeric_limits<double>::max(), mx = -std::numeric_limits<double>::max();
+            for (size_t i = 0; i < np; ++i) { mn = std::min(mn, (double)psf[i]); mx = std::max(mx, (double)psf[i]); }
+            for (size_t i = 0; i < np; ++i) psf[i] = (float)(((double)psf[i] - mn) / (mx - mn));
+        }
+    });
+}
+
+extern "C" int mvdTransformedPSFSize(const int psfDim[3], const double model[12], int newDim[3]) {
+    return guarded([&] {
+        require(psfDim && model && newDim && psfDim[0] > 0 && psfDim[1] > 0 && psfDim[2] > 0, "mvdTransformedPSFSize: bad argument");
+        double offset[3];
+        transformed_psf_geometry(psfDim, model, newDim, offset);
+    });
+}
+
+extern "C" int mvdTransformPSF(int device, const float* psf, const int psfDim[3], const double model[12], const int newDim[3], float* out) {
+    return guarded([&] {
+        require(psf && psfDim && model && newDim && out, "mvdTransformPSF: null argument");
+        use_device(device);
+        PsfArgs a;
+        std::memset(&a, 0, sizeof(a));
+        int want[3];
+        transformed_psf_geometry(psfDim, model, want, a.offset);
+        for (int d = 0; d < 3; ++d) {
+            require(psfDim[d] > 0 && newDim[d] == want[d], "mvdTransformPSF: newDim must come from mvdTransformedPSFSize");
+            a.dim[d] = psfDim[d];
+            a.size[d] = newDim[d];
+        }
+        invert_affine(model, a.inv);
+        const size_t ns = (size_t)psfDim[0] * psfDim[1] * psfDim[2], no = (size_t)newDim[0] * newDim[1] * newDim[2];
+        require(no < (1u << 30), "mvdTransformPSF: result too large");
+        StreamGuard sg;
+        DevBuf dsrc, dout;
+        dsrc.alloc(ns * sizeof(float));
+        dout.alloc(no * sizeof(float));
+        MVD_CUDA(cudaMemcpyAsync(dsrc.p, psf, ns * sizeof(float), cudaMemcpyHostToDevice, sg.st));
+        MVD_CUDA(launch_transform_psf(static_cast<const float*>(dsrc.p), a, static_cast<float*>(dout.p), sg.st));
+        ++g_kernel_launches;
+        MVD_CUDA(cudaMemcpyAsync(out, dout.p, no * sizeof(float), cudaMemcpyDeviceToHost, sg.st));
+        MVD_CUDA(cudaStreamSynchronize(sg.st));
+    });
+}
+
 // ---- stand-alone convolution ---------------------------------------------------------------
 // dims in (x,y,z); src/out host pointers.
 static void convolve_device(Device& dev, const float* d_src, const int dim[3], const float* kernel, const int k[3], int ext,

@@ -87,8 +87,11 @@ template <int BX, int BY> struct XYCfg {
 };
 
 // ---------------------------------------------------------------------------------------------
+#ifndef MVD_FWD_MINCTAS
+#define MVD_FWD_MINCTAS 3
+#endif
 template <int BX, int BY>
-__global__ void __launch_bounds__(NT, XYCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Volume src, const Tile* __restrict__ tiles,
+__global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_FWD_MINCTAS ? XYCfg<BX, BY>::MIN_CTAS : MVD_FWD_MINCTAS)) fwd_xy_kernel(Volume src, const Tile* __restrict__ tiles,
                                                                            float2* __restrict__ scratch, size_t tile_stride, int bz,
                                                                            int n_items, Twiddles tw) {
     using C = XYCfg<BX, BY>;

@@ -139,6 +139,74 @@ __global__ void __launch_bounds__(256) osem_kernel(float* __restrict__ w, size_t
     }
 }
 
+// ---- PSF extraction (ExtractPSF.java) -------------------------------------------------------------
+// n-linear sample of `img` at a double position; mode 0: zero outside (Views.extendZero), 1: periodic
+__device__ __forceinline__ double sample_linear(const float* __restrict__ img, const int dim[3], double px, double py, double pz, int mode) {
+    const double p[3] = {px, py, pz};
+    int i0[3], i1[3];
+    double w[3];
+    bool in0[3], in1[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const double f = floor(p[d]);
+        w[d] = p[d] - f;
+        const long long a = (long long)f, b = a + 1;
+        if (mode == 1) {
+            long long ma = a % dim[d], mb = b % dim[d];
+            if (ma < 0) ma += dim[d];
+            if (mb < 0) mb += dim[d];
+            i0[d] = (int)ma; i1[d] = (int)mb;
+            in0[d] = in1[d] = true;
+        } else {
+            in0[d] = a >= 0 && a < dim[d];
+            in1[d] = b >= 0 && b < dim[d];
+            i0[d] = in0[d] ? (int)a : 0;
+            i1[d] = in1[d] ? (int)b : 0;
+        }
+    }
+    const size_t sx = dim[0], sxy = (size_t)dim[0] * dim[1];
+    auto at = [&](bool okx, int xx, bool oky, int yy, bool okz, int zz) {
+        return (okx && oky && okz) ? (double)__ldg(img + xx + sx * yy + sxy * zz) : 0.0;
+    };
+    const double c00 = at(in0[0], i0[0], in0[1], i0[1], in0[2], i0[2]) * (1.0 - w[0]) + at(in1[0], i1[0], in0[1], i0[1], in0[2], i0[2]) * w[0];
+    const double c10 = at(in0[0], i0[0], in1[1], i1[1], in0[2], i0[2]) * (1.0 - w[0]) + at(in1[0], i1[0], in1[1], i1[1], in0[2], i0[2]) * w[0];
+    const double c01 = at(in0[0], i0[0], in0[1], i0[1], in1[2], i1[2]) * (1.0 - w[0]) + at(in1[0], i1[0], in0[1], i0[1], in1[2], i1[2]) * w[0];
+    const double c11 = at(in0[0], i0[0], in1[1], i1[1], in1[2], i1[2]) * (1.0 - w[0]) + at(in1[0], i1[0], in1[1], i1[1], in1[2], i1[2]) * w[0];
+    const double c0 = c00 * (1.0 - w[1]) + c10 * w[1];
+    const double c1 = c01 * (1.0 - w[1]) + c11 * w[1];
+    return c0 * (1.0 - w[2]) + c1 * w[2];
+}
+
+// ExtractPSF.extractPSFLocal (:353-394): psf(v) = sum over the bead locations of the view sampled at
+// v - size/2 + location (periodic extension), accumulated in float in the order of the locations
+__global__ void __launch_bounds__(128) extract_psf_kernel(const float* __restrict__ img, PsfArgs a, const double* __restrict__ loc, int n_loc,
+                                                          float* __restrict__ psf) {
+    const int n = a.size[0] * a.size[1] * a.size[2];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int x = i % a.size[0], y = (i / a.size[0]) % a.size[1], z = i / (a.size[0] * a.size[1]);
+    float acc = 0.f;
+    for (int l = 0; l < n_loc; ++l) {
+        const double px = (double)(x - a.size[0] / 2) + loc[3 * l], py = (double)(y - a.size[1] / 2) + loc[3 * l + 1],
+                     pz = (double)(z - a.size[2] / 2) + loc[3 * l + 2];
+        acc = __fadd_rn(acc, (float)sample_linear(img, a.dim, px, py, pz, 1));
+    }
+    psf[i] = acc;
+}
+
+// ExtractPSF.transform (:396-437): out(v) = psf sampled (zero outside) at inverse(v + offset)
+__global__ void __launch_bounds__(128) transform_psf_kernel(const float* __restrict__ psf, PsfArgs a, float* __restrict__ out) {
+    const int n = a.size[0] * a.size[1] * a.size[2];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int x = i % a.size[0], y = (i / a.size[0]) % a.size[1], z = i / (a.size[0] * a.size[1]);
+    const double t0 = (double)x + a.offset[0], t1 = (double)y + a.offset[1], t2 = (double)z + a.offset[2];
+    double p[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) p[d] = a.inv[4 * d] * t0 + a.inv[4 * d + 1] * t1 + a.inv[4 * d + 2] * t2 + a.inv[4 * d + 3];
+    out[i] = (float)sample_linear(psf, a.dim, p[0], p[1], p[2], 0);
+}
+
 int grid_for(size_t n) {
     const size_t want = (n + 255) / 256;
     return (int)(want < (size_t)(148 * 16) ? (want ? want : 1) : (size_t)(148 * 16));
@@ -170,6 +238,20 @@ cudaError_t launch_transform_view(const float* src, const TransformArgs& a, floa
 cudaError_t launch_normalize_weights(const WeightPtrs& w, size_t n, unsigned long long* d_count, int* d_min, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     normalize_weights_kernel<<<grid_for(n), 256, 0, st>>>(w, n, d_count, d_min);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_extract_psf(const float* img, const PsfArgs& a, const double* d_loc, int n_loc, float* d_psf, cudaStream_t st) {
+    const int n = a.size[0] * a.size[1] * a.size[2];
+    if (n <= 0) return cudaSuccess;
+    extract_psf_kernel<<<(n + 127) / 128, 128, 0, st>>>(img, a, d_loc, n_loc, d_psf);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_transform_psf(const float* d_psf, const PsfArgs& a, float* d_out, cudaStream_t st) {
+    const int n = a.size[0] * a.size[1] * a.size[2];
+    if (n <= 0) return cudaSuccess;
+    transform_psf_kernel<<<(n + 127) / 128, 128, 0, st>>>(d_psf, a, d_out);
     return cudaGetLastError();
 }
 

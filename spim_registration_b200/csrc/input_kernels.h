@@ -21,7 +21,16 @@ struct WeightPtrs {
     int n;
 };
 
+struct PsfArgs {
+    int dim[3];        // source image (extraction) or source PSF (transformation)
+    int size[3];       // extracted / transformed PSF
+    double inv[12];    // transformation: row-major 3x4 inverse of the view's model
+    double offset[3];  // transformation: position of output voxel 0 in transformed coordinates
+};
+
 cudaError_t upload_blend_table();
+cudaError_t launch_extract_psf(const float* img, const PsfArgs& a, const double* d_loc, int n_loc, float* d_psf, cudaStream_t st);
+cudaError_t launch_transform_psf(const float* d_psf, const PsfArgs& a, float* d_out, cudaStream_t st);
 cudaError_t launch_transform_view(const float* src, const TransformArgs& a, float* out_img, float* out_w, cudaStream_t st);
 cudaError_t launch_normalize_weights(const WeightPtrs& w, size_t n, unsigned long long* d_count, int* d_min, cudaStream_t st);
 cudaError_t launch_osem(float* w, size_t n, float speedup, cudaStream_t st);

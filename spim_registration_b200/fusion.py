@@ -63,3 +63,66 @@ class WeightNormalizer:
 
     def getAvgOverlappingViews(self):
         return self.avgOverlappingViews
+
+
+class ExtractPSF:
+    """ExtractPSF.java: extraction of a view's PSF from bead locations and its transformation into the
+    fused coordinate system; the sampling runs in libmvdecon.so (csrc/input_kernels.cu)."""
+
+    def __init__(self, device=0):
+        self.device = device
+        self.pointSpreadFunctions, self.originalPSFs = [], []
+
+    @staticmethod
+    def _model(model):
+        return np.ascontiguousarray(np.asarray(model, dtype=np.float64)[:3, :4])
+
+    def extractPSFLocal(self, img, locations, size, normalize=False):
+        """:353-394 (+ normalize, :277-295).  img [z,y,x]; locations [[x,y,z], ...]; size (x,y,z)."""
+        lib = _lib.load()
+        img = np.ascontiguousarray(img, dtype=F32)
+        loc = np.ascontiguousarray(np.asarray(locations, dtype=np.float64).reshape(-1, 3))
+        psf = np.empty(tuple(size[::-1]), F32)
+        _lib.check(lib.mvdExtractPSF(int(self.device), img.ctypes.data_as(C.c_void_p), _lib.int3(img.shape[::-1]),
+                                     loc.ctypes.data_as(_lib.c_double_p), len(loc), _lib.int3(size), int(bool(normalize)),
+                                     psf.ctypes.data_as(_lib.c_float_p), 0), "mvdExtractPSF")
+        return psf
+
+    def transformPSF(self, psf, model):
+        """:304-346.  model: the view's registration (view -> world), 3x4 or 4x4."""
+        lib = _lib.load()
+        psf = np.ascontiguousarray(psf, dtype=F32)
+        m = self._model(model)
+        new = (C.c_int * 3)()
+        _lib.check(lib.mvdTransformedPSFSize(_lib.int3(psf.shape[::-1]), m.ctypes.data_as(_lib.c_double_p), new), "mvdTransformedPSFSize")
+        out = np.empty((new[2], new[1], new[0]), F32)
+        _lib.check(lib.mvdTransformPSF(int(self.device), psf.ctypes.data_as(_lib.c_float_p), _lib.int3(psf.shape[::-1]),
+                                       m.ctypes.data_as(_lib.c_double_p), new, out.ctypes.data_as(_lib.c_float_p)), "mvdTransformPSF")
+        return out
+
+    def extractNextImg(self, img, model, locations, psfSize):
+        """:256-275: extract, normalise, transform; keeps both PSFs."""
+        original = self.extractPSFLocal(img, locations, psfSize, normalize=True)
+        psf = self.transformPSF(original, model)
+        self.originalPSFs.append(original)
+        self.pointSpreadFunctions.append(psf)
+        return psf
+
+    def computeAverageTransformedPSF(self):
+        """:173-215 (host arithmetic: a few thousand additions): the PSFs added point-mirrored about their centres."""
+        psfs = self.pointSpreadFunctions
+        size = [max(p.shape[2 - d] for p in psfs) for d in range(3)]
+        avg = np.zeros(size[::-1], F32)
+        ac = [s // 2 for s in size]
+        for p in psfs:
+            pz, py, px = p.shape
+            flipped = p[::-1, ::-1, ::-1]  # loc = centre - loc + avgCentre
+            # index of the flipped image's voxel 0: centre - (n - 1) + avgCentre
+            o = [px // 2 - (px - 1) + ac[0], py // 2 - (py - 1) + ac[1], pz // 2 - (pz - 1) + ac[2]]
+            sl_a, sl_p = [], []
+            for d, n in zip(range(3), (px, py, pz)):
+                lo, hi = max(0, o[d]), min(size[d], o[d] + n)
+                sl_a.append(slice(lo, hi))
+                sl_p.append(slice(lo - o[d], hi - o[d]))
+            avg[sl_a[2], sl_a[1], sl_a[0]] += flipped[sl_p[2], sl_p[1], sl_p[0]]
+        return avg

@@ -466,3 +466,26 @@ def test_view_without_any_data_and_never_updated_voxels(m, o):
     dec = m.MVDeconvolution(_views(m, imgs, [1 / 3] * 3, psfs), "EFFICIENT_BAYESIAN", 3, 0.006)
     assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
     assert (dec.getPsi()[:, :, 30:] == 0).all() and (dec.getPsi()[:, :, :30] > 0).all()
+
+
+# ---- PSF extraction on the device ------------------------------------------------
+def test_extract_and_transform_psf_match_oracle(m, o):
+    rng = np.random.default_rng(41)
+    img = rng.random((40, 60, 70), dtype=np.float32)
+    locs = np.column_stack([rng.uniform(0, 70, 25), rng.uniform(0, 60, 25), rng.uniform(0, 40, 25)])
+    locs[0] = (0.25, 59.5, 39.75)                                    # windows that wrap around (periodic extension)
+    e = m.ExtractPSF()
+    size = (19, 17, 11)
+    got = e.extractPSFLocal(img, locs, size)
+    ref = o.extract_psf_local(img, locs, size)
+    np.testing.assert_allclose(got, ref, rtol=0, atol=4e-6)         # 25 float additions of values < 1
+    gotn = e.extractPSFLocal(img, locs, size, normalize=True)
+    np.testing.assert_allclose(gotn, o.normalize_psf(ref), rtol=0, atol=2e-6)
+    for angle, sz in ((0.0, 1.0), (30.0, 2.5), (90.0, 3.0)):
+        model = _registration(angle, sz, (12.0, -3.0, 7.5))
+        t = e.transformPSF(gotn, model)
+        rt = o.transform_psf(gotn, model[:3, :4])
+        assert t.shape == rt.shape and all(s % 2 == 1 for s in t.shape)
+        np.testing.assert_allclose(t, rt, rtol=0, atol=2e-7)
+    psf = e.extractNextImg(img, _registration(45.0, 2.0, (0, 0, 0)), locs, size)
+    assert psf.shape == e.pointSpreadFunctions[0].shape and len(e.originalPSFs) == 1

@@ -318,3 +318,52 @@ def test_weight_normalisation_and_osem():
     a = o.adjust_for_osem(n[1], 2.0)
     np.testing.assert_allclose(a[:3], [1.0, 1.0, 1.0])
     assert np.isnan(a[3]) and o.adjust_for_osem(n[1], 1.0) is n[1]
+
+
+# ---- PSF extraction (ExtractPSF.java) -------------------------------------------
+def test_extract_psf_known_answers():
+    rng = np.random.default_rng(31)
+    img = rng.random((12, 14, 16), dtype=np.float32)
+    # one bead at an integer position: the PSF is the window around it (periodic wrap at the border)
+    psf = o.extract_psf_local(img, [(8, 7, 6)], (5, 5, 3))
+    np.testing.assert_array_equal(psf, img[5:8, 5:10, 6:11])
+    wrap = o.extract_psf_local(img, [(0, 0, 0)], (3, 3, 3))
+    np.testing.assert_array_equal(wrap, np.roll(img, (1, 1, 1), (0, 1, 2))[:3, :3, :3])
+    # two beads add; half-voxel positions average neighbours
+    two = o.extract_psf_local(img, [(8, 7, 6), (4, 5, 6)], (5, 5, 3))
+    np.testing.assert_allclose(two, img[5:8, 5:10, 6:11] + img[5:8, 3:8, 2:7], rtol=1e-6)
+    half = o.extract_psf_local(img, [(8.5, 7, 6)], (5, 5, 3))
+    np.testing.assert_allclose(half, (img[5:8, 5:10, 6:11].astype(np.float64) + img[5:8, 5:10, 7:12]) / 2, rtol=1e-6)
+    n = o.normalize_psf(psf)
+    assert n.min() == 0 and n.max() == 1
+
+
+def test_transform_psf_geometry_and_identity():
+    psf = np.random.default_rng(32).random((7, 9, 11), dtype=np.float32)
+    ident = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, 0]], float)
+    size, off = o.transformed_psf_geometry((11, 9, 7), ident)
+    assert size == [11, 9, 7] and off == [0.0, 0.0, 0.0]
+    np.testing.assert_array_equal(o.transform_psf(psf, ident), psf)
+    # z scaling 2.5 (anisotropic stack): z extent (7-1)*2.5 = 15 -> 16 -> odd 17; the centre voxel stays the centre
+    scale = np.diag([1.0, 1.0, 2.5, 1.0])[:3]
+    size, off = o.transformed_psf_geometry((11, 9, 7), scale)
+    assert size == [11, 9, 17] and off[2] == 3 * 2.5 - 8
+    t = o.transform_psf(psf, scale)
+    assert t.shape == (17, 9, 11)
+    np.testing.assert_allclose(t[8], psf[3], rtol=1e-6)  # centre plane is reproduced
+    even = np.random.default_rng(33).random((6, 6, 6), dtype=np.float32)
+    assert o.transform_psf(even, ident).shape == (7, 7, 7)  # even sizes become odd ("works if the kernel is even")
+
+
+def test_average_transformed_psf_mirrors_about_the_centre():
+    a = np.zeros((3, 3, 5), np.float32)
+    a[1, 1, 4] = 1.0                                   # one voxel right of the centre (x = 2) by 2
+    b = np.zeros((5, 3, 3), np.float32)
+    b[0, 1, 1] = 2.0
+    avg = o.average_transformed_psf([a, b])
+    assert avg.shape == (5, 3, 5)
+    assert avg[2, 1, 0] == 1.0 and avg[4, 1, 2] == 2.0 and avg.sum() == 3.0   # point-mirrored: centre - loc + avgCentre
+    import spim_registration_b200 as m
+    e = m.ExtractPSF()
+    e.pointSpreadFunctions = [a, b]
+    np.testing.assert_array_equal(e.computeAverageTransformedPSF(), avg)
