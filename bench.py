@@ -227,10 +227,12 @@ def run_ours(args, cfg):
         sampler.start()
     launches0 = dec.kernel_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.profiler.start()  # `ncu --profile-from-start off` captures exactly the timed steps
     e0.record()
     dec.run_iterations(args.steps)
     e1.record()
     barrier()
+    torch.cuda.profiler.stop()
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -330,8 +332,8 @@ def run_ours(args, cfg):
         "roofline": {"bound": "hbm", "kernel": names[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "achieved_bytes_per_launch": pb[top] / pl[top] if pl[top] else None, "peak_source": peak_src,
-                     "share_of_step": pms[top] / sum(pms), "kernels": kern,
-                     "timing": "CUDA events around every launch, %d serial step(s) after the timed region: kernels %.1f ms/step, wall %.1f ms/step with the event calls; timed region %.1f ms/step (MVD_LANES=%s); share_of_step = kernel / sum of the three kernels"
+                     "share_of_step": (pms[top] / prof_steps) / (ms / args.steps), "kernels": kern,
+                     "timing": "CUDA events around every launch, %d serial step(s) after the timed region: kernels %.1f ms/step, wall %.1f ms/step with the event calls; timed region %.1f ms/step (MVD_LANES=%s); share_of_step = kernel ms per step / timed ms per step (views on the direct separable path are not in `kernels`)"
                                % (prof_steps, sum(pms) / prof_steps, prof_ms / prof_steps, ms / args.steps, os.environ.get("MVD_LANES", "4")),
                      "loop": {"alg_bytes_per_voxel_view_iteration": ALG_BYTES_PER_VOXEL_VIEW[cfg["dense_weights"]],
                               "achieved": loop_bytes / 1e9 / (ms * 1e-3), "frac": loop_bytes / 1e9 / (ms * 1e-3) / peak,

@@ -29,7 +29,7 @@ namespace mvd {
 
 static constexpr int NT = 256;  // threads per CTA of the xy kernels
 #ifndef MVD_XY_ZPC
-#define MVD_XY_ZPC 2
+#define MVD_XY_ZPC 4  // planes per work item of the xy kernels (measured: 1 -> 32.1, 2 -> 31.9, 4 -> 31.5 ms per iteration)
 #endif
 #ifndef MVD_PREFETCH
 #define MVD_PREFETCH 0
