@@ -212,6 +212,28 @@ int mvdTransformView(int device, const float* src, const int srcDim[3], const do
 int mvdNormalizeWeights(int device, float* const* weights, int numViews, long long numVoxels, double osemSpeedup,
                         int* minOverlappingViews, double* avgOverlappingViews, int memKind);
 
+/* Virtual weights -- the dialog's default weight type (EfficientBayesianBased.java:71,84;
+ * ProcessForDeconvolution.java:204-208, 308-309, 375-379).  The reference keeps no weight images: every
+ * read of w_v(x) inside the loop evaluates
+ *     min(1, blend_v(A_v^-1 (x + outOffset)) / sumW(x) * osemSpeedup)        NormalizingRandomAccess.java:36-45
+ * with the position from TransformedInterpolatedRealRandomAccess.applyInverse (:68-95) and the float image
+ *     sumW(x) = sum_u blend_u(...) where that exceeds 1, else 1              WeightNormalizer.java:183-232
+ * With 180 GB of HBM the same values are evaluated once and stay resident (pass them to mvdAddView as dense
+ * weights): identical results, no affine transform and lookup per voxel, view and iteration.
+ *   mvdVirtualWeightSum  sumW and the overlap statistics (WeightNormalizer.java:74-88) for numViews views:
+ *                        srcDims 3 ints, inverses 12 doubles (row-major 3x4, world -> view), blendBorders /
+ *                        blendRanges 3 floats per view.  avgOverlappingViews is the mean over all voxels (the
+ *                        reference averages the means of 2 x numThreads equal portions).
+ *   mvdVirtualWeight     one view's weight image from sumW and the OSEM speed-up
+ *                        (NormalizingRandomAccessibleInterval.setOSEMspeedup, ProcessForDeconvolution.java:375-379).
+ * sumWeights / outWeight: host or device arrays of outDim voxels (x fastest) according to memKind. */
+int mvdVirtualWeightSum(int device, int numViews, const int* srcDims, const double* inverses, const float* blendBorders,
+                        const float* blendRanges, const int outOffset[3], const int outDim[3], float* sumWeights,
+                        int* minOverlappingViews, double* avgOverlappingViews, int memKind);
+int mvdVirtualWeight(int device, const int srcDim[3], const double inverse[12], const float blendBorder[3], const float blendRange[3],
+                     const int outOffset[3], const int outDim[3], const float* sumWeights, double osemSpeedup, float* outWeight,
+                     int memKind);
+
 /* PSF extraction (ExtractPSF.java).
  * mvdExtractPSF = extractPSFLocal (:353-394): psf(v) = sum over the bead locations (x,y,z triples, view
  *   coordinates) of the view sampled n-linearly with periodic extension at v - psfSize/2 + location, float

@@ -322,6 +322,43 @@ def adjust_for_osem(w, osemspeedup):
     return np.where(np.isnan(v), v, np.minimum(F32(1), v)).astype(F32)
 
 
+# ---- virtual weights (the dialog's default weight type) ------------------------------------------
+def virtual_blending(inverse, offset_xyz, out_dim_xyz, src_dim_xyz, border, blending):
+    """The view's blending function seen through TransformedRealRandomAccessibleInterval
+    (ProcessForDeconvolution.java:204-208): TransformedInterpolatedRealRandomAccess.applyInverse (:68-95)
+    maps the integer world coordinate (voxel + offset, as double) through the inverse registration,
+    t0*i00 + t1*i01 + t2*i02 + i03 evaluated left to right in double and stored as float; the float
+    position is handed to BlendingRealRandomAccess.computeWeight (:71-101).  Returns float32 [z,y,x]."""
+    inv = np.asarray(inverse, dtype=np.float64).reshape(3, 4)
+    X, Y, Z = out_dim_xyz
+    zz, yy, xx = np.meshgrid(np.arange(Z), np.arange(Y), np.arange(X), indexing="ij")
+    t0 = (xx + int(offset_xyz[0])).astype(np.float64)
+    t1 = (yy + int(offset_xyz[1])).astype(np.float64)
+    t2 = (zz + int(offset_xyz[2])).astype(np.float64)
+    t = np.stack([(((t0 * inv[d, 0] + t1 * inv[d, 1]) + t2 * inv[d, 2]) + inv[d, 3]).astype(F32) for d in range(3)], axis=-1)
+    return blending_weight(t, src_dim_xyz, border, blending)
+
+
+def compute_sum_image(weights):
+    """WeightNormalizer.ComputeSumImage (WeightNormalizer.java:183-232): per voxel the double sum of the
+    views' float weights, stored as float where it exceeds 1 and as 1 elsewhere; returns
+    (sumWeights, min overlapping views, average overlapping views (global mean))."""
+    stack = np.stack([np.asarray(w, dtype=F32) for w in weights])
+    s = np.zeros(stack.shape[1:], np.float64)
+    for w in stack:  # same order of additions as the cursor loop
+        s = s + w.astype(np.float64)
+    cnt = (stack > 0).sum(axis=0)
+    sum_w = np.where(s > 1, s.astype(F32), F32(1)).astype(F32)
+    return sum_w, int(cnt.min()), float(cnt.mean())
+
+
+def normalizing_weight(w, sum_w, osemspeedup=1.0):
+    """NormalizingRandomAccess.get (NormalizingRandomAccess.java:36-45):
+    (float) Math.min(1, (double)w / (double)sumW * osemspeedup)."""
+    v = np.asarray(w, dtype=F32).astype(np.float64) / np.asarray(sum_w, dtype=F32).astype(np.float64) * float(osemspeedup)
+    return np.where(np.isnan(v), v, np.minimum(1.0, v)).astype(F32)
+
+
 # ---- PSF extraction (ExtractPSF.java, SURVEY.md 8f row 3) -----------------------------------------
 def _sample_linear(img, px, py, pz, mode):
     """n-linear interpolation of img [z,y,x] at double positions (arrays); mode "zero" (Views.extendZero)

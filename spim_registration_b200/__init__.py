@@ -7,8 +7,8 @@ from . import _lib
 from ._lib import MVDeconError, load
 from .cuda import (Block, BlockGeneratorFixedSizePrecise, CUDADevice, CUDAFourierConvolution, CUDASeparableConvolution,
                    CUDASeparableConvolutionFunctions, CUDATools, convolve, plan_tiles)
-from .fusion import ExtractPSF, WeightNormalizer, transformInputAndWeights
+from .fusion import ExtractPSF, VirtualWeights, WeightNormalizer, transformInputAndWeights
 from .deconvolution import AdjustInput, Mirror, MVDeconFFT, MVDeconInput, MVDeconvolution, PSFTYPE
 
-__all__ = ["ExtractPSF", "WeightNormalizer", "transformInputAndWeights", "MVDeconError", "load", "Block", "BlockGeneratorFixedSizePrecise", "CUDADevice", "CUDAFourierConvolution", "CUDASeparableConvolution", "CUDASeparableConvolutionFunctions", "CUDATools",
+__all__ = ["ExtractPSF", "VirtualWeights", "WeightNormalizer", "transformInputAndWeights", "MVDeconError", "load", "Block", "BlockGeneratorFixedSizePrecise", "CUDADevice", "CUDAFourierConvolution", "CUDASeparableConvolution", "CUDASeparableConvolutionFunctions", "CUDATools",
            "convolve", "plan_tiles", "AdjustInput", "Mirror", "MVDeconFFT", "MVDeconInput", "MVDeconvolution", "PSFTYPE"]

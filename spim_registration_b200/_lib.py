@@ -54,6 +54,9 @@ PROTOTYPES = {
     "mvdTransformView": (C.c_int, [C.c_int, C.c_void_p, c_int_p, c_double_p, c_int_p, c_int_p, c_float_p, c_float_p, C.c_float, C.c_void_p,
                                    C.c_void_p, C.c_int, C.c_int]),
     "mvdNormalizeWeights": (C.c_int, [C.c_int, C.POINTER(C.c_void_p), C.c_int, C.c_longlong, C.c_double, c_int_p, c_double_p, C.c_int]),
+    "mvdVirtualWeightSum": (C.c_int, [C.c_int, C.c_int, c_int_p, c_double_p, c_float_p, c_float_p, c_int_p, c_int_p, C.c_void_p, c_int_p, c_double_p,
+                                      C.c_int]),
+    "mvdVirtualWeight": (C.c_int, [C.c_int, c_int_p, c_double_p, c_float_p, c_float_p, c_int_p, c_int_p, C.c_void_p, C.c_double, C.c_void_p, C.c_int]),
     "mvdExtractPSF": (C.c_int, [C.c_int, C.c_void_p, c_int_p, c_double_p, C.c_int, c_int_p, C.c_int, c_float_p, C.c_int]),
     "mvdTransformedPSFSize": (C.c_int, [c_int_p, c_double_p, c_int_p]),
     "mvdTransformPSF": (C.c_int, [C.c_int, c_float_p, c_int_p, c_double_p, c_int_p, c_float_p]),

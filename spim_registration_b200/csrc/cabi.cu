@@ -897,6 +897,95 @@ extern "C" int mvdNormalizeWeights(int device, float* const* weights, int numVie
     });
 }
 
+// ---- virtual weights (WeightNormalizer with a sum image + NormalizingRandomAccess) ---------------------
+static BlendView make_blend_view(const int srcDim[3], const double inverse[12], const float border[3], const float range[3]) {
+    BlendView b;
+    for (int i = 0; i < 12; ++i) b.inv[i] = inverse[i];
+    for (int d = 0; d < 3; ++d) {
+        require(srcDim[d] > 0, "virtual weights: empty view");
+        b.dim_minus1[d] = srcDim[d] - 1;
+        b.border[d] = border[d];
+        b.blending[d] = range[d];
+    }
+    return b;
+}
+static VolumeBox make_box(const int outOffset[3], const int outDim[3]) {
+    VolumeBox box;
+    for (int d = 0; d < 3; ++d) {
+        require(outDim[d] > 0, "virtual weights: empty bounding box");
+        box.offset[d] = outOffset[d];
+        box.dim[d] = outDim[d];
+    }
+    return box;
+}
+
+extern "C" int mvdVirtualWeightSum(int device, int numViews, const int* srcDims, const double* inverses, const float* blendBorders,
+                                   const float* blendRanges, const int outOffset[3], const int outDim[3], float* sumWeights,
+                                   int* minOverlappingViews, double* avgOverlappingViews, int memKind) {
+    return guarded([&] {
+        require(numViews > 0 && numViews <= kMaxViews && srcDims && inverses && blendBorders && blendRanges && outOffset && outDim && sumWeights,
+                "mvdVirtualWeightSum: bad argument");
+        use_device(device);
+        const VolumeBox box = make_box(outOffset, outDim);
+        const size_t n = (size_t)outDim[0] * outDim[1] * outDim[2];
+        std::vector<BlendView> views(numViews);
+        for (int v = 0; v < numViews; ++v) views[v] = make_blend_view(srcDims + 3 * v, inverses + 12 * v, blendBorders + 3 * v, blendRanges + 3 * v);
+        StreamGuard sg;
+        DevBuf dviews, dsum, stats;
+        dviews.alloc(views.size() * sizeof(BlendView));
+        MVD_CUDA(cudaMemcpyAsync(dviews.p, views.data(), views.size() * sizeof(BlendView), cudaMemcpyHostToDevice, sg.st));
+        float* out = sumWeights;
+        if (memKind != MVD_MEM_DEVICE) {
+            dsum.alloc(n * sizeof(float));
+            out = static_cast<float*>(dsum.p);
+        }
+        stats.alloc(16);
+        unsigned long long* d_count = static_cast<unsigned long long*>(stats.p);
+        int* d_min = reinterpret_cast<int*>(d_count + 1);
+        const unsigned long long zero = 0;
+        const int big = numViews;
+        MVD_CUDA(cudaMemcpyAsync(d_count, &zero, sizeof(zero), cudaMemcpyHostToDevice, sg.st));
+        MVD_CUDA(cudaMemcpyAsync(d_min, &big, sizeof(big), cudaMemcpyHostToDevice, sg.st));
+        MVD_CUDA(launch_virtual_weight_sum(static_cast<const BlendView*>(dviews.p), numViews, box, out, d_count, d_min, sg.st));
+        ++g_kernel_launches;
+        unsigned long long cnt = 0;
+        int mn = 0;
+        MVD_CUDA(cudaMemcpyAsync(&cnt, d_count, sizeof(cnt), cudaMemcpyDeviceToHost, sg.st));
+        MVD_CUDA(cudaMemcpyAsync(&mn, d_min, sizeof(mn), cudaMemcpyDeviceToHost, sg.st));
+        if (memKind != MVD_MEM_DEVICE) MVD_CUDA(cudaMemcpyAsync(sumWeights, out, n * sizeof(float), cudaMemcpyDeviceToHost, sg.st));
+        MVD_CUDA(cudaStreamSynchronize(sg.st));
+        if (minOverlappingViews) *minOverlappingViews = mn;
+        if (avgOverlappingViews) *avgOverlappingViews = (double)cnt / (double)n;
+    });
+}
+
+extern "C" int mvdVirtualWeight(int device, const int srcDim[3], const double inverse[12], const float blendBorder[3], const float blendRange[3],
+                                const int outOffset[3], const int outDim[3], const float* sumWeights, double osemSpeedup, float* outWeight,
+                                int memKind) {
+    return guarded([&] {
+        require(srcDim && inverse && blendBorder && blendRange && outOffset && outDim && sumWeights && outWeight, "mvdVirtualWeight: null argument");
+        use_device(device);
+        const VolumeBox box = make_box(outOffset, outDim);
+        const BlendView view = make_blend_view(srcDim, inverse, blendBorder, blendRange);
+        const size_t n = (size_t)outDim[0] * outDim[1] * outDim[2];
+        StreamGuard sg;
+        DevBuf dsum, dout;
+        const float* sw = sumWeights;
+        float* out = outWeight;
+        if (memKind != MVD_MEM_DEVICE) {
+            dsum.alloc(n * sizeof(float));
+            dout.alloc(n * sizeof(float));
+            MVD_CUDA(cudaMemcpyAsync(dsum.p, sumWeights, n * sizeof(float), cudaMemcpyHostToDevice, sg.st));
+            sw = static_cast<const float*>(dsum.p);
+            out = static_cast<float*>(dout.p);
+        }
+        MVD_CUDA(launch_virtual_weight(view, box, sw, osemSpeedup, out, sg.st));
+        ++g_kernel_launches;
+        if (memKind != MVD_MEM_DEVICE) MVD_CUDA(cudaMemcpyAsync(outWeight, out, n * sizeof(float), cudaMemcpyDeviceToHost, sg.st));
+        MVD_CUDA(cudaStreamSynchronize(sg.st));
+    });
+}
+
 // ---- PSF extraction (ExtractPSF.java) --------------------------------------------------------------
 static void invert_affine(const double m[12], double inv[12]) {
     // AffineTransform3D.inverse(): adjugate of the 3x3 part over its determinant, translation -R^-1 t

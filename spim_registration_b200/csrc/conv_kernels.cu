@@ -312,8 +312,16 @@ template <int BZ> struct ZCfg {
     static constexpr int PW = MVD_Z_PW;  // 8 (16): 64 (128) contiguous bytes per z index
     static constexpr int THREADS = PW * TZ;
     static constexpr bool ASYNC = MVD_Z_ASYNC != 0;
-    // exchange buffer | twiddles | (ASYNC) staging of the CTA's next item, EPT thread-private slots per thread
-    static constexpr size_t SMEM = (size_t)PW * BZ * sizeof(float2) * (ASYNC ? 2 : 1) + (size_t)BZ * sizeof(float2);
+#ifndef MVD_Z_PIPE
+#define MVD_Z_PIPE 0
+#endif
+    // PIPE: persistent grid, software-pipelined through registers -- the loads of the CTA's next item are
+    // issued before the current item is transformed (and land in a second register set), the kernel
+    // spectrum of the current item is staged in thread-private shared-memory slots by cp.async while the
+    // forward transform runs.  Needs 2 x EPT float2 registers per thread: fewer, fatter CTAs.
+    static constexpr bool PIPE = MVD_Z_PIPE != 0 && !ASYNC && BZ >= MVD_Z_PIPE;
+    // exchange buffer | twiddles | (ASYNC, PIPE) staging, EPT thread-private slots per thread
+    static constexpr size_t SMEM = (size_t)PW * BZ * sizeof(float2) * (ASYNC || PIPE ? 2 : 1) + (size_t)BZ * sizeof(float2);
 #ifndef MVD_Z_MINCTAS512
 #define MVD_Z_MINCTAS512 (MVD_Z_ASYNC ? 768 / THREADS : 1024 / THREADS)
 #endif
@@ -369,6 +377,21 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
         }
     };
     if constexpr (C::ASYNC) prefetch_item(blockIdx.x);
+    constexpr bool PIPE = C::PIPE && MODE == 1;
+    float2 nxt[PIPE ? EPT : 1];
+    auto load_item = [&](int it, float2 (&dst)[PIPE ? EPT : 1]) {
+        if constexpr (PIPE) {
+            if (it < n_items) {
+                bool nv;
+                int nti;
+                const float2* nb = item_base(it, nv, nti);
+                const unsigned pl = (unsigned)opaque(plane_elems);
+#pragma unroll
+                for (int m = 0; m < EPT; ++m) dst[m] = nb[(unsigned)(t + m * TZ) * pl];
+            }
+        }
+    };
+    load_item(blockIdx.x, nxt);
 
 #pragma unroll 1
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
@@ -381,7 +404,20 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
     // loads, the spectrum reads and the stores use the same EPT addresses, and common-subexpression
     // elimination would otherwise keep all of them (2 registers each) alive across both transforms.
     float2 v[EPT];
-    if constexpr (C::ASYNC) {
+    int zlo_p = 0, zhi_p = 0;  // PIPE: planes to write back, requested before the transforms
+    if constexpr (PIPE) {
+        zlo_p = __ldg(&tiles[ti].e[2]) - __ldg(&tiles[ti].o[2]);
+        zhi_p = zlo_p + __ldg(&tiles[ti].n[2]);
+#pragma unroll
+        for (int m = 0; m < EPT; ++m) v[m] = nxt[m];
+        {   // this item's part of the kernel spectrum (L2) -> thread-private staging slots
+            const float2* kbp = kspec + (valid ? pos : 0);
+            const unsigned pl = (unsigned)opaque(plane_elems);
+#pragma unroll
+            for (int m = 0; m < EPT; ++m) cp_async8(stage + m * NTH, kbp + (unsigned)(t + m * TZ) * pl);
+        }
+        load_item(item + gridDim.x, nxt);
+    } else if constexpr (C::ASYNC) {
         cp_async_wait_all();
 #pragma unroll
         for (int m = 0; m < EPT; ++m) v[m] = stage[m * NTH];
@@ -418,6 +454,11 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
 #endif
         constexpr int KB_ = BZ >= 512 ? MVD_Z_KB : MVD_Z_KB_SHORT;
         constexpr int KB = EPT >= KB_ ? KB_ : EPT;
+        if constexpr (PIPE) {
+            cp_async_wait_all();
+#pragma unroll
+            for (int m = 0; m < EPT; ++m) v[m] = cmul(v[m], stage[m * NTH]);
+        } else
 #pragma unroll
         for (int h = 0; h < EPT; h += KB) {
             float2 kk[KB];
@@ -430,8 +471,15 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
         }
         if constexpr (TZ > 1) __syncthreads();
         line_fft<BZ, EPT, true>(v, t, twz, put, get, sync);
-        const Tile tile = tiles[ti];
-        const int zlo = tile.e[2] - tile.o[2], zhi = zlo + tile.n[2];
+        int zlo, zhi;
+        if constexpr (PIPE) {
+            zlo = zlo_p;
+            zhi = zhi_p;
+        } else {
+            const Tile tile = tiles[ti];
+            zlo = tile.e[2] - tile.o[2];
+            zhi = zlo + tile.n[2];
+        }
         if (valid) {
             const unsigned pl = (unsigned)opaque(plane_elems);
 #pragma unroll
@@ -963,7 +1011,7 @@ cudaError_t launch_z_pass(int bx, int by, int bz, int mode, float2* scratch, con
 #define F(BZ)                                                                                                          \
     {                                                                                                                  \
         const int n_items = n_tiles * ((pe + ZCfg<BZ>::PW - 1) / ZCfg<BZ>::PW);                                        \
-        const int cap = g_z_grid_cap > 0 ? g_z_grid_cap : (ZCfg<BZ>::ASYNC ? g_num_sms * ZCfg<BZ>::MIN_CTAS : 0);       \
+        const int cap = g_z_grid_cap > 0 ? g_z_grid_cap : ((ZCfg<BZ>::ASYNC || (ZCfg<BZ>::PIPE && mode == 1)) ? g_num_sms * ZCfg<BZ>::MIN_CTAS : 0); \
         const int grid = cap > 0 ? std::min(n_items, cap) : n_items;                                                   \
         if (mode == 0) z_pass_kernel<BZ, 0><<<grid, ZCfg<BZ>::THREADS, ZCfg<BZ>::SMEM, st>>>(scratch, stride, kspec, d_tiles, pe, scale, n_tiles, n_items, to_dev(tw)); \
         else z_pass_kernel<BZ, 1><<<grid, ZCfg<BZ>::THREADS, ZCfg<BZ>::SMEM, st>>>(scratch, stride, kspec, d_tiles, pe, scale, n_tiles, n_items, to_dev(tw)); \

@@ -83,7 +83,14 @@ static const int kZSizes[] = {16, 32, 64, 128, 256, 512};
 static std::vector<AxisTile> plan_axes(const int dim[3], const int k[3], int d) {
     if (d == 0) return plan_axis(dim[0], k[0], 4, kXYSizes, 3);
     if (d == 1) return plan_axis(dim[1], k[1], 4, kXYSizes, 3);  // multiples of 4 rows: whole row rounds in inv_xy
-    return plan_axis(dim[2], k[2], 1, kZSizes, 6);
+    // MVD_ZMAX (tuning): largest z window.  Shorter windows make tiles small enough for a batch's
+    // scratch to stay in L2 between the three kernels, at the price of more halo planes.
+    int nz = 6;
+    if (const char* s = std::getenv("MVD_ZMAX")) {
+        const int zmax = std::atoi(s);
+        while (nz > 1 && zmax > 0 && kZSizes[nz - 1] > zmax) --nz;
+    }
+    return plan_axis(dim[2], k[2], 1, kZSizes, nz);
 }
 
 std::unique_ptr<ConvPlan> make_plan(const int dim[3], const int k[3]) {
@@ -192,6 +199,16 @@ Device::Device(int id) : id_(id) {
     if (const char* s = std::getenv("MVD_XY_CTAS")) xy = std::atoi(s);
     if (const char* s = std::getenv("MVD_Z_CTAS")) z = std::atoi(s);
     set_grid_caps(xy * prop.multiProcessorCount, z * prop.multiProcessorCount);
+    // MVD_L2_PERSIST=<MB> (tuning): keep batch scratch of at most that size persisting in L2 between the
+    // three kernels of a batch (access policy window on the batch's stream)
+    if (const char* s = std::getenv("MVD_L2_PERSIST")) {
+        const long v = std::atol(s);
+        if (v > 0 && prop.persistingL2CacheMaxSize > 0) {
+            l2_persist_bytes_ = std::min<size_t>((size_t)v << 20, (size_t)prop.persistingL2CacheMaxSize);
+            l2_window_max_ = (size_t)prop.accessPolicyMaxWindowSize;
+            MVD_CUDA(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, l2_persist_bytes_));
+        }
+    }
 }
 
 void Scratch::init(int n) {
@@ -354,6 +371,20 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
             }
             scratch.reserve(li, (size_t)batch * te);
             float2* buf = scratch.data[li];
+            if (dev.l2_persist_bytes() > 0 && scratch.window[li] != buf) {
+                const size_t bytes = (size_t)batch * te * sizeof(float2);
+                if (bytes <= dev.l2_persist_bytes() && bytes <= dev.l2_window_max()) {
+                    cudaStreamAttrValue av;
+                    std::memset(&av, 0, sizeof(av));
+                    av.accessPolicyWindow.base_ptr = buf;
+                    av.accessPolicyWindow.num_bytes = bytes;
+                    av.accessPolicyWindow.hitRatio = 1.f;
+                    av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                    av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                    MVD_CUDA(cudaStreamSetAttribute(ls, cudaStreamAttributeAccessPolicyWindow, &av));
+                }
+                scratch.window[li] = buf;
+            }
             double nz_sum = 0, out_vox = 0;
             if (prof)
                 for (int i = s; i < s + cnt; ++i) {

@@ -79,6 +79,8 @@ public:
     size_t scratch_budget_bytes() const { return scratch_budget_; }
     int lanes() const { return lanes_; }
     int sm_count() const { return sm_count_; }
+    size_t l2_persist_bytes() const { return l2_persist_bytes_; }
+    size_t l2_window_max() const { return l2_window_max_; }
     std::mutex legacy_mutex;  // serialises the drop-in symbol per device
 
 private:
@@ -88,6 +90,7 @@ private:
     size_t scratch_budget_;
     int lanes_ = 1;
     int sm_count_ = 148;
+    size_t l2_persist_bytes_ = 0, l2_window_max_ = 0;
 };
 
 // Scratch for the tile batches of one convolution stream.  Lane 0 is the caller's stream; batches too
@@ -101,6 +104,7 @@ struct Scratch {
     cudaEvent_t fork = nullptr;
     cudaEvent_t join[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
     int lanes = 0;  // 0 = not initialised
+    const float2* window[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};  // buffer the lane's L2 access-policy window covers
     void init(int n);
     void reserve(int lane_index, size_t n);
     ~Scratch();

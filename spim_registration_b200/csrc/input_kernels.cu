@@ -20,6 +20,7 @@
 // the Java code (AffineTransform3D.applyInverse, the interpolation weights, the weight sum).
 #include "input_kernels.h"
 
+#include <algorithm>
 #include <cmath>
 
 namespace mvd {
@@ -128,6 +129,80 @@ __global__ void __launch_bounds__(256) normalize_weights_kernel(WeightPtrs w, si
         for (int i = 0; i < 8; ++i) { c += s_cnt[i]; m = min(m, s_min[i]); }
         atomicAdd(d_count, c);
         atomicMin(d_min, m);
+    }
+}
+
+// ---- virtual weights (the dialog's default weight type) -------------------------------------------
+// The reference evaluates, per voxel, per view and per iteration, the blending function at the voxel's
+// position inside the view (TransformedInterpolatedRealRandomAccess.applyInverse :68-95: integer world
+// coordinate -> double, t0*i00 + t1*i01 + t2*i02 + i03 left to right, cast to float) divided by the
+// float image of weight sums (NormalizingRandomAccess.get :36-45).  Here both are evaluated once and kept.
+__device__ __forceinline__ void view_position(const double* __restrict__ inv, int wx, int wy, int wz, float t[3]) {
+    const double t0 = (double)wx, t1 = (double)wy, t2 = (double)wz;
+#pragma unroll
+    for (int d = 0; d < 3; ++d)  // no fused multiply-add: Java rounds every product and sum
+        t[d] = (float)__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(t0, inv[4 * d]), __dmul_rn(t1, inv[4 * d + 1])), __dmul_rn(t2, inv[4 * d + 2])), inv[4 * d + 3]);
+}
+
+// WeightNormalizer.ComputeSumImage (:183-232): double sum of the views' float weights, stored as float
+// where it exceeds 1 and as 1 elsewhere; number of views with weight > 0 per voxel (min and total).
+__global__ void __launch_bounds__(256) virtual_weight_sum_kernel(const BlendView* __restrict__ views, int n_views, VolumeBox box,
+                                                                 float* __restrict__ sum_w, unsigned long long* __restrict__ d_count,
+                                                                 int* __restrict__ d_min) {
+    __shared__ unsigned long long s_cnt[8];
+    __shared__ int s_min[8];
+    unsigned long long lcnt = 0;
+    int lmin = n_views;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const long long rows = (long long)box.dim[1] * box.dim[2];
+    if (x < box.dim[0]) {
+        for (long long r = blockIdx.y; r < rows; r += gridDim.y) {
+            const int y = (int)(r % box.dim[1]), z = (int)(r / box.dim[1]);
+            double sum = 0.0;
+            int count = 0;
+            for (int v = 0; v < n_views; ++v) {
+                const BlendView& bv = views[v];
+                float t[3];
+                view_position(bv.inv, x + box.offset[0], y + box.offset[1], z + box.offset[2], t);
+                const float w = blend_weight(t, bv.dim_minus1, bv.border, bv.blending);
+                sum += (double)w;
+                if (w > 0.f) ++count;
+            }
+            lcnt += count;
+            lmin = min(lmin, count);
+            sum_w[(size_t)r * box.dim[0] + x] = sum > 1.0 ? (float)sum : 1.f;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lcnt += __shfl_xor_sync(0xffffffffu, lcnt, o);
+        lmin = min(lmin, __shfl_xor_sync(0xffffffffu, lmin, o));
+    }
+    if ((threadIdx.x & 31) == 0) { s_cnt[threadIdx.x >> 5] = lcnt; s_min[threadIdx.x >> 5] = lmin; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long c = 0;
+        int m = n_views;
+        for (int i = 0; i < 8; ++i) { c += s_cnt[i]; m = min(m, s_min[i]); }
+        atomicAdd(d_count, c);
+        atomicMin(d_min, m);
+    }
+}
+
+// NormalizingRandomAccess.get (:36-45): (float) min(1, (double)w / (double)sumW * osemspeedup)
+__global__ void __launch_bounds__(256) virtual_weight_kernel(BlendView bv, VolumeBox box, const float* __restrict__ sum_w, double osem,
+                                                             float* __restrict__ out_w) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const long long rows = (long long)box.dim[1] * box.dim[2];
+    if (x >= box.dim[0]) return;
+    for (long long r = blockIdx.y; r < rows; r += gridDim.y) {
+        const int y = (int)(r % box.dim[1]), z = (int)(r / box.dim[1]);
+        const size_t i = (size_t)r * box.dim[0] + x;
+        float t[3];
+        view_position(bv.inv, x + box.offset[0], y + box.offset[1], z + box.offset[2], t);
+        const float w = blend_weight(t, bv.dim_minus1, bv.border, bv.blending);
+        const double v = __dmul_rn(__ddiv_rn((double)w, (double)__ldg(sum_w + i)), osem);
+        out_w[i] = v != v ? (float)v : (float)fmin(1.0, v);  // Math.min(1, NaN) is NaN
     }
 }
 
@@ -252,6 +327,22 @@ cudaError_t launch_transform_psf(const float* d_psf, const PsfArgs& a, float* d_
     const int n = a.size[0] * a.size[1] * a.size[2];
     if (n <= 0) return cudaSuccess;
     transform_psf_kernel<<<(n + 127) / 128, 128, 0, st>>>(d_psf, a, d_out);
+    return cudaGetLastError();
+}
+
+static dim3 row_grid(const int dim[3]) {
+    const long long rows = (long long)dim[1] * dim[2];
+    return dim3((unsigned)((dim[0] + 255) / 256), (unsigned)std::min<long long>(rows, 65535), 1);
+}
+
+cudaError_t launch_virtual_weight_sum(const BlendView* d_views, int n_views, const VolumeBox& box, float* sum_w, unsigned long long* d_count,
+                                      int* d_min, cudaStream_t st) {
+    virtual_weight_sum_kernel<<<row_grid(box.dim), 256, 0, st>>>(d_views, n_views, box, sum_w, d_count, d_min);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_virtual_weight(const BlendView& view, const VolumeBox& box, const float* sum_w, double osem, float* out_w, cudaStream_t st) {
+    virtual_weight_kernel<<<row_grid(box.dim), 256, 0, st>>>(view, box, sum_w, osem, out_w);
     return cudaGetLastError();
 }
 

@@ -16,6 +16,18 @@ struct TransformArgs {
     float min_value;    // MVDeconvolution.minValue (1e-4f)
 };
 
+// one view of the virtual-weight evaluation (Blending + the inverse of the view's registration)
+struct BlendView {
+    double inv[12];     // row-major 3x4: world voxel -> view voxel coordinates
+    int dim_minus1[3];  // view size - 1 (BlendingRealRandomAccess.dimMinus1)
+    float border[3];
+    float blending[3];
+};
+struct VolumeBox {
+    int offset[3];  // bounding-box minimum in world voxels
+    int dim[3];
+};
+
 struct WeightPtrs {
     float* w[kMaxViews];
     int n;
@@ -33,6 +45,9 @@ cudaError_t launch_extract_psf(const float* img, const PsfArgs& a, const double*
 cudaError_t launch_transform_psf(const float* d_psf, const PsfArgs& a, float* d_out, cudaStream_t st);
 cudaError_t launch_transform_view(const float* src, const TransformArgs& a, float* out_img, float* out_w, cudaStream_t st);
 cudaError_t launch_normalize_weights(const WeightPtrs& w, size_t n, unsigned long long* d_count, int* d_min, cudaStream_t st);
+cudaError_t launch_virtual_weight_sum(const BlendView* d_views, int n_views, const VolumeBox& box, float* sum_w, unsigned long long* d_count,
+                                      int* d_min, cudaStream_t st);
+cudaError_t launch_virtual_weight(const BlendView& view, const VolumeBox& box, const float* sum_w, double osem, float* out_w, cudaStream_t st);
 cudaError_t launch_osem(float* w, size_t n, float speedup, cudaStream_t st);
 
 }  // namespace mvd

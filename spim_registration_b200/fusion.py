@@ -65,6 +65,51 @@ class WeightNormalizer:
         return self.avgOverlappingViews
 
 
+class VirtualWeights:
+    """WeightType.VIRTUAL_WEIGHTS (ProcessForDeconvolution.java:204-208, 308-309, 375-379): blending functions
+    seen through the views' registrations, normalised by a sum image (WeightNormalizer.java:42-46, 183-232,
+    NormalizingRandomAccess.java:36-45).  The reference evaluates them on every access; here every view's
+    weight image is evaluated once on the device (csrc/input_kernels.cu) with identical values.
+
+    views: list of (srcDim (x,y,z), transform (view -> world, 3x4 or 4x4), blendingBorder, blendingRange)."""
+
+    def __init__(self, views, offset, dimensions, device=0):
+        self.views = [(tuple(int(v) for v in d), _inverse_3x4(t), tuple(map(float, b)), tuple(map(float, r))) for d, t, b, r in views]
+        self.offset, self.dimensions, self.device = tuple(offset), tuple(dimensions), device
+        self.sumWeights = None
+        self.minOverlappingViews, self.avgOverlappingViews = None, None
+        self.osemspeedup = 1.0
+
+    def process(self):
+        """WeightNormalizer.process with a sum image: computes sumWeights and the overlap statistics."""
+        lib = _lib.load()
+        n = len(self.views)
+        dims = (C.c_int * (3 * n))(*[v for d, _, _, _ in self.views for v in d])
+        inv = np.ascontiguousarray(np.stack([i for _, i, _, _ in self.views]).reshape(-1))
+        fb = (C.c_float * (3 * n))(*[v for _, _, b, _ in self.views for v in b])
+        fr = (C.c_float * (3 * n))(*[v for _, _, _, r in self.views for v in r])
+        self.sumWeights = np.empty(self.dimensions[::-1], F32)
+        mn, avg = C.c_int(), C.c_double()
+        _lib.check(lib.mvdVirtualWeightSum(int(self.device), n, dims, inv.ctypes.data_as(_lib.c_double_p), fb, fr, _lib.int3(self.offset),
+                                           _lib.int3(self.dimensions), self.sumWeights.ctypes.data_as(C.c_void_p), C.byref(mn), C.byref(avg), 0),
+                   "mvdVirtualWeightSum")
+        self.minOverlappingViews, self.avgOverlappingViews = mn.value, avg.value
+        return True
+
+    def setOSEMspeedup(self, osemspeedup):
+        self.osemspeedup = float(osemspeedup)
+
+    def weight(self, view):
+        """The values NormalizingRandomAccess.get returns for one view, as float32 [z,y,x]."""
+        lib = _lib.load()
+        d, inv, b, r = self.views[view]
+        out = np.empty(self.dimensions[::-1], F32)
+        _lib.check(lib.mvdVirtualWeight(int(self.device), _lib.int3(d), inv.ctypes.data_as(_lib.c_double_p), (C.c_float * 3)(*b), (C.c_float * 3)(*r),
+                                        _lib.int3(self.offset), _lib.int3(self.dimensions), self.sumWeights.ctypes.data_as(C.c_void_p),
+                                        self.osemspeedup, out.ctypes.data_as(C.c_void_p), 0), "mvdVirtualWeight")
+        return out
+
+
 class ExtractPSF:
     """ExtractPSF.java: extraction of a view's PSF from bead locations and its transformation into the
     fused coordinate system; the sampling runs in libmvdecon.so (csrc/input_kernels.cu)."""

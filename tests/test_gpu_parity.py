@@ -48,6 +48,8 @@ def _kernel(shape, seed):
     ((64, 64, 64), (15, 15, 15)),
     ((70, 130, 150), (15, 11, 9)),   # several windows per axis, mixed window sizes
     ((96, 200, 260), (31, 31, 31)),
+    ((300, 36, 40), (31, 5, 7)),     # z needs the 512-point window
+    ((530, 20, 24), (15, 3, 3)),     # z = 512-point window + a short one
 ])
 @pytest.mark.parametrize("mode", ["zero", "const", "mirror"])
 def test_convolution_matches_oracle(m, o, shape, ks, mode):
@@ -404,6 +406,37 @@ def test_weight_normalizer_matches_oracle(m, o):
         assert wn.getMinOverlappingViews() == mn and abs(wn.getAvgOverlappingViews() - avg) < 1e-9
         for a, b in zip(wn.weights, ref):
             np.testing.assert_array_equal(a, o.adjust_for_osem(b, speed))  # NaN == NaN position-wise, values bit-exact
+
+
+@pytest.mark.parametrize("osem", [1.0, 2.0])
+def test_virtual_weights_match_oracle(m, o, osem):
+    """WeightType.VIRTUAL_WEIGHTS materialised on the device == NormalizingRandomAccess over the blending functions
+    restated by the oracle: sum image, overlap statistics and every view's weights bit-exact."""
+    offset, dims = (-10, -4, -8), (120, 60, 110)
+    views = [((52, 44, 30), _registration(0.0, 2.5, (20.0, 5.0, 30.0)), (0, 0, 0), (8, 8, 4)),
+             ((52, 44, 30), _registration(35.0, 2.5, (25.0, 3.0, 20.0)), (3, 2, 1), (10, 12, 6)),
+             ((40, 50, 36), _registration(90.0, 2.0, (60.0, 0.0, 10.0)), (-2, 0, 0), (5, 5, 5))]
+    vw = m.VirtualWeights(views, offset, dims)
+    assert vw.process()
+    blends = [o.virtual_blending(np.linalg.inv(reg)[:3, :4], offset, dims, d, b, r) for d, reg, b, r in views]
+    ref_sum, mn, avg = o.compute_sum_image(blends)
+    assert (ref_sum > 1).mean() > 0.01 and (ref_sum == 1).mean() > 0.01   # both branches of the sum image
+    np.testing.assert_array_equal(vw.sumWeights, ref_sum)
+    assert vw.minOverlappingViews == mn and abs(vw.avgOverlappingViews - avg) < 1e-9
+    vw.setOSEMspeedup(osem)
+    for v in range(len(views)):
+        np.testing.assert_array_equal(vw.weight(v), o.normalizing_weight(blends[v], ref_sum, osem))
+
+
+def test_virtual_weights_equal_the_blending_of_transform_view(m, o):
+    """The two routes to a blending weight (TransformInputAndWeights and the virtual accessor) see the same positions."""
+    reg = _registration(35.0, 2.5, (20.0, 5.0, 30.0))
+    offset, dims = (-10, -4, -8), (96, 60, 70)
+    img = np.ones((30, 44, 52), np.float32)
+    _, w = m.transformInputAndWeights(img, reg, offset, dims, (3, 2, 1), (10, 12, 6))
+    vw = m.VirtualWeights([((52, 44, 30), reg, (3, 2, 1), (10, 12, 6))], offset, dims)
+    vw.process()
+    np.testing.assert_array_equal(vw.weight(0), o.normalizing_weight(w, vw.sumWeights))
 
 
 def test_device_prepared_inputs_drive_the_loop(m, o):

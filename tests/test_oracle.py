@@ -321,6 +321,30 @@ def test_weight_normalisation_and_osem():
 
 
 # ---- PSF extraction (ExtractPSF.java) -------------------------------------------
+def test_virtual_weights_known_answers():
+    """WeightType.VIRTUAL_WEIGHTS: identity registration -> the plain blending image; sum image = max(1, sum);
+    NormalizingRandomAccess = min(1, w / sumW * osem); with two identical views each gets 1/2 in the plateau."""
+    dims = (40, 30, 20)
+    ident = np.eye(4)[:3, :4]
+    b = o.virtual_blending(ident, (0, 0, 0), dims, dims, (0, 0, 0), (6, 6, 6))
+    assert b.shape == dims[::-1] and b.dtype == np.float32
+    assert b[10, 15, 20] == 1.0 and b[0, 15, 20] == 0.0 and b[10, 15, 39] == 0.0
+    # position convention: shifted bounding box and view
+    shifted = o.virtual_blending(np.array([[1, 0, 0, -5.0], [0, 1, 0, 0], [0, 0, 1, 0]]), (5, 0, 0), dims, dims, (0, 0, 0), (6, 6, 6))
+    np.testing.assert_array_equal(shifted, b)
+    s, mn, avg = o.compute_sum_image([b, b])
+    assert s.min() == 1.0 and s[10, 15, 20] == 2.0 and mn == 0 and 0 < avg < 2
+    w = o.normalizing_weight(b, s)
+    assert w[10, 15, 20] == 0.5 and w[0, 15, 20] == 0.0
+    # in the ramp the sum stays <= 1 until both weights exceed 1/2: there the weight is not normalised
+    ramp = (s == 1) & (b > 0)
+    np.testing.assert_array_equal(w[ramp], b[ramp])
+    np.testing.assert_array_equal(o.normalizing_weight(b, s, 3.0), np.minimum(np.float32(1), (b.astype(np.float64) / s * 3.0)).astype(np.float32))
+    # same positions as the TransformInputAndWeights route
+    _, w2 = o.transform_input_and_weights(np.ones(dims[::-1], np.float32), ident, (0, 0, 0), dims, (0, 0, 0), (6, 6, 6))
+    np.testing.assert_array_equal(w2, b)
+
+
 def test_extract_psf_known_answers():
     rng = np.random.default_rng(31)
     img = rng.random((12, 14, 16), dtype=np.float32)
