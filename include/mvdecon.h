@@ -89,6 +89,7 @@ const char* mvdVersion(void);
 
 #define MVD_MEM_HOST 0
 #define MVD_MEM_DEVICE 1
+#define MVD_MEM_HOST_IMG_DEVICE_WEIGHT 2 /* mvdAddView only: img on the host, weight evaluated on the device (mvdVirtualWeight) */
 
 /* Create a context on CUDA device `device` for one brick of the deconvolved volume.
  *   globalDim   (x,y,z) size of the whole deconvolved volume psi.
@@ -113,7 +114,8 @@ int mvdSynchronize(mvdContext* ctx);
  *   weight   brickDim floats or NULL; with NULL the constant `weightConst` is used (the
  *            reference's NO_WEIGHTS case after normalisation, ProcessForDeconvolution.java:351-384).
  *   kernel1, kernel2  already prepared as by MVDeconFFT.init (MVDeconFFT.java:162-303), dims (x,y,z).
- *   memKind  MVD_MEM_HOST or MVD_MEM_DEVICE: where img and weight live (kernels are always host).
+ *   memKind  MVD_MEM_HOST or MVD_MEM_DEVICE: where img and weight live (kernels are always host);
+ *            MVD_MEM_HOST_IMG_DEVICE_WEIGHT: img on the host, weight on the device.
  * Returns the view index through *viewIndex (may be NULL). */
 int mvdAddView(mvdContext* ctx, const float* img, const float* weight, float weightConst, const float* kernel1,
                const int kernel1Dim[3], const float* kernel2, const int kernel2Dim[3], int memKind, int* viewIndex);

@@ -36,6 +36,14 @@ static int latch(int code, const std::string& msg) {
     return code;
 }
 
+namespace {
+struct StreamGuard {
+    cudaStream_t st = nullptr;
+    StreamGuard() { MVD_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)); }
+    ~StreamGuard() { if (st) cudaStreamDestroy(st); }
+};
+}  // namespace
+
 template <class F> static int guarded(F&& f) {
     try {
         f();
@@ -370,20 +378,25 @@ extern "C" int mvdAddView(mvdContext* c, const float* img, const float* weight, 
             if (hi_nb) require(c->ghi[d] >= std::max(k1[d] / 2, need1) && c->ghi[d] >= std::max(k2[d] / 2, need2),
                                "mvdAddView: ghost layer narrower than the kernel halo");
         }
+        require(memKind == MVD_MEM_HOST || memKind == MVD_MEM_DEVICE || memKind == MVD_MEM_HOST_IMG_DEVICE_WEIGHT, "mvdAddView: bad memKind");
         const cudaMemcpyKind kind = memKind == MVD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+        const cudaMemcpyKind wkind = memKind == MVD_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
         ViewData v;
         const size_t bytes = c->brick_elems() * sizeof(float);
         MVD_CUDA(cudaMalloc(&v.img, bytes));
         MVD_CUDA(cudaMemcpyAsync(v.img, img, bytes, kind, c->stream));
         if (weight) {
             MVD_CUDA(cudaMalloc(&v.weight, bytes));
-            MVD_CUDA(cudaMemcpyAsync(v.weight, weight, bytes, kind, c->stream));
+            MVD_CUDA(cudaMemcpyAsync(v.weight, weight, bytes, wkind, c->stream));
         }
         v.weight_const = weightConst;
         v.plan1 = c->plan_for(k1);
         v.plan2 = c->plan_for(k2);
-        v.spec1 = build_spectra(*c->dev, *c->plans[v.plan1], kernel1, c->stream);
-        v.spec2 = build_spectra(*c->dev, *c->plans[v.plan2], kernel2, c->stream);
+        {   // on a stream of their own: the spectra are built while the image and the weights upload
+            StreamGuard aux;
+            v.spec1 = build_spectra(*c->dev, *c->plans[v.plan1], kernel1, aux.st);
+            v.spec2 = build_spectra(*c->dev, *c->plans[v.plan2], kernel2, aux.st);
+        }
         v.sep_kmax1 = separate_kernel(kernel1, k1, v.taps1);
         v.sep_kmax2 = separate_kernel(kernel2, k2, v.taps2);
         MVD_CUDA(cudaStreamSynchronize(c->stream));  // caller buffers may go away after return
@@ -778,11 +791,6 @@ struct DevBuf {
     void* p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
     void alloc(size_t bytes) { MVD_CUDA(cudaMalloc(&p, bytes)); }
-};
-struct StreamGuard {
-    cudaStream_t st = nullptr;
-    StreamGuard() { MVD_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)); }
-    ~StreamGuard() { if (st) cudaStreamDestroy(st); }
 };
 void use_device(int device) {
     int n_dev = 0;

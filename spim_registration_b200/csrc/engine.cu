@@ -1,5 +1,6 @@
 // Host side of the tiled convolution engine (see engine.h).
 #include "engine.h"
+#include "volume_kernels.h"
 
 #include <algorithm>
 #include <cmath>
@@ -245,43 +246,49 @@ std::unique_ptr<KernelSpectra> build_spectra(Device& dev, const ConvPlan& plan, 
     double sum = 0.0;
     for (size_t i = 0; i < (size_t)k[0] * k[1] * k[2]; ++i) sum += kernel_host[i];
     spec->kernel_sum = sum;
-    for (const auto& c : plan.classes) {
+    // The kernel goes to the device once (K floats); padding and rotation happen there, so the host does
+    // no work proportional to the window size and nothing here waits for the caller's stream.
+    const size_t kn = (size_t)k[0] * k[1] * k[2];
+    size_t max_elems = 0;
+    for (const auto& c : plan.classes) max_elems = std::max(max_elems, (size_t)c.b[0] * c.b[1] * c.b[2]);
+    float* d_k = nullptr;
+    float* d_kc = nullptr;
+    Tile* d_tile = nullptr;
+    // stream-ordered temporaries: cudaFree would wait for the whole device, i.e. for the caller's uploads
+    struct Cleanup {
+        float*& a; float*& b; Tile*& t; cudaStream_t st;
+        ~Cleanup() { if (a) cudaFreeAsync(a, st); if (b) cudaFreeAsync(b, st); if (t) cudaFreeAsync(t, st); }
+    } cleanup{d_k, d_kc, d_tile, st};
+    MVD_CUDA(cudaMallocAsync(&d_k, kn * sizeof(float), st));
+    MVD_CUDA(cudaMallocAsync(&d_kc, max_elems * sizeof(float), st));
+    MVD_CUDA(cudaMallocAsync(&d_tile, plan.classes.size() * sizeof(Tile), st));
+    MVD_CUDA(cudaMemcpyAsync(d_k, kernel_host, kn * sizeof(float), cudaMemcpyHostToDevice, st));
+    std::vector<Tile> tiles(plan.classes.size());
+    for (size_t ci = 0; ci < plan.classes.size(); ++ci)
+        for (int d = 0; d < 3; ++d) { tiles[ci].o[d] = 0; tiles[ci].e[d] = 0; tiles[ci].n[d] = plan.classes[ci].b[d]; }
+    MVD_CUDA(cudaMemcpyAsync(d_tile, tiles.data(), tiles.size() * sizeof(Tile), cudaMemcpyHostToDevice, st));
+    for (size_t ci = 0; ci < plan.classes.size(); ++ci) {
+        const auto& c = plan.classes[ci];
         const int bx = c.b[0], by = c.b[1], bz = c.b[2];
-        // kernel centre (k/2) moved to index 0, wrapped circularly (FFTConvolution.java:506-516)
-        std::vector<float> kc((size_t)bx * by * bz, 0.f);
-        for (int z = 0; z < k[2]; ++z)
-            for (int y = 0; y < k[1]; ++y)
-                for (int x = 0; x < k[0]; ++x) {
-                    const int px = ((x - k[0] / 2) % bx + bx) % bx, py = ((y - k[1] / 2) % by + by) % by,
-                              pz = ((z - k[2] / 2) % bz + bz) % bz;
-                    kc[px + (size_t)bx * (py + (size_t)by * pz)] = kernel_host[x + (size_t)k[0] * (y + (size_t)k[1] * z)];
-                }
-        float* d_kc = nullptr;
-        Tile* d_tile = nullptr;
         float2* d_spec = nullptr;
         MVD_CUDA(cudaMalloc(&d_spec, tile_scratch_elems(bx, by, bz) * sizeof(float2)));
         spec->per_class.push_back(d_spec);
-        MVD_CUDA(cudaMalloc(&d_kc, kc.size() * sizeof(float)));
-        MVD_CUDA(cudaMalloc(&d_tile, sizeof(Tile)));
-        Tile t;
-        for (int d = 0; d < 3; ++d) { t.o[d] = 0; t.e[d] = 0; t.n[d] = c.b[d]; }
-        MVD_CUDA(cudaMemcpyAsync(d_kc, kc.data(), kc.size() * sizeof(float), cudaMemcpyHostToDevice, st));
-        MVD_CUDA(cudaMemcpyAsync(d_tile, &t, sizeof(Tile), cudaMemcpyHostToDevice, st));
+        // kernel centre (k/2) moved to index 0, wrapped circularly (FFTConvolution.java:506-516)
+        MVD_CUDA(cudaMemsetAsync(d_kc, 0, (size_t)bx * by * bz * sizeof(float), st));
+        MVD_CUDA(launch_wrap_kernel(d_k, k, d_kc, c.b, st));
         Volume v;
         v.data = d_kc;
         for (int d = 0; d < 3; ++d) { v.dim[d] = c.b[d]; v.off[d] = 0; v.gmin[d] = 0; v.gdim[d] = c.b[d]; }
         v.ext = EXT_ZERO;
         v.ext_value = 0.f;
-        MVD_CUDA(launch_fwd_xy(bx, by, bz, v, d_tile, 1, d_spec, dev.twiddles(), st));
+        MVD_CUDA(launch_fwd_xy(bx, by, bz, v, d_tile + ci, 1, d_spec, dev.twiddles(), st));
         // the forward x untangle omits its 1/2 for the image AND for this kernel spectrum (factor 4),
         // the unnormalised inverse contributes bx*by*bz
         const float scale = (float)(1.0 / (4.0 * (double)bx * (double)by * (double)bz));
-        MVD_CUDA(launch_z_pass(bx, by, bz, 0, d_spec, nullptr, d_tile, 1, scale, dev.twiddles(), st));
-        g_kernel_launches += 2;
-        MVD_CUDA(cudaStreamSynchronize(st));
-        cudaFree(d_kc);
-        cudaFree(d_tile);
+        MVD_CUDA(launch_z_pass(bx, by, bz, 0, d_spec, nullptr, d_tile + ci, 1, scale, dev.twiddles(), st));
+        g_kernel_launches += 3;
     }
+    MVD_CUDA(cudaStreamSynchronize(st));  // kernel_host and `tiles` may go away on return
     return spec;
 }
 

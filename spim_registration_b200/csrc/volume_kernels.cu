@@ -72,6 +72,28 @@ __global__ void __launch_bounds__(256) mask_kernel(ViewPtrs views, Int3 brick, f
     }
 }
 
+// Kernel image for one window size: zero-padded to the window and rotated so that the kernel centre
+// (k / 2) sits at index 0 (FFTConvolution.java:506-516).  `out` must be zeroed; one thread per kernel voxel.
+__global__ void __launch_bounds__(256) wrap_kernel_kernel(const float* __restrict__ k, Int3 kd, float* __restrict__ out, Int3 bd) {
+    const int n = kd.v[0] * kd.v[1] * kd.v[2];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int x = i % kd.v[0], y = (i / kd.v[0]) % kd.v[1], z = i / (kd.v[0] * kd.v[1]);
+        const int px = ((x - kd.v[0] / 2) % bd.v[0] + bd.v[0]) % bd.v[0], py = ((y - kd.v[1] / 2) % bd.v[1] + bd.v[1]) % bd.v[1],
+                  pz = ((z - kd.v[2] / 2) % bd.v[2] + bd.v[2]) % bd.v[2];
+        // windows are at least as long as the kernel, so no two kernel voxels land on the same slot
+        out[px + (size_t)bd.v[0] * (py + (size_t)bd.v[1] * pz)] = k[i];
+    }
+}
+
+cudaError_t launch_wrap_kernel(const float* d_kernel, const int k[3], float* d_out, const int b[3], cudaStream_t st) {
+    Int3 kd, bd;
+    for (int i = 0; i < 3; ++i) { kd.v[i] = k[i]; bd.v[i] = b[i]; }
+    const int n = k[0] * k[1] * k[2];
+    if (n <= 0) return cudaSuccess;
+    wrap_kernel_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_kernel, kd, d_out, bd);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_mask_never_updated(const ViewPtrs& views, const int brick[3], float* psi, const int psi_dim[3], const int psi_off[3],
                                       cudaStream_t st) {
     const size_t n = (size_t)brick[0] * brick[1] * brick[2];

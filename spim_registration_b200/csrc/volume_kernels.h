@@ -18,4 +18,7 @@ cudaError_t launch_first_iteration_sums(const ViewPtrs& views, size_t n, double*
 cudaError_t launch_mask_never_updated(const ViewPtrs& views, const int brick[3], float* psi, const int psi_dim[3], const int psi_off[3],
                                       cudaStream_t st);
 
+// kernel zero-padded to a window of size b with its centre rotated to index 0; d_out must be zeroed
+cudaError_t launch_wrap_kernel(const float* d_kernel, const int k[3], float* d_out, const int b[3], cudaStream_t st);
+
 }  // namespace mvd

@@ -119,14 +119,16 @@ class ShardedDeconvolution:
             img, w = imgs[v], weights[v]
             is_dev = hasattr(img, "data_ptr")
             ip = C.c_void_p(img.data_ptr()) if is_dev else img.ctypes.data_as(C.c_void_p)
+            w_dev = hasattr(w, "data_ptr")
             if w is None or np.isscalar(w):
                 wp, wc = None, (1.0 if w is None else float(w))
             else:
-                wp, wc = (C.c_void_p(w.data_ptr()) if is_dev else w.ctypes.data_as(C.c_void_p)), 1.0
+                assert w_dev or not is_dev, "device images with host weights are not supported"
+                wp, wc = (C.c_void_p(w.data_ptr()) if w_dev else w.ctypes.data_as(C.c_void_p)), 1.0
             k1 = np.ascontiguousarray(kernel1[v], dtype=np.float32)
             k2 = np.ascontiguousarray(kernel2[v], dtype=np.float32)
             L.check(self.lib.mvdAddView(self.ctx, ip, wp, wc, k1.ctypes.data_as(L.c_float_p), L.int3(k1.shape[::-1]),
-                                        k2.ctypes.data_as(L.c_float_p), L.int3(k2.shape[::-1]), 1 if is_dev else 0, None), "mvdAddView")
+                                        k2.ctypes.data_as(L.c_float_p), L.int3(k2.shape[::-1]), 1 if is_dev else (2 if w_dev else 0), None), "mvdAddView")
         self._arrays = {}
         for which in (0, 1):
             ptr, dim, off = C.c_void_p(), (C.c_int * 3)(), (C.c_int * 3)()
