@@ -229,6 +229,41 @@ def test_config1_full_size(m, o):
     assert rel_l2(dec.getPsi(), ref) <= LOOP_TOL
 
 
+def test_config3_full_size_convolution_properties(m):
+    """BASELINE.json configs[2] geometry (1024x1024x512, kernel 31^3: 11 x 11 windows of 128 in xy, the 512- and
+    64-point windows in z) checked through size-independent properties, since the oracle does not finish at this
+    size: (i) a constant volume under mirror extension stays constant x sum(kernel) in every voxel of every tile;
+    (ii) deltas on tile seams, volume faces and corners each land one unflipped copy of an asymmetric kernel
+    (zero extension) and nothing else -- the volume sum equals the clipped kernel sums."""
+    Z, Y, X = 512, 1024, 1024
+    k = _kernel((31, 31, 31), 5)
+    h = 15
+    const = m.convolve(np.full((Z, Y, X), 0.75, np.float32), k, "mirror")
+    want = np.float32(0.75) * np.float32(k.astype(np.float64).sum())
+    assert np.abs(const - want).max() <= 4e-6 * want
+    del const
+    tiles = m.plan_tiles((X, Y, Z), (31, 31, 31))          # [n, (origin, first output, extent, window), xyz]
+    seam_x = sorted({int(t[1][0]) for t in tiles})[1]      # first output voxel of the second window along x
+    seam_y = sorted({int(t[1][1]) for t in tiles})[2]
+    seam_z = sorted({int(t[1][2]) for t in tiles})[-1]     # start of the short z window behind the 512-point one
+    pts = [(0, 0, 0), (Z - 1, Y - 1, X - 1), (seam_z, seam_y, seam_x), (seam_z - 1, seam_y - 1, seam_x - 1), (200, 500, X - 1),
+           (Z - 1, 40, 700), (300, seam_y, 3), (seam_z, 900, seam_x + 1)]
+    f = np.zeros((Z, Y, X), np.float32)
+    for i, p in enumerate(pts):
+        f[p] = 1.0 + i
+    out = m.convolve(f, k, "zero")
+    expected_sum = 0.0
+    for i, (z, y, x) in enumerate(pts):
+        lo = [max(0, c - h) for c in (z, y, x)]
+        hi = [min(n, c + h + 1) for c, n in zip((z, y, x), (Z, Y, X))]
+        patch = out[lo[0]:hi[0], lo[1]:hi[1], lo[2]:hi[2]]
+        kk = k[lo[0] - z + h:hi[0] - z + h, lo[1] - y + h:hi[1] - y + h, lo[2] - x + h:hi[2] - x + h] * np.float32(1.0 + i)
+        assert np.abs(patch - kk).max() <= 2e-6 * kk.max()
+        expected_sum += float(kk.astype(np.float64).sum())
+    assert abs(float(out.sum(dtype=np.float64)) - expected_sum) <= 1e-4 * expected_sum
+    assert float(np.abs(out).sum(dtype=np.float64)) <= expected_sum * (1 + 1e-3)   # nothing of either sign elsewhere
+
+
 @pytest.mark.parametrize("fused", [False, True])
 @pytest.mark.parametrize("grid,shape", [((2, 1, 1), (40, 56, 72)), ((1, 2, 2), (40, 56, 72)), ((2, 2, 2), (40, 56, 72)),
                                         ((2, 2, 2), (41, 54, 70)), ((4, 1, 2), (40, 30, 150))])
