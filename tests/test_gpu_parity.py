@@ -242,10 +242,11 @@ def test_config3_full_size_convolution_properties(m):
     want = np.float32(0.75) * np.float32(k.astype(np.float64).sum())
     assert np.abs(const - want).max() <= 4e-6 * want
     del const
-    tiles = m.plan_tiles((X, Y, Z), (31, 31, 31))          # [n, (origin, first output, extent, window), xyz]
-    seam_x = sorted({int(t[1][0]) for t in tiles})[1]      # first output voxel of the second window along x
-    seam_y = sorted({int(t[1][1]) for t in tiles})[2]
-    seam_z = sorted({int(t[1][2]) for t in tiles})[-1]     # start of the short z window behind the 512-point one
+    tiles = m.plan_tiles((X, Y, Z), (31, 31, 31))          # [n, (window, origin, first output voxel, output count), xyz]
+    seam_x = sorted({int(t[2][0]) for t in tiles})[1]      # first output voxel of the second window along x
+    seam_y = sorted({int(t[2][1]) for t in tiles})[2]
+    seam_z = sorted({int(t[2][2]) for t in tiles})[-1]     # start of the short z window behind the 512-point one
+    assert 0 < seam_x < X and 0 < seam_y < Y and 400 < seam_z < Z
     pts = [(0, 0, 0), (Z - 1, Y - 1, X - 1), (seam_z, seam_y, seam_x), (seam_z - 1, seam_y - 1, seam_x - 1), (200, 500, X - 1),
            (Z - 1, 40, 700), (300, seam_y, 3), (seam_z, 900, seam_x + 1)]
     f = np.zeros((Z, Y, X), np.float32)
