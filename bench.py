@@ -13,6 +13,7 @@ import argparse
 import ctypes as C
 import json
 import os
+import re
 import subprocess
 import sys
 import threading
@@ -330,13 +331,15 @@ def run_ours(args, cfg):
     # (dram__bytes_read.sum + dram__bytes_write.sum over complete convolutions) as a ratio to the byte
     # model, profiles/*_dram_traffic.json; applied to this run's algorithmic bytes per launch
     traffic, traffic_src = None, None
-    tj = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_v5_dram_traffic.json")
-    if os.path.exists(tj) and pl[top] > 0:
+    import glob
+    tjs = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_dram_traffic.json")), key=lambda f: [int(x) for x in re.findall(r"\d+", os.path.basename(f))])
+    tj = tjs[-1] if tjs else ""
+    if tj and pl[top] > 0:
         tk = json.load(open(tj))["kernels"]
         ratios = [v["traffic_over_model"] for k, v in tk.items() if k.startswith(names[top])]
         if ratios:
             traffic = sum(ratios) / len(ratios) * pb[top] / pl[top]
-            traffic_src = "profiles/r01_v5_dram_traffic.json (ncu --set full, dram bytes / byte model = %.3f) x this run's algorithmic bytes per launch" % (sum(ratios) / len(ratios))
+            traffic_src = "profiles/%s (ncu --set full, dram bytes / byte model = %.3f) x this run's algorithmic bytes per launch" % (os.path.basename(tj), sum(ratios) / len(ratios))
     loop_bytes = ALG_BYTES_PER_VOXEL_VIEW[cfg["dense_weights"]] * V * nvox * args.steps / world
     line = {
         "metric": "Gvoxel-iterations/sec (all views)", "value": value, "unit": "Gvoxel-iterations/s", "n_gpus": world,
