@@ -209,6 +209,7 @@ def run_ours(args, cfg):
     dev_index = local_device()
     torch.cuda.set_device(dev_index)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", dev_index))
     lib = m.load()
     Z, Y, X = cfg["shape"]
