@@ -204,6 +204,35 @@ def test_fixed_point_independent(m, o):
     assert rel_l2(dec.getPsi(), truth) <= 2e-5
 
 
+def test_fixed_point_at_config3_size(m):
+    """The fixed point of the INDEPENDENT update (SURVEY 8a invariant ii) at the 1024x1024x512 geometry of
+    BASELINE.json configs[2..3]: two views with their own asymmetric 31^3 kernels, a dense weight image,
+    a no-data slab.  img_v = conv1_v(truth) through the same engine, so the quotient is exactly 1 wherever
+    there is data and psi must stay at truth in every voxel of every tile; the slab is zeroed by the final mask."""
+    Z, Y, X = 512, 1024, 1024
+    rng = np.random.default_rng(21)
+    truth = rng.random((Z, Y, X), dtype=np.float32)
+    truth += np.float32(0.05)
+    weight = rng.random((Z, Y, X), dtype=np.float32)
+    weight *= np.float32(0.7)
+    weight += np.float32(0.3)
+    inp = m.MVDeconInput()
+    for v in range(2):
+        k = _kernel((31, 31, 31), 30 + v)
+        img = m.convolve(truth, k, "mirror")
+        img[:, :, :100] = 0          # no data in either view
+        view = m.MVDeconFFT(img, weight, k)
+        view.kernel2 = m.MVDeconFFT.computeInvertedKernel(k)
+        inp.add(view)
+        del img
+    dec = m.MVDeconvolution(inp, "INDEPENDENT", 1, 0.0, initialImage=truth, prepared=True)
+    psi = dec.getPsi()
+    assert (psi[:, :, :100] == 0).all()
+    diff = psi[:, :, 100:] - truth[:, :, 100:]
+    assert np.abs(diff).max() <= 1e-5
+    assert rel_l2(psi[:, :, 100:], truth[:, :, 100:]) <= 2e-6
+
+
 def test_no_data_and_constant_weight_edge_cases(m, o):
     shape = (24, 28, 36)
     rng = np.random.default_rng(3)
