@@ -3,7 +3,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <limits>
+#include <map>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -1266,25 +1268,107 @@ extern "C" long long getFreeMemDeviceCUDA(int dev) {
     return (long long)f;
 }
 
+// State the drop-in symbol keeps per device between calls (guarded by Device::legacy_mutex): the Java side calls
+// it once per block, convolution, view and iteration with the same few kernels (MVDeconFFTThreads.java:52-94), so
+// the block buffers, the tile plan and the kernel spectra are built once and reused.  Never destroyed: the CUDA
+// context may be gone by the time static destructors run.
+namespace {
+struct LegacyEntry {
+    int dim[3], k[3];
+    std::vector<float> kernel;  // compared byte-wise: the caller owns its array and may change it
+    std::unique_ptr<ConvPlan> plan;
+    std::unique_ptr<KernelSpectra> spec;
+    unsigned long long stamp = 0;
+};
+struct LegacyState {
+    cudaStream_t st = nullptr;
+    float* d_src = nullptr;
+    float* d_out = nullptr;
+    size_t cap = 0;
+    Scratch scratch;
+    std::vector<LegacyEntry> cache;
+    unsigned long long clock = 0;
+    static constexpr size_t kMaxEntries = 32;
+};
+std::mutex g_legacy_map_mutex;
+std::map<int, LegacyState*> g_legacy;
+
+LegacyState& legacy_state(int dev) {
+    std::lock_guard<std::mutex> lk(g_legacy_map_mutex);
+    LegacyState*& s = g_legacy[dev];
+    if (!s) s = new LegacyState();
+    return *s;
+}
+}  // namespace
+
 static int legacy_convolve(const float* im, const int* imDim, const float* kernel, const int* kernelDim, int dev, float* out) {
     return guarded([&] {
         require(im && imDim && kernel && kernelDim && out, "convolution3DfftCUDA: null argument");
         // the reference passes (z,y,x) (MVDeconFFTThreads.java:136-144)
         const int dim[3] = {imDim[2], imDim[1], imDim[0]};
         const int k[3] = {kernelDim[2], kernelDim[1], kernelDim[0]};
-        Device& d = Device::get(dev);
-        std::lock_guard<std::mutex> lk(d.legacy_mutex);
-        convolve_host(dev, im, dim, kernel, k, EXT_ZERO, 0.f, out);
+        for (int d = 0; d < 3; ++d) require(dim[d] > 0 && k[d] > 0, "convolution3DfftCUDA: non-positive size");
+        Device& device = Device::get(dev);
+        std::lock_guard<std::mutex> lk(device.legacy_mutex);
+        LegacyState& s = legacy_state(dev);
+        const size_t n = (size_t)dim[0] * dim[1] * dim[2], kn = (size_t)k[0] * k[1] * k[2];
+        if (!s.st) MVD_CUDA(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+        if (s.cap < n) {
+            if (s.d_src) cudaFree(s.d_src);
+            if (s.d_out) cudaFree(s.d_out);
+            s.d_src = s.d_out = nullptr;
+            s.cap = 0;
+            MVD_CUDA(cudaMalloc(&s.d_src, n * sizeof(float)));
+            MVD_CUDA(cudaMalloc(&s.d_out, n * sizeof(float)));
+            s.cap = n;
+        }
+        // the block goes up while the kernel is looked up (or its spectra are built on a stream of their own)
+        MVD_CUDA(cudaMemcpyAsync(s.d_src, im, n * sizeof(float), cudaMemcpyHostToDevice, s.st));
+        LegacyEntry* e = nullptr;
+        for (auto& c : s.cache)
+            if (std::memcmp(c.dim, dim, sizeof(dim)) == 0 && std::memcmp(c.k, k, sizeof(k)) == 0 &&
+                std::memcmp(c.kernel.data(), kernel, kn * sizeof(float)) == 0) {
+                e = &c;
+                break;
+            }
+        if (!e) {
+            if (s.cache.size() >= LegacyState::kMaxEntries) {
+                // the spectra of the least recently used kernel may still be read by nothing: every call synchronises
+                auto lru = std::min_element(s.cache.begin(), s.cache.end(), [](const LegacyEntry& a, const LegacyEntry& b) { return a.stamp < b.stamp; });
+                s.cache.erase(lru);
+            }
+            LegacyEntry ne;
+            std::memcpy(ne.dim, dim, sizeof(dim));
+            std::memcpy(ne.k, k, sizeof(k));
+            ne.kernel.assign(kernel, kernel + kn);
+            ne.plan = make_plan(dim, k);
+            StreamGuard aux;
+            ne.spec = build_spectra(device, *ne.plan, kernel, aux.st);
+            s.cache.push_back(std::move(ne));
+            e = &s.cache.back();
+        }
+        e->stamp = ++s.clock;
+        Volume v;
+        v.data = s.d_src;
+        for (int d = 0; d < 3; ++d) { v.dim[d] = dim[d]; v.off[d] = 0; v.gmin[d] = 0; v.gdim[d] = dim[d]; }
+        v.ext = EXT_ZERO;
+        v.ext_value = 0.f;
+        EpilogueArgs ep;
+        std::memset(&ep, 0, sizeof(ep));
+        ep.out = s.d_out;
+        for (int d = 0; d < 3; ++d) { ep.out_dim[d] = dim[d]; ep.out_off[d] = 0; ep.aux_dim[d] = dim[d]; }
+        run_convolution(device, *e->plan, *e->spec, v, EPI_STORE, ep, s.scratch, s.st);
+        // `out` may be the caller's block: nothing is written to it before the device has finished without error
+        MVD_CUDA(cudaStreamSynchronize(s.st));
+        MVD_CUDA(cudaMemcpyAsync(out, s.d_out, n * sizeof(float), cudaMemcpyDeviceToHost, s.st));
+        MVD_CUDA(cudaStreamSynchronize(s.st));
     });
 }
 
 extern "C" void convolution3DfftCUDAInPlace(float* im, int* imDim, float* kernel, int* kernelDim, int devCUDA) {
     if (!im || !imDim) { latch(1, "convolution3DfftCUDAInPlace: null argument"); return; }
-    const size_t n = (size_t)imDim[0] * imDim[1] * imDim[2];
-    float* tmp = (float*)std::malloc(n * sizeof(float));
-    if (!tmp) { latch(3, "out of host memory"); return; }
-    if (legacy_convolve(im, imDim, kernel, kernelDim, devCUDA, tmp) == 0) std::memcpy(im, tmp, n * sizeof(float));
-    std::free(tmp);  // on failure im is untouched
+    // on failure im is untouched (the result is copied back only after the device finished without error)
+    legacy_convolve(im, imDim, kernel, kernelDim, devCUDA, im);
 }
 
 extern "C" float* convolution3DfftCUDA(float* im, int* imDim, float* kernel, int* kernelDim, int devCUDA) {

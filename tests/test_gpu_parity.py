@@ -286,10 +286,17 @@ def test_config3_full_size_convolution_properties(m):
     for i, (z, y, x) in enumerate(pts):
         lo = [max(0, c - h) for c in (z, y, x)]
         hi = [min(n, c + h + 1) for c, n in zip((z, y, x), (Z, Y, X))]
+        want_patch = np.zeros([b - a for a, b in zip(lo, hi)], np.float64)
+        for j, q in enumerate(pts):   # neighbouring deltas overlap: every delta's footprint inside this patch
+            a = [max(l, c - h) for l, c in zip(lo, q)]
+            b = [min(u, c + h + 1) for u, c in zip(hi, q)]
+            if all(bb > aa for aa, bb in zip(a, b)):
+                want_patch[a[0] - lo[0]:b[0] - lo[0], a[1] - lo[1]:b[1] - lo[1], a[2] - lo[2]:b[2] - lo[2]] += (1.0 + j) * k[
+                    a[0] - q[0] + h:b[0] - q[0] + h, a[1] - q[1] + h:b[1] - q[1] + h, a[2] - q[2] + h:b[2] - q[2] + h]
         patch = out[lo[0]:hi[0], lo[1]:hi[1], lo[2]:hi[2]]
-        kk = k[lo[0] - z + h:hi[0] - z + h, lo[1] - y + h:hi[1] - y + h, lo[2] - x + h:hi[2] - x + h] * np.float32(1.0 + i)
-        assert np.abs(patch - kk).max() <= 2e-6 * kk.max()
-        expected_sum += float(kk.astype(np.float64).sum())
+        assert np.abs(patch - want_patch).max() <= 2e-6 * want_patch.max()
+        own = k[lo[0] - z + h:hi[0] - z + h, lo[1] - y + h:hi[1] - y + h, lo[2] - x + h:hi[2] - x + h]
+        expected_sum += (1.0 + i) * float(own.astype(np.float64).sum())
     assert abs(float(out.sum(dtype=np.float64)) - expected_sum) <= 1e-4 * expected_sum
     assert float(np.abs(out).sum(dtype=np.float64)) <= expected_sum * (1 + 1e-3)   # nothing of either sign elsewhere
 
