@@ -42,6 +42,28 @@ LAMBDA = 0.006
 ALG_BYTES_PER_VOXEL_VIEW = {True: 36.0, False: 32.0}  # SURVEY.md 8d / BASELINE.md section 3
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """stdout carries the one JSON line only: whatever libraries write to file descriptor 1 (NCCL prints its version
+    there) is sent to stderr, the line itself goes to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -209,7 +231,6 @@ def run_ours(args, cfg):
     dev_index = local_device()
     torch.cuda.set_device(dev_index)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", dev_index))
     lib = m.load()
     Z, Y, X = cfg["shape"]
@@ -367,7 +388,7 @@ def run_ours(args, cfg):
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_sample(cfg, k1, k2, budget_s=args.cpu_seconds)
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -444,7 +465,7 @@ def run_reference(args, cfg):
             "cpu_baseline": {"value": value, "unit": "Gvoxel-iterations/s", "cores": sample["cores"], "kind": "port", "sample": sample["sample"]},
             "e2e": {"value": value, "unit": "Gvoxel-iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -458,6 +479,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=20.0)
     args = ap.parse_args()
     cfg = CONFIGS[args.config]
+    quiet_stdout()
     if args.impl == "reference":
         run_reference(args, cfg)
     else:
