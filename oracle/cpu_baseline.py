@@ -8,8 +8,8 @@ through per-element accessors, J/fftMethods/FFTMethods.java:934-992):
   * block-wise copyBlock -> float32 R2C FFT -> pointwise multiply with the cached kernel FFT ->
     inverse FFT -> pasteBlock (MVDeconFFT.java:363-535, MVDeconFFTThreads.java:18-49,
     Block.java:114-195, J/fftMethods/FFTConvolution.java:470-551);
-  * the quotient and the update as separate elementwise passes
-    (MVDeconvolution.java:473-525, 582-703);
+  * the quotient and the update as separate elementwise passes, split over a pool of host threads
+    like the reference's portions (MVDeconvolution.java:446-463, 473-525, 582-703);
   * psi updated after every view (MVDeconvolution.java:353-441).
 
 Only bench.py's cpu_baseline leg / --impl reference and tests may import this.
@@ -63,6 +63,36 @@ def convolve_blocks(src, conv, mode, value, blocks):
     return out
 
 
+def _slabs(n, parts):
+    edges = np.linspace(0, n, min(parts, n) + 1).astype(int)
+    return [(int(a), int(b)) for a, b in zip(edges[:-1], edges[1:]) if b > a]
+
+
+def threaded_quotient(pool, parts, blurred, img):
+    """computeQuotient on z-slabs, one per thread (the reference splits the image into portions for a
+    thread pool, MVDeconvolution.java:446-463, 473-525); numpy releases the GIL inside the array operations."""
+    out = np.empty_like(blurred)
+
+    def work(ab):
+        a, b = ab
+        out[a:b] = o.compute_quotient(blurred[a:b], img[a:b])
+    list(pool.map(work, _slabs(blurred.shape[0], parts)))
+    return out
+
+
+def threaded_final_values(pool, parts, psi, integral, weight, lam):
+    """computeFinalValues on z-slabs (MVDeconvolution.java:582-659)."""
+    out = np.empty_like(psi)
+    dense = not np.isscalar(weight) and np.ndim(weight) > 0
+
+    def work(ab):
+        a, b = ab
+        out[a:b], s, mx = o.compute_final_values(psi[a:b], integral[a:b], weight[a:b] if dense else weight, lam)
+        return s, mx
+    stats = list(pool.map(work, _slabs(psi.shape[0], parts)))
+    return out, sum(s for s, _ in stats), max(mx for _, mx in stats)
+
+
 def run_iterations(imgs, weights, k1, k2, iterations, lam, block_size_xyz, psi, workers=None):
     """`iterations` passes over all views on the given volume; returns (psi, seconds)."""
     workers = workers or host_threads()
@@ -72,11 +102,13 @@ def run_iterations(imgs, weights, k1, k2, iterations, lam, block_size_xyz, psi, 
     conv2 = [BlockConvolver(k2[v], block_size_xyz, workers) for v in range(V)]
     blocks1 = [o.divide_into_blocks(shape_xyz, list(k1[v].shape[::-1]), block_size_xyz) for v in range(V)]
     blocks2 = [o.divide_into_blocks(shape_xyz, list(k2[v].shape[::-1]), block_size_xyz) for v in range(V)]
+    from concurrent.futures import ThreadPoolExecutor
     t0 = time.perf_counter()
-    for _ in range(iterations):
-        for v in range(V):
-            t1 = convolve_blocks(psi, conv1[v], "mirror", 0.0, blocks1[v])
-            t1 = o.compute_quotient(t1, imgs[v])
-            t2 = convolve_blocks(t1, conv2[v], "const", 1.0, blocks2[v])
-            psi, _, _ = o.compute_final_values(psi, t2, weights[v], lam)
+    with ThreadPoolExecutor(max_workers=workers) as pool:
+        for _ in range(iterations):
+            for v in range(V):
+                t1 = convolve_blocks(psi, conv1[v], "mirror", 0.0, blocks1[v])
+                t1 = threaded_quotient(pool, workers, t1, imgs[v])
+                t2 = convolve_blocks(t1, conv2[v], "const", 1.0, blocks2[v])
+                psi, _, _ = threaded_final_values(pool, workers, psi, t2, weights[v], lam)
     return psi, time.perf_counter() - t0

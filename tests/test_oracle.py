@@ -391,3 +391,20 @@ def test_average_transformed_psf_mirrors_about_the_centre():
     e = m.ExtractPSF()
     e.pointSpreadFunctions = [a, b]
     np.testing.assert_array_equal(e.computeAverageTransformedPSF(), avg)
+
+
+def test_cpu_baseline_port_matches_oracle():
+    """The timed CPU port (float32 pocketfft, 64^3 blocks, threaded elementwise passes) computes the oracle's loop."""
+    import cpu_baseline as cb
+    from spim_registration_b200 import synthetic
+    shape, V = (40, 72, 90), 2
+    ds = synthetic.make_dataset(shape, V, (7, 7, 7), convolve=lambda f, k: o.convolve_extended(f, k, "mirror"))
+    k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
+    rng = np.random.default_rng(4)
+    w = [(rng.random(shape, dtype=np.float32) * np.float32(0.5) + np.float32(0.2)) for _ in range(V)]
+    psi0 = np.full(shape, 0.3, np.float32)
+    ref, _, _ = o.run_deconvolution(ds["imgs"], w, k1, k2, 2, 0.006, psi0=psi0.copy())
+    got, seconds = cb.run_iterations(ds["imgs"], w, k1, k2, 2, 0.006, [64, 64, 64], psi0.copy(), workers=3)
+    assert seconds > 0
+    err = np.linalg.norm(got.astype(np.float64) - ref) / np.linalg.norm(ref.astype(np.float64))
+    assert err <= 1e-4
