@@ -29,8 +29,14 @@ namespace mvd {
 namespace {
 
 constexpr int SEP_NT = 128;   // threads per CTA = columns per CTA
-constexpr int SEP_CHY = 64;   // rows per CTA in the xy kernel
-constexpr int SEP_CHZ = 128;  // planes per CTA in the z kernel
+#ifndef MVD_SEP_CHY
+#define MVD_SEP_CHY 256
+#endif
+constexpr int SEP_CHY = MVD_SEP_CHY;  // rows per CTA in the xy kernel: the x pass also runs on the KMAX - 1 halo rows of a chunk
+#ifndef MVD_SEP_CHZ
+#define MVD_SEP_CHZ 256
+#endif
+constexpr int SEP_CHZ = MVD_SEP_CHZ;  // planes per CTA in the z kernel (+ KMAX - 1 halo planes read per chunk)
 
 constexpr int SEP_R = 16;    // rows per marching step of the xy kernel
 constexpr int SEP_WP = 164;  // pitch of the input strip: >= 128 + 31 - 1, multiple of 4, = 4 (mod 32) -> conflict-free LDS.128 across 8 rows
@@ -42,11 +48,13 @@ __global__ void __launch_bounds__(SEP_NT) sep_xy_kernel(Volume src, SepTaps taps
     // tmp: [src.dim[2]][by][bx] -- every resident plane of the source (brick and ghost planes)
     constexpr int H = KMAX / 2, R = SEP_R, W = SEP_NT + KMAX - 1;
     constexpr int NIN = (16 + KMAX - 1 + 3) / 4;  // float4 loads feeding 16 adjacent outputs
+    constexpr int HW = KMAX - 1;                  // halo columns of the strip (right of the CTA's 128)
+    constexpr int NH = (HW * R + SEP_NT - 1) / SEP_NT;  // halo elements per thread and step
     static_assert(W <= SEP_WP && 4 * NIN + 16 * 7 <= SEP_WP, "input strip too narrow");
     __shared__ __align__(16) float in[R][SEP_WP];
     __shared__ __align__(16) float xs[R][SEP_XP];
     __shared__ int xmap[W];
-    __shared__ int ymap[R];
+    __shared__ int ymap[2][R];
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * SEP_NT, y0 = blockIdx.y * SEP_CHY, za = blockIdx.z;
     const float fillv = src.ext == EXT_CONST ? src.ext_value : 0.f;
@@ -64,21 +72,49 @@ __global__ void __launch_bounds__(SEP_NT) sep_xy_kernel(Volume src, SepTaps taps
     const int yend = min(y0 + SEP_CHY, by);
     // x pass mapping: 8 consecutive threads take 8 different rows (conflict-free float4 reads), a thread makes 16 adjacent outputs
     const int xr = (tid & 7) + 8 * ((tid >> 3) & 1), xseg = (tid >> 4) * 16;
-#pragma unroll 1
-    for (int r0 = y0 - H; r0 < yend + H; r0 += R) {
-        __syncthreads();  // the previous step's column reads are done (first step: xmap and the cleared strip are ready)
-        if (tid < R) ymap[tid] = map_coord(r0 + tid, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
-        __syncthreads();
-        for (int idx = tid; idx < R * W; idx += SEP_NT) {
-            const int r = idx / W, i = idx - r * W;
-            const int yl = ymap[r];
-            if (yl >= 0) {
-                const int xi = xmap[i];
-                in[r][i] = xi >= 0 ? __ldg(zbase + (size_t)yl * src.dim[0] + xi) : (xi == -1 ? fillv : 0.f);
+    // The strip of the NEXT step is requested before the current step is convolved and waits in registers
+    // (pre: this thread's column of the 16 rows, coalesced; preh: its share of the halo columns), so the load
+    // latency hides behind the 2 x 16 x KMAX multiply-adds of a step.
+    float pre[R], preh[NH];
+    if (tid < R) ymap[0][tid] = map_coord(y0 - H + tid, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
+    __syncthreads();
+    const int xm = xmap[tid];
+    auto sample = [&](int yl, int xi) -> float {
+        return yl >= 0 ? (xi >= 0 ? __ldg(zbase + (size_t)yl * src.dim[0] + xi) : (xi == -1 ? fillv : 0.f)) : 0.f;
+    };
+    auto request = [&](const int* ym) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) pre[r] = sample(ym[r], xm);
+#pragma unroll
+        for (int j = 0; j < NH; ++j) {
+            const int e = tid + SEP_NT * j;
+            preh[j] = 0.f;
+            if (e < HW * R) {
+                const int r = e / HW;
+                preh[j] = sample(ym[r], xmap[SEP_NT + e - r * HW]);
             }
         }
+    };
+    request(ymap[0]);
+    int cur = 0;
+#pragma unroll 1
+    for (int r0 = y0 - H; r0 < yend + H; r0 += R, cur ^= 1) {
+        __syncthreads();  // the previous step's column reads of xs are done, ymap[cur ^ 1] is free
+#pragma unroll
+        for (int r = 0; r < R; ++r) in[r][tid] = pre[r];
+#pragma unroll
+        for (int j = 0; j < NH; ++j) {
+            const int e = tid + SEP_NT * j;
+            if (e < HW * R) {
+                const int r = e / HW;
+                in[r][SEP_NT + e - r * HW] = preh[j];
+            }
+        }
+        if (tid < R) ymap[cur ^ 1][tid] = map_coord(r0 + R + tid, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
         __syncthreads();
-        if (ymap[xr] >= 0) {
+        if (r0 + R < yend + H) request(ymap[cur ^ 1]);
+        const int* __restrict__ ym = ymap[cur];
+        if (ym[xr] >= 0) {
             float v[4 * NIN];
 #pragma unroll
             for (int j = 0; j < NIN; ++j) {
@@ -101,7 +137,7 @@ __global__ void __launch_bounds__(SEP_NT) sep_xy_kernel(Volume src, SepTaps taps
         for (int i = 0; i < KMAX - 1; ++i) win[i] = win[i + R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const int yl = ymap[r];
+            const int yl = ym[r];
             win[KMAX - 1 + r] = yl >= 0 ? xs[r][tid] : (yl == -1 ? fill_row : 0.f);
         }
         float* __restrict__ op = tmp + ((size_t)za * by + (r0 - H)) * bx + x0 + tid;
@@ -147,35 +183,46 @@ __global__ void __launch_bounds__(SEP_NT) sep_z_kernel(const float* __restrict__
     float* optr = ep.out + ((size_t)(z0 - 2 * H + ep.out_off[2]) * ep.out_dim[1] + (y + ep.out_off[1])) * (size_t)ep.out_dim[0] + ep.out_off[0] + (live ? x : 0);
     const float* iptr = ep.img + ((size_t)(z0 - 2 * H) * ep.aux_dim[1] + y) * (size_t)ep.aux_dim[0] + (live ? x : 0);
     const float* wptr = ep.weight + ((size_t)(z0 - 2 * H) * ep.aux_dim[1] + y) * (size_t)ep.aux_dim[0] + (live ? x : 0);
+    // One step ahead: the U planes of tmp and the epilogue operands of the NEXT step are requested before the
+    // current step's multiply-adds and wait in registers (nxt, an, bn).
+    float nxt[U], an[U], bn[U];
+    auto request = [&](int r0n, const float* op, const float* ip, const float* wp) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int zl = map_coord(r0n + u, src.dim[2], src.off[2], src.gmin[2], src.gdim[2], src.ext);
+            nxt[u] = zl >= 0 ? __ldg(tcol + (size_t)zl * plane) : (zl == -1 ? fill_t : 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int z = r0n + u - H;
+            an[u] = 0.f;
+            bn[u] = ep.weight_const;
+            if (z >= z0 && z < zend && live) {
+                if constexpr (EPI == EPI_QUOTIENT) an[u] = __ldg(ip + u * aplane);
+                if constexpr (EPI == EPI_UPDATE) {
+                    an[u] = op[u * oplane];
+                    if (ep.weight) bn[u] = __ldg(wp + u * aplane);
+                }
+            }
+        }
+    };
+    request(z0 - H, optr, iptr, wptr);
 #pragma unroll 1
     for (int r0 = z0 - H; r0 < zend + H; r0 += U, optr += U * oplane, iptr += U * aplane, wptr += U * aplane) {
 #pragma unroll
         for (int i = 0; i < KMAX - 1; ++i) win[i] = win[i + U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int zl = map_coord(r0 + u, src.dim[2], src.off[2], src.gmin[2], src.gdim[2], src.ext);
-            win[KMAX - 1 + u] = zl >= 0 ? __ldg(tcol + (size_t)zl * plane) : (zl == -1 ? fill_t : 0.f);
-        }
-        // epilogue operands of the U outputs of this step, requested before the arithmetic
-        bool on[U];
         float a[U], b[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const int z = r0 + u - H;
-            on[u] = z >= z0 && z < zend && live;
-            a[u] = 0.f;
-            b[u] = ep.weight_const;
-            if (on[u]) {
-                if constexpr (EPI == EPI_QUOTIENT) a[u] = __ldg(iptr + u * aplane);
-                if constexpr (EPI == EPI_UPDATE) {
-                    a[u] = optr[u * oplane];
-                    if (ep.weight) b[u] = __ldg(wptr + u * aplane);
-                }
-            }
+            win[KMAX - 1 + u] = nxt[u];
+            a[u] = an[u];
+            b[u] = bn[u];
         }
+        if (r0 + U < zend + H) request(r0 + U, optr + U * oplane, iptr + U * aplane, wptr + U * aplane);
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            if (!on[u]) continue;
+            const int z = r0 + u - H;
+            if (!(z >= z0 && z < zend && live)) continue;
             float acc = 0.f;
 #pragma unroll
             for (int i = 0; i < KMAX; ++i) acc = fmaf(taps.z[i], win[u + i], acc);
