@@ -163,7 +163,7 @@ struct mvdContext {
     bool direct_enabled = true;
     float* sep_tmp = nullptr;
     size_t sep_tmp_cap = 0;
-    bool direct_ok() const { return direct_enabled && peers_psi.empty(); }  // the direct kernels do not push ghost layers
+    bool direct_ok() const { return direct_enabled; }
     float* sep_scratch(const Volume& src) {
         const size_t n = sep_tmp_elems(src, bdim);
         if (n > sep_tmp_cap) {

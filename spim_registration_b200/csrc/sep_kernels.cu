@@ -154,15 +154,38 @@ __global__ void __launch_bounds__(SEP_NT) sep_xy_kernel(Volume src, SepTaps taps
     }
 }
 
-template <int KMAX, int EPI>
+// PUSH: fused ghost exchange as in the FFT path's epilogue -- every output voxel a neighbouring brick needs is
+// also stored into that neighbour's ghost layers (PeerTarget, conv_types.h).  A thread owns one (x, y) column,
+// so the neighbours whose x / y range contains it are found once; per voxel only the z range is tested.
+template <int KMAX, int EPI, bool PUSH>
 __global__ void __launch_bounds__(SEP_NT) sep_z_kernel(const float* __restrict__ tmp, Volume src, SepTaps taps, EpilogueArgs ep, int bx,
                                                        int by, int bz) {
     constexpr int H = KMAX / 2, U = SEP_U;
     __shared__ double s_sum[SEP_NT / 32];
     __shared__ float s_max[SEP_NT / 32];
+    __shared__ PeerTarget s_peer[PUSH ? kMaxPeers : 1];
     const int tid = threadIdx.x;
     const int x = blockIdx.x * SEP_NT + tid, y = blockIdx.y, z0 = blockIdx.z * SEP_CHZ;
     const bool live = x < bx;
+    unsigned pmask = 0;
+    if constexpr (PUSH) {
+        for (int i = tid; i < ep.n_peers; i += SEP_NT) s_peer[i] = ep.peers[i];
+        __syncthreads();
+        if (live)
+            for (int i = 0; i < ep.n_peers; ++i) {
+                const PeerTarget& t = s_peer[i];
+                if (x >= t.lo[0] && x < t.hi[0] && y >= t.lo[1] && y < t.hi[1]) pmask |= 1u << i;
+            }
+    }
+    auto push = [&](int z, float val) {
+        if constexpr (PUSH) {
+            for (unsigned m = pmask; m; m &= m - 1) {
+                const PeerTarget& t = s_peer[__ffs(m) - 1];
+                if (z >= t.lo[2] && z < t.hi[2])
+                    t.base[((size_t)(z + t.shift[2]) * t.dim[1] + (y + t.shift[1])) * (size_t)t.dim[0] + (x + t.shift[0])] = val;
+            }
+        }
+    };
     const float fillv = src.ext == EXT_CONST ? src.ext_value : 0.f;
     float sxy = 0.f, sy = 0.f;  // a plane of constant fill convolved in x and y
 #pragma unroll
@@ -229,11 +252,15 @@ __global__ void __launch_bounds__(SEP_NT) sep_z_kernel(const float* __restrict__
             acc += ep.add_const;
             if constexpr (EPI == EPI_STORE) {
                 optr[u * oplane] = acc;
+                push(z, acc);
             } else if constexpr (EPI == EPI_QUOTIENT) {
-                optr[u * oplane] = quotient_value(a[u], acc);
+                const float qv = quotient_value(a[u], acc);
+                optr[u * oplane] = qv;
+                push(z, qv);
             } else {
                 const float nv = next_psi_value(a[u], acc, b[u], use_tik, two_lambda, inv_lambda, ep.min_value);
                 optr[u * oplane] = nv;
+                push(z, nv);
                 const float ch = fabsf(__fsub_rn(nv, a[u]));
                 lsum += (double)ch;
                 lmax = fmaxf(lmax, ch);
@@ -285,12 +312,16 @@ cudaError_t launch_separable(const Volume& src, const int bdim[3], const SepTaps
     const dim3 g1((bx + SEP_NT - 1) / SEP_NT, (by + SEP_CHY - 1) / SEP_CHY, src.dim[2]);
     const dim3 g2((bx + SEP_NT - 1) / SEP_NT, by, (bz + SEP_CHZ - 1) / SEP_CHZ);
     if (g1.y > 65535u || g1.z > 65535u || g2.y > 65535u || g2.z > 65535u) return cudaErrorInvalidValue;
+    const bool push = ep.peers != nullptr && ep.n_peers > 0;
+    if (push && (ep.n_peers > kMaxPeers || epilogue == EPI_STORE)) return cudaErrorInvalidValue;
 #define SEP_LAUNCH(KM)                                                                                                  \
     {                                                                                                                   \
         sep_xy_kernel<KM><<<g1, SEP_NT, 0, st>>>(src, taps, tmp, bx, by);                                               \
-        if (epilogue == EPI_STORE) sep_z_kernel<KM, EPI_STORE><<<g2, SEP_NT, 0, st>>>(tmp, src, taps, ep, bx, by, bz);    \
-        else if (epilogue == EPI_QUOTIENT) sep_z_kernel<KM, EPI_QUOTIENT><<<g2, SEP_NT, 0, st>>>(tmp, src, taps, ep, bx, by, bz); \
-        else sep_z_kernel<KM, EPI_UPDATE><<<g2, SEP_NT, 0, st>>>(tmp, src, taps, ep, bx, by, bz);                        \
+        if (epilogue == EPI_STORE) sep_z_kernel<KM, EPI_STORE, false><<<g2, SEP_NT, 0, st>>>(tmp, src, taps, ep, bx, by, bz); \
+        else if (epilogue == EPI_QUOTIENT && !push) sep_z_kernel<KM, EPI_QUOTIENT, false><<<g2, SEP_NT, 0, st>>>(tmp, src, taps, ep, bx, by, bz); \
+        else if (epilogue == EPI_QUOTIENT) sep_z_kernel<KM, EPI_QUOTIENT, true><<<g2, SEP_NT, 0, st>>>(tmp, src, taps, ep, bx, by, bz); \
+        else if (!push) sep_z_kernel<KM, EPI_UPDATE, false><<<g2, SEP_NT, 0, st>>>(tmp, src, taps, ep, bx, by, bz);      \
+        else sep_z_kernel<KM, EPI_UPDATE, true><<<g2, SEP_NT, 0, st>>>(tmp, src, taps, ep, bx, by, bz);                  \
     }
     if (kmax == 7) SEP_LAUNCH(7)
     else if (kmax == 15) SEP_LAUNCH(15)

@@ -329,8 +329,10 @@ def test_bricks_with_ghost_layers_equal_whole_volume(m, o, grid, shape, fused):
     assert rel_l2(got, ref) <= LOOP_TOL
 
 
-def test_fused_ghost_exchange_is_bit_identical_to_copies(m, o):
-    """Pushing ghost voxels from the epilogue changes where values are stored, not the values."""
+@pytest.mark.parametrize("direct", [0, 1])
+def test_fused_ghost_exchange_is_bit_identical_to_copies(m, o, direct):
+    """Pushing ghost voxels from the epilogue changes where values are stored, not the values -- for the FFT
+    engine (direct = 0) and for the direct separable kernels the Gaussian PSFs of this data set qualify for."""
     from spim_registration_b200 import synthetic
     from spim_registration_b200.parallel import LocalBrickGroup
     shape, V, grid = (37, 50, 150), 2, (2, 2, 2)
@@ -341,8 +343,11 @@ def test_fused_ghost_exchange_is_bit_identical_to_copies(m, o):
     for fused in (False, True):
         grp = LocalBrickGroup(shape[::-1], grid, ds["imgs"], weights, k1, k2, 0.006)
         try:
-            for b in grp.bricks:  # contexts with peers use the FFT engine: compare like with like
-                b.L.check(b.lib.mvdSetDirectPath(b.ctx, 0), "mvdSetDirectPath")
+            for b in grp.bricks:
+                b.L.check(b.lib.mvdSetDirectPath(b.ctx, direct), "mvdSetDirectPath")
+                a_, b_ = C.c_int(), C.c_int()
+                b.L.check(b.lib.mvdViewUsesDirectPath(b.ctx, 0, C.byref(a_), C.byref(b_)), "mvdViewUsesDirectPath")
+                assert bool(a_.value) == bool(direct) and bool(b_.value) == bool(direct)
             grp.init_psi_average()
             if fused:
                 grp.attach_peers()
