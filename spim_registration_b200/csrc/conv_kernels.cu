@@ -90,8 +90,17 @@ template <int BX, int BY> struct XYCfg {
 #ifndef MVD_FWD_MINCTAS
 #define MVD_FWD_MINCTAS 3
 #endif
+#ifndef MVD_FWD_PIPE
+#define MVD_FWD_PIPE 1  // 128 x 128 windows: both row rounds of a plane requested up front (8.59 vs 9.09 ms per 4 convolutions)
+#endif
+// the up-front loads of the 128 x 128 kernel need 126 registers: two CTAs per SM (measured equal to three at 77 registers without them)
+template <int BX, int BY> struct FwdCfg {
+    static constexpr bool PIPE = MVD_FWD_PIPE != 0 && BX == 128 && BY == 2 * (NT / 4);
+    static constexpr int WANT = PIPE ? 2 : MVD_FWD_MINCTAS;
+    static constexpr int MIN_CTAS = XYCfg<BX, BY>::MIN_CTAS < WANT ? XYCfg<BX, BY>::MIN_CTAS : WANT;
+};
 template <int BX, int BY>
-__global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_FWD_MINCTAS ? XYCfg<BX, BY>::MIN_CTAS : MVD_FWD_MINCTAS)) fwd_xy_kernel(Volume src, const Tile* __restrict__ tiles,
+__global__ void __launch_bounds__(NT, FwdCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Volume src, const Tile* __restrict__ tiles,
                                                                            float2* __restrict__ scratch, size_t tile_stride, int bz,
                                                                            int n_items, Twiddles tw) {
     using C = XYCfg<BX, BY>;
@@ -169,9 +178,7 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_FWD_MINCTAS
                 const int xa = xo + 16 * m + 4 * q, xgl = xg + 16 * m + 4 * q;
                 if (al4 && xa >= 0 && xa + 3 < src.dim[0] && xgl >= 0 && xgl + 3 < src.gdim[0]) qmask |= 1u << m;
             }
-#pragma unroll 1
-            for (int row = tid >> 2; row < BY; row += NT / 4) {
-                float2 a[8], b[8];
+            auto load_row = [&](int row, float2 (&a)[8], float2 (&b)[8]) {
                 const int yl = zl < 0 ? zl : map_coord(tile.o[1] + row, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
                 if (yl < 0) {
                     const float f = yl == -1 ? fillv : 0.f;
@@ -198,7 +205,22 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_FWD_MINCTAS
                         }
                     }
                 }
-                row128_forward(a, b, plane + row * P, twr, twu, q, 0xffffffffu);
+            };
+            if constexpr (FwdCfg<BX, BY>::PIPE) {
+                // both row rounds of the plane requested up front: one exposed load latency per plane instead of two
+                float2 a0[8], b0[8], a1[8], b1[8];
+                const int r0 = tid >> 2, r1 = r0 + NT / 4;
+                load_row(r0, a0, b0);
+                load_row(r1, a1, b1);
+                row128_forward(a0, b0, plane + r0 * P, twr, twu, q, 0xffffffffu);
+                row128_forward(a1, b1, plane + r1 * P, twr, twu, q, 0xffffffffu);
+            } else {
+#pragma unroll 1
+                for (int row = tid >> 2; row < BY; row += NT / 4) {
+                    float2 a[8], b[8];
+                    load_row(row, a, b);
+                    row128_forward(a, b, plane + row * P, twr, twu, q, 0xffffffffu);
+                }
             }
         } else {
 #pragma unroll 1
