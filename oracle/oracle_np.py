@@ -21,9 +21,13 @@ reference does (J/fftMethods/FFTConvolution.java:470-551); the convention is TRU
 with the kernel centre at floor(K/2) (FFTConvolution.java:506-516), see SURVEY.md 8c caveat.
 """
 import math
+import os
 
 import numpy as np
+from scipy import fft as sfft
 from scipy import signal
+
+WORKERS = int(os.environ.get("ORACLE_WORKERS", "0")) or (os.cpu_count() or 1)
 
 F32 = np.float32
 MIN_VALUE = F32(0.0001)  # MVDeconvolution.java:49 / MVDeconInput.java:12
@@ -133,7 +137,8 @@ def convolve_extended(f, kernel, mode, value=0.0):
     hr = [s // 2 for s in K]           # reads up to x + K//2
     hl = [s - 1 - s // 2 for s in K]   # and down to x - (K-1-K//2)
     fe = extend(np.asarray(f, dtype=np.float64), hl, hr, mode, value)
-    out = signal.fftconvolve(fe, k, mode="valid")
+    with sfft.set_workers(WORKERS):  # lines are independent: same values for every worker count
+        out = signal.fftconvolve(fe, k, mode="valid")
     assert out.shape == np.asarray(f).shape
     return out.astype(F32)
 
@@ -540,9 +545,12 @@ def compute_final_values(psi, integral, weight, lam, min_value=MIN_VALUE):
     return new, sum_change, max_change
 
 
-def run_deconvolution(imgs, weights, kernel1, kernel2, num_iterations, lam, psi0=None, min_value=MIN_VALUE, conv=None):
+def run_deconvolution(imgs, weights, kernel1, kernel2, num_iterations, lam, psi0=None, min_value=MIN_VALUE, conv=None,
+                      on_iteration=None):
     """MVDeconvolution constructor (MVDeconvolution.java:73-190) given prepared kernels.
-    weights[v]: array or scalar.  Returns (psi, stats[iter][view] = (sum, max), avg)."""
+    weights[v]: array or scalar.  Returns (psi, stats[iter][view] = (sum, max), avg).
+    on_iteration(i, psi) sees the estimate after every iteration (the reference's debug stack,
+    MVDeconvolution.java:139-175), before the final mask."""
     conv = conv or convolve_extended
     V = len(imgs)
     avg, cnt = fuse_first_iteration(imgs)
@@ -562,6 +570,8 @@ def run_deconvolution(imgs, weights, kernel1, kernel2, num_iterations, lam, psi0
             psi, s, m = compute_final_values(psi, t2, weights[v], lam, min_value)  # :405-436
             row.append((s, m))
         stats.append(row)
+        if on_iteration is not None:
+            on_iteration(len(stats) - 1, psi)
     psi = np.where(cnt == 0, F32(0), psi).astype(F32)       # :180-187
     return psi, stats, avg
 

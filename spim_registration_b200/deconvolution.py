@@ -181,7 +181,7 @@ class MVDeconvolution:
     minValue = F32(0.0001)  # MVDeconvolution.java:49
 
     def __init__(self, views, iterationType, numIterations, lam, osemspeedup=1.0, osemspeedupindex=0, name="",
-                 initialImage=None, device=None, numThreads=8, prepared=False, directPath=True):
+                 initialImage=None, device=None, numThreads=8, prepared=False, directPath=True, debug=False, debugInterval=1):
         lib = _lib.load()
         self.views, self.name, self.lam = views, name, float(lam)
         self.data = views.getViews()
@@ -218,7 +218,20 @@ class MVDeconvolution:
                 self.avg = avg.value
             n = numIterations * self.numViews
             s, m = (C.c_double * max(n, 1))(), (C.c_double * max(n, 1))()
-            _lib.check(lib.mvdRunIterations(self._ctx, numIterations, s, m), "mvdRunIterations")
+            # debug mode (MVDeconvolution.java:139-175): a copy of psi every debugInterval iterations, before the final mask
+            self.debugStack = []
+            if debug:
+                for it in range(numIterations):
+                    s1, m1 = (C.c_double * self.numViews)(), (C.c_double * self.numViews)()
+                    _lib.check(lib.mvdRunIterations(self._ctx, 1, s1, m1), "mvdRunIterations")
+                    s[it * self.numViews:(it + 1) * self.numViews] = s1[:]
+                    m[it * self.numViews:(it + 1) * self.numViews] = m1[:]
+                    if it % max(1, debugInterval) == 0:
+                        snap = np.empty(shape, dtype=F32)
+                        _lib.check(lib.mvdGetPsi(self._ctx, snap.ctypes.data_as(C.c_void_p), 0), "mvdGetPsi")
+                        self.debugStack.append((it, snap))
+            else:
+                _lib.check(lib.mvdRunIterations(self._ctx, numIterations, s, m), "mvdRunIterations")
             self.sumChange = np.array(s[:n]).reshape(numIterations, self.numViews)
             self.maxChange = np.array(m[:n]).reshape(numIterations, self.numViews)
             self.i = numIterations

@@ -192,6 +192,19 @@ class ShardedDeconvolution:
         self.L.check(self.lib.mvdFillPsi(self.ctx, avg), "mvdFillPsi")
         return avg
 
+    def set_psi(self, brick):
+        """mvdSetPsi for this rank's brick ([z,y,x] numpy or CUDA tensor) followed by a real ghost exchange: in
+        fused mode `_exchange` is only a barrier (the step kernels fill the ghosts), so a psi that did not come
+        from a step has to be sent explicitly."""
+        is_dev = hasattr(brick, "data_ptr")
+        ptr = C.c_void_p(brick.data_ptr()) if is_dev else np.ascontiguousarray(brick, dtype=np.float32).ctypes.data_as(C.c_void_p)
+        self.L.check(self.lib.mvdSetPsi(self.ctx, ptr, 1 if is_dev else 0), "mvdSetPsi")
+        if self.world > 1:
+            t, off = self._arrays[0]
+            exchange_ghosts(t, off, self.size[::-1], self.ghost, self.coords, self.grid, self.dist)
+            if self.fused:
+                self.dist.all_reduce(self._flag)
+
     def _exchange(self, which):
         if self.world == 1:
             return
