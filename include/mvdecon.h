@@ -278,6 +278,12 @@ long long mvdDivideIntoBlocks(const long long* imgSize, const long long* kernelS
 /* Counters for bench.py: kernels launched by this library in the calling process. */
 long long mvdKernelLaunchCount(void);
 
+/* Process-wide switches between kernel generations, for A/B measurements and tests (defaults: the faster one).
+ *   "z_tma"   1 = z pass with TMA bulk-tensor loads / stores (z_tma_kernels.cu), 0 = register-loading z pass
+ *   "inv_tma" 1 = inverse xy pass fed by bulk copies into a shared-memory ring, 0 = register-loading kernel
+ * Returns the previous value, or -1 for an unknown name. */
+int mvdSetTuning(const char* name, int value);
+
 #ifdef __cplusplus
 }
 #endif

@@ -606,14 +606,23 @@ def divide_into_blocks(img_size, kernel_size, block_size):
 
 # Block.copyBlock (Block.java:114-153, 233-271): block[p] = extended_source(p + offset)
 def copy_block(source, block, mode, value=0.0):
+    """Block.copyBlock (Block.java:114-153, 233-271): block[x] = extended_source(x + offset) for the B^3 block.
+    Reads the block's part of the volume only, like the reference -- the out-of-bounds rule is applied to the faces
+    of that part that lie on the volume border (whole-volume padding only for volumes thinner than the halo)."""
     src = np.asarray(source, dtype=F32)
     bs, off = block["blockSize"], block["offset"]
     n = src.shape[::-1]  # (x,y,z)
     lo = [max(0, -off[d]) for d in range(3)]
     hi = [max(0, off[d] + bs[d] - n[d]) for d in range(3)]
-    ext = extend(src, lo[::-1], hi[::-1], mode, value)
-    s = [off[d] + lo[d] for d in range(3)]
-    return np.ascontiguousarray(ext[s[2]:s[2] + bs[2], s[1]:s[1] + bs[1], s[0]:s[0] + bs[0]]).astype(F32)
+    s = [max(0, off[d]) for d in range(3)]
+    e = [min(n[d], off[d] + bs[d]) for d in range(3)]
+    small = any(e[d] - s[d] <= max(lo[d], hi[d]) or e[d] <= s[d] for d in range(3))
+    if small:
+        ext = extend(src, lo[::-1], hi[::-1], mode, value)
+        t = [off[d] + lo[d] for d in range(3)]
+        return np.ascontiguousarray(ext[t[2]:t[2] + bs[2], t[1]:t[1] + bs[1], t[0]:t[0] + bs[0]]).astype(F32)
+    sub = src[s[2]:e[2], s[1]:e[1], s[0]:e[0]]  # clipped exactly at the volume faces the block crosses
+    return np.ascontiguousarray(extend(sub, lo[::-1], hi[::-1], mode, value)).astype(F32)
 
 
 # Block.pasteBlock (Block.java:155-195, 313-359)

@@ -71,6 +71,7 @@ PROTOTYPES = {
     "mvdPlanTiles": (C.c_int, [c_int_p, c_int_p, c_int_p, C.c_int]),
     "mvdDivideIntoBlocks": (C.c_longlong, [c_ll_p, c_ll_p, c_ll_p, C.c_int, c_ll_p, C.c_longlong]),
     "mvdKernelLaunchCount": (C.c_longlong, []),
+    "mvdSetTuning": (C.c_int, [C.c_char_p, C.c_int]),
 }
 
 _lib = None

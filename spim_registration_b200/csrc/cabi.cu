@@ -89,6 +89,11 @@ extern "C" int mvdGetLastError(char* buf, int n) {
 
 extern "C" const char* mvdVersion(void) { return "mvdecon-b200 0.1 sm_100a (tiled overlap-save FFT, fused epilogues)"; }
 extern "C" long long mvdKernelLaunchCount(void) { return g_kernel_launches.load(); }
+extern "C" int mvdSetTuning(const char* name, int value) {
+    if (!name) return -1;
+    if (std::strcmp(name, "z_tma") == 0) return g_use_z_tma.exchange(value);
+    return -1;
+}
 
 // ---- context -------------------------------------------------------------------------------
 struct ViewData {

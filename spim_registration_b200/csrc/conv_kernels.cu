@@ -21,6 +21,7 @@
 #include "conv_kernels.h"
 #include "fft_device.cuh"
 #include "row128.cuh"
+#include "z_items.cuh"
 #include "device_common.cuh"
 
 #include <algorithm>
@@ -367,21 +368,6 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // Work item -> (position block, tile).  Tiles run fastest so that the CTAs in flight read the same part of
 // the kernel spectrum; with MVD_Z_PGROUP = G > 1, G neighbouring position blocks (G * PW * 8 contiguous
 // bytes per z index) run fastest of all, so that CTAs in flight also share DRAM pages.
-#ifndef MVD_Z_PGROUP
-#define MVD_Z_PGROUP 4  // measured (cfg3 class, 4 convolutions): 1 -> 11.14 ms, 4 -> 10.88, 8 -> 10.93, 16 -> 11.03
-#endif
-__device__ __forceinline__ void decode_item(int item, int n_tiles, int& pblk, int& ti) {
-    if constexpr (MVD_Z_PGROUP > 1) {
-        const int per_group = MVD_Z_PGROUP * n_tiles;
-        const int g = item / per_group, r = item - g * per_group;
-        ti = r / MVD_Z_PGROUP;
-        pblk = g * MVD_Z_PGROUP + (r - ti * MVD_Z_PGROUP);
-    } else {
-        pblk = item / n_tiles;
-        ti = item - pblk * n_tiles;
-    }
-}
-
 template <int BZ, int MODE>
 __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_kernel(float2* __restrict__ scratch, size_t tile_stride,
                                                                                      const float2* __restrict__ kspec,
@@ -612,7 +598,7 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
     const int cu = tid / CPR;
     const ConstTw128 twc{7 - ilog2<BY>()};
     const bool use_tik = ep.lambda > 0.0;
-    const double two_lambda = 2.0 * ep.lambda, inv_lambda = use_tik ? 1.0 / ep.lambda : 0.0;
+    const TikhonovConst tik = make_tikhonov(ep.lambda);
     double lsum = 0.0;
     float lmax = 0.f;
     __syncthreads();
@@ -766,7 +752,7 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
                                 if constexpr (EPI == EPI_STORE) r[i] = c[i];
                                 else if constexpr (EPI == EPI_QUOTIENT) r[i] = quotient_value(av[i], c[i]);
                                 else {
-                                    r[i] = next_psi_value(av[i], c[i], bv[i], use_tik, two_lambda, inv_lambda, ep.min_value);
+                                    r[i] = next_psi_value(av[i], c[i], bv[i], use_tik, tik, ep.min_value);
                                     const float ch = fabsf(__fsub_rn(r[i], av[i]));
                                     rsum += ch;
                                     lmax = fmaxf(lmax, ch);  // fmaxf drops NaN
@@ -810,7 +796,7 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
                             } else {
                                 const float last = ep.out[idx];
                                 const float w = ep.weight ? __ldg(ep.weight + aidx) : ep.weight_const;
-                                nv = next_psi_value(last, c[i], w, use_tik, two_lambda, inv_lambda, ep.min_value);
+                                nv = next_psi_value(last, c[i], w, use_tik, tik, ep.min_value);
                                 const float ch = fabsf(__fsub_rn(nv, last));
                                 rsum += ch;
                                 lmax = fmaxf(lmax, ch);
@@ -884,8 +870,8 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
                         if constexpr (EPI == EPI_STORE) r = make_float2(c0, c1);
                         else if constexpr (EPI == EPI_QUOTIENT) r = make_float2(quotient_value(a[m].x, c0), quotient_value(a[m].y, c1));
                         else {
-                            r.x = next_psi_value(a[m].x, c0, b[m].x, use_tik, two_lambda, inv_lambda, ep.min_value);
-                            r.y = next_psi_value(a[m].y, c1, b[m].y, use_tik, two_lambda, inv_lambda, ep.min_value);
+                            r.x = next_psi_value(a[m].x, c0, b[m].x, use_tik, tik, ep.min_value);
+                            r.y = next_psi_value(a[m].y, c1, b[m].y, use_tik, tik, ep.min_value);
                             const float ch0 = fabsf(__fsub_rn(r.x, a[m].x)), ch1 = fabsf(__fsub_rn(r.y, a[m].y));
                             lsum += (double)(ch0 + ch1);
                             lmax = fmaxf(lmax, fmaxf(ch0, ch1));  // fmaxf drops NaN
@@ -920,7 +906,7 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
                         } else {
                             const float last = ep.out[idx];
                             const float w = ep.weight ? __ldg(ep.weight + aidx) : ep.weight_const;
-                            nv = next_psi_value(last, c[q], w, use_tik, two_lambda, inv_lambda, ep.min_value);
+                            nv = next_psi_value(last, c[q], w, use_tik, tik, ep.min_value);
                             const float ch = fabsf(__fsub_rn(nv, last));
                             lsum += (double)ch;
                             lmax = fmaxf(lmax, ch);

@@ -24,6 +24,12 @@ cudaError_t launch_z_pass(int bx, int by, int bz, int mode, float2* scratch, con
                           float scale, const TwiddleTables& tw, cudaStream_t st);
 cudaError_t launch_inv_xy(int bx, int by, int bz, int epilogue, const float2* scratch, const Tile* d_tiles, int n_tiles, int max_nz,
                           const EpilogueArgs& ep, const TwiddleTables& tw, cudaStream_t st);
+// z pass with TMA data movement (z_tma_kernels.cu): bulk tensor loads / stores of whole work items, two thread groups and
+// three shared-memory slots per CTA.  mode 1 only; bz in {128, 256, 512}.
+bool z_tma_supported(int bz);
+cudaError_t configure_z_tma_kernels();
+cudaError_t launch_z_pass_tma(int bx, int by, int bz, float2* scratch, const float2* kspec, int n_tiles, int zlo, int max_nz, int num_sms,
+                              const TwiddleTables& tw, cudaStream_t st);
 void set_grid_caps(int xy_cap, int z_cap);  // persistent-grid sizes, 0 = one CTA per work item
 cudaError_t configure_conv_kernels();  // opt in to > 48 KB dynamic shared memory
 

@@ -11,6 +11,11 @@
 namespace mvd {
 
 std::atomic<long long> g_kernel_launches{0};
+static int env_flag(const char* name, int dflt) {
+    const char* s = std::getenv(name);
+    return s ? std::atoi(s) : dflt;
+}
+std::atomic<int> g_use_z_tma{env_flag("MVD_Z_TMA", 0)};
 
 void cuda_check(cudaError_t e, const char* what) {
     if (e != cudaSuccess) throw CudaError(std::string(what) + ": " + cudaGetErrorString(e));
@@ -167,6 +172,7 @@ Device::Device(int id) : id_(id) {
         throw CudaError(std::string("libmvdecon is built for sm_100a (B200); device '") + prop.name + "' is sm_" +
                         std::to_string(prop.major) + std::to_string(prop.minor));
     MVD_CUDA(configure_conv_kernels());
+    MVD_CUDA(configure_z_tma_kernels());
     const double two_pi = 6.283185307179586476925286766559;
     for (int l = 0; l < 11; ++l) {
         const int n = 1 << l;
@@ -401,7 +407,11 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
             if (prof) prof->begin(0, cnt * ((double)bx * by * bz * 4.0 + pe * bz * 8.0), ls);
             MVD_CUDA(launch_fwd_xy(bx, by, bz, src, c.d_tiles + s, cnt, buf, dev.twiddles(), ls));
             if (prof) { prof->end(ls); prof->begin(1, cnt * pe * bz * 8.0 + pe * bz * 8.0 + nz_sum * pe * 8.0, ls); }
-            MVD_CUDA(launch_z_pass(bx, by, bz, 1, buf, spec.per_class[ci], c.d_tiles + s, cnt, 1.f, dev.twiddles(), ls));
+            if (g_use_z_tma.load() && z_tma_supported(bz))
+                MVD_CUDA(launch_z_pass_tma(bx, by, bz, buf, spec.per_class[ci], cnt, c.tiles[s].e[2] - c.tiles[s].o[2], c.max_nz, dev.sm_count(),
+                                           dev.twiddles(), ls));
+            else
+                MVD_CUDA(launch_z_pass(bx, by, bz, 1, buf, spec.per_class[ci], c.d_tiles + s, cnt, 1.f, dev.twiddles(), ls));
             if (prof) { prof->end(ls); prof->begin(2, nz_sum * pe * 8.0 + out_vox * epi_bytes, ls); }
             if (ep.n_peers > 0 && c.n_interior >= 0) {
                 // interior tiles with the plain epilogue, tiles at the brick faces with the one that also

@@ -21,6 +21,8 @@ void cuda_check(cudaError_t e, const char* what);
 #define MVD_CUDA(x) ::mvd::cuda_check((x), #x)
 
 extern std::atomic<long long> g_kernel_launches;
+// run-time switches between kernel generations (A/B measurements; mvdSetTuning / environment MVD_Z_TMA, MVD_INV_TMA)
+extern std::atomic<int> g_use_z_tma;
 
 // ---- planner ---------------------------------------------------------------------------
 struct AxisTile {

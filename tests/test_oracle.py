@@ -408,3 +408,87 @@ def test_cpu_baseline_port_matches_oracle():
     assert seconds > 0
     err = np.linalg.norm(got.astype(np.float64) - ref) / np.linalg.norm(ref.astype(np.float64))
     assert err <= 1e-4
+
+
+# ---- the second, independent restatement (oracle/cpu_ref.cpp): the reference's own FFT route in float32 --------------
+def _cpu_ref():
+    import cpu_ref
+    cpu_ref.load()
+    return cpu_ref
+
+
+def test_prime_factor_sizes_of_the_fft_padding():
+    """Valid Mines-JTK lengths are products of mutually prime factors from {2,3,4,5,7,8,9,11,13,16}
+    (FFTMethods.java:1279-1291 pads every dimension to one of them; x to an even one)."""
+    lib = _cpu_ref().load()
+    assert [lib.ref_nfft_small_complex(n) for n in (1, 17, 32, 33, 142, 286, 287)] == [1, 18, 33, 33, 143, 286, 308]
+    assert lib.ref_nfft_small_complex(32) == 33          # 32 = 2^5 is not valid: the largest power of two is 16
+    assert [lib.ref_nfft_small_real(n) for n in (142, 286, 45)] == [144, 286, 48]
+
+
+@pytest.mark.parametrize("shape,ks", [((12, 14, 17), (3, 5, 7)), ((20, 9, 11), (4, 6, 5)), ((6, 7, 8), (9, 9, 9))])
+@pytest.mark.parametrize("mode", ["zero", "const", "mirror"])
+def test_fft_route_without_conjugate_is_the_convolution_formula(shape, ks, mode):
+    """Restating FFTConvolution.convolve (pad, rotate the kernel to its centre K/2, multiply, crop) WITHOUT the complex
+    conjugate reproduces conv(ext(f), k)(x) = sum_j ext(f)(x + K/2 - j) k(j) -- the formula oracle_np.py evaluates in
+    float64 and the brute-force sum -- for all three out-of-bounds rules, odd and even kernels."""
+    cr = _cpu_ref()
+    rng = np.random.default_rng(5)
+    f = rng.random(shape, dtype=np.float32) + np.float32(0.1)
+    k = rng.random(ks, dtype=np.float32)
+    got, pad = cr.fft_convolve(f, k, mode, 0.7, conjugate=False)
+    assert all(p >= n + q - 1 for p, n, q in zip(pad, shape[::-1], ks[::-1]))
+    assert rel_l2(got, o.convolve_extended(f, k, mode, 0.7)) <= 2e-6
+    assert rel_l2(got, o.convolve_direct(f, k, mode, 0.7)) <= 2e-6
+
+
+def test_conjugate_switch_is_correlation_and_which_setting_the_path_needs():
+    """The vendored copy defaults complexConjugate = true (J/fftMethods/FFTConvolution.java:95, :528-531).  With the
+    kernel spectrum conjugated the same route computes the CORRELATION sum_j ext(f)(x - K/2 + j) k(j), i.e. the
+    convolution with the kernel mirrored about its centre.  Which setting the deconvolution path needs follows from
+    the reference's own construction: PSFs are averaged bead IMAGES (ExtractPSF.java:353-394), so an observed view is
+    conv(truth, psf) in image orientation; conv1 must reproduce it and conv2 uses the explicitly mirrored kernel
+    (computeInvertedKernel, MVDeconFFT.java:315-323).  Only without the conjugate is the truth a fixed point of the
+    iteration for an asymmetric PSF; with it the estimate drifts away."""
+    cr = _cpu_ref()
+    rng = np.random.default_rng(6)
+    f = rng.random((10, 12, 14), dtype=np.float32)
+    k = rng.random((5, 3, 7), dtype=np.float32)
+    corr, _ = cr.fft_convolve(f, k, "zero", conjugate=True)
+    flipped = np.ascontiguousarray(k[::-1, ::-1, ::-1])
+    assert rel_l2(corr, o.convolve_extended(f, flipped, "zero")) <= 2e-6
+    assert rel_l2(corr, o.convolve_extended(f, k, "zero")) > 0.05
+    # fixed point: img = physical blur of the truth by an asymmetric PSF (a one-sided tail along x)
+    shape = (18, 20, 22)
+    truth = (rng.random(shape, dtype=np.float32) + np.float32(0.5))
+    psf = np.zeros((5, 5, 5), np.float32)
+    psf[2, 2, 2:] = (0.5, 0.3, 0.2)
+    img = o.convolve_direct(truth, psf, "mirror")
+    k1 = [psf]
+    k2 = [o.compute_inverted_kernel(psf)]
+    drift = {}
+    for conj in (False, True):
+        psi, _ = cr.run_deconvolution([img], [np.float32(1.0)], k1, k2, 3, 0.0, truth, conjugate=conj)
+        inner = (slice(4, -4),) * 3   # away from the border, where ext(q) = 1 differs from the interior anyway
+        drift[conj] = rel_l2(psi[inner], truth[inner])
+    assert drift[False] <= 5e-6
+    assert drift[True] > 1e-2
+
+
+def test_cpp_loop_equals_numpy_oracle():
+    """Two independent restatements of the loop (float32 prime-factor-padded FFT route in C++ vs float64 formula in
+    numpy) agree to float rounding over several iterations, statistics included."""
+    cr = _cpu_ref()
+    from spim_registration_b200 import synthetic
+    shape, V, iters = (20, 24, 28), 3, 4
+    ds = synthetic.make_dataset(shape, V, (7, 7, 7), convolve=lambda a, b: o.convolve_extended(a, b, "mirror"))
+    k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
+    weights = synthetic.blending_weights(shape, V)
+    ref, stats, avg = o.run_deconvolution(ds["imgs"], weights, k1, k2, iters, 0.006)
+    psi0 = np.full(shape, np.float32(avg), np.float32)
+    got, gstats = cr.run_deconvolution(ds["imgs"], weights, k1, k2, iters, 0.006, psi0)
+    cnt = sum((np.asarray(i) > 0) for i in ds["imgs"])
+    got = np.where(cnt == 0, np.float32(0), got)
+    assert rel_l2(got, ref) <= 2e-6
+    np.testing.assert_allclose(np.array(gstats)[:, :, 0], np.array([[s for s, _ in r] for r in stats]), rtol=2e-5)
+    np.testing.assert_allclose(np.array(gstats)[:, :, 1], np.array([[m for _, m in r] for r in stats]), rtol=1e-4)
