@@ -90,6 +90,9 @@ const char* mvdVersion(void);
 #define MVD_MEM_HOST 0
 #define MVD_MEM_DEVICE 1
 #define MVD_MEM_HOST_IMG_DEVICE_WEIGHT 2 /* mvdAddView only: img on the host, weight evaluated on the device (mvdVirtualWeight) */
+#define MVD_MEM_HOST_ASYNC 3 /* mvdAddView only: host arrays (pinned for a real overlap) that the caller keeps alive until the next
+                              * mvdSynchronize / mvdRunIterations / mvdInitPsiAverage returns: the call does not wait for the upload, the
+                              * first step that reads the view does (on the device) */
 
 /* Create a context on CUDA device `device` for one brick of the deconvolved volume.
  *   globalDim   (x,y,z) size of the whole deconvolved volume psi.
@@ -251,6 +254,32 @@ int mvdTransformPSF(int device, const float* psf, const int psfDim[3], const dou
 
 /* psi = 0 where no view has data (MVDeconvolution.java:180-187). */
 int mvdMaskNeverUpdated(mvdContext* ctx);
+
+/* ---- several devices behind one handle, one process -------------------------------------------------------------
+ * The reference drives N devices from one JVM, one Java thread per device pulling blocks through host RAM
+ * (MVDeconFFT.java:426-445, MVDeconFFTThreads.java:96-134).  mvdMulti keeps the same calling pattern -- one handle,
+ * one process, no torch / NCCL -- but shards the resident state: the volume is cut into one brick per device
+ * (power-of-two device count; longest axis first), every brick with ghost layers of the kernel half-width, and the
+ * step kernels store ghost voxels straight into the neighbouring devices' arrays (peer access over NVLink).  A
+ * worker thread per device issues its launches; between two steps a device waits only for the events of its
+ * neighbours.  `devices` may name a device several times (bricks then share it).
+ *   maxKernelDim  largest extent per axis of any kernel1 / kernel2 that will be added (sizes the ghost layers)
+ *   img / weight of mvdMultiAddView and psi of mvdMultiSetPsi / mvdMultiGetPsi are WHOLE-VOLUME host arrays
+ *   (x fastest, extent globalDim); statistics are summed / maximised over the bricks. */
+typedef struct mvdMulti mvdMulti;
+int mvdCreateMulti(mvdMulti** multi, const int* devices, int numDevices, const int globalDim[3], const int maxKernelDim[3],
+                   double lambda, float minValue);
+int mvdDestroyMulti(mvdMulti* multi);
+int mvdMultiNumBricks(mvdMulti* multi);
+int mvdMultiBrickInfo(mvdMulti* multi, int brick, int* device, int offset[3], int dim[3]);
+int mvdMultiAddView(mvdMulti* multi, const float* img, const float* weight, float weightConst, const float* kernel1,
+                    const int kernel1Dim[3], const float* kernel2, const int kernel2Dim[3]);
+int mvdMultiSetDirectPath(mvdMulti* multi, int enable);
+int mvdMultiInitPsiAverage(mvdMulti* multi, double* avg);
+int mvdMultiSetPsi(mvdMulti* multi, const float* psi);
+int mvdMultiRunIterations(mvdMulti* multi, int numIterations, double* sumChange, double* maxChange);
+int mvdMultiMaskNeverUpdated(mvdMulti* multi);
+int mvdMultiGetPsi(mvdMulti* multi, float* psi);
 
 /* Stand-alone resident convolution with the engine used by the loop: out = conv(ext(src), kernel)
  * restricted to the volume, src/out dim (x,y,z) host arrays.  extMode 0 zero, 1 constant

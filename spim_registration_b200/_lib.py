@@ -72,6 +72,17 @@ PROTOTYPES = {
     "mvdDivideIntoBlocks": (C.c_longlong, [c_ll_p, c_ll_p, c_ll_p, C.c_int, c_ll_p, C.c_longlong]),
     "mvdKernelLaunchCount": (C.c_longlong, []),
     "mvdSetTuning": (C.c_int, [C.c_char_p, C.c_int]),
+    "mvdCreateMulti": (C.c_int, [C.POINTER(C.c_void_p), c_int_p, C.c_int, c_int_p, c_int_p, C.c_double, C.c_float]),
+    "mvdDestroyMulti": (C.c_int, [C.c_void_p]),
+    "mvdMultiNumBricks": (C.c_int, [C.c_void_p]),
+    "mvdMultiBrickInfo": (C.c_int, [C.c_void_p, C.c_int, c_int_p, c_int_p, c_int_p]),
+    "mvdMultiAddView": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, c_float_p, c_int_p, c_float_p, c_int_p]),
+    "mvdMultiSetDirectPath": (C.c_int, [C.c_void_p, C.c_int]),
+    "mvdMultiInitPsiAverage": (C.c_int, [C.c_void_p, c_double_p]),
+    "mvdMultiSetPsi": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "mvdMultiRunIterations": (C.c_int, [C.c_void_p, C.c_int, c_double_p, c_double_p]),
+    "mvdMultiMaskNeverUpdated": (C.c_int, [C.c_void_p]),
+    "mvdMultiGetPsi": (C.c_int, [C.c_void_p, C.c_void_p]),
 }
 
 _lib = None

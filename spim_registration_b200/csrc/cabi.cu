@@ -2,6 +2,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <array>
 #include <cstring>
 #include <algorithm>
 #include <limits>
@@ -92,14 +93,46 @@ extern "C" long long mvdKernelLaunchCount(void) { return g_kernel_launches.load(
 extern "C" int mvdSetTuning(const char* name, int value) {
     if (!name) return -1;
     if (std::strcmp(name, "z_tma") == 0) return g_use_z_tma.exchange(value);
+    if (std::strcmp(name, "inv_ring") == 0) return g_use_inv_ring.exchange(value);
     return -1;
 }
 
 // ---- context -------------------------------------------------------------------------------
+// device allocation owned by its holder (a view that fails half way through mvdAddView leaks nothing)
+struct DevMem {
+    float* p = nullptr;
+    DevMem() = default;
+    DevMem(const DevMem&) = delete;
+    DevMem& operator=(const DevMem&) = delete;
+    DevMem(DevMem&& o) noexcept : p(o.p) { o.p = nullptr; }
+    DevMem& operator=(DevMem&& o) noexcept {
+        if (this != &o) { reset(); p = o.p; o.p = nullptr; }
+        return *this;
+    }
+    ~DevMem() { reset(); }
+    void reset() { if (p) cudaFree(p); p = nullptr; }
+    void alloc(size_t bytes) { reset(); MVD_CUDA(cudaMalloc(&p, bytes)); }
+    operator float*() const { return p; }
+};
+
 struct ViewData {
-    float* img = nullptr;
-    float* weight = nullptr;
+    DevMem img;
+    DevMem weight;
     float weight_const = 1.f;
+    // upload of img / weight on the context's copy stream; the first step that touches the view waits for it
+    cudaEvent_t ready = nullptr;
+    bool ready_pending = false;
+    ViewData() = default;
+    ViewData(ViewData&& o) noexcept { *this = std::move(o); }
+    ViewData& operator=(ViewData&& o) noexcept {
+        img = std::move(o.img); weight = std::move(o.weight); weight_const = o.weight_const;
+        if (ready) cudaEventDestroy(ready);
+        ready = o.ready; o.ready = nullptr; ready_pending = o.ready_pending;
+        plan1 = o.plan1; plan2 = o.plan2; spec1 = std::move(o.spec1); spec2 = std::move(o.spec2);
+        sep_kmax1 = o.sep_kmax1; sep_kmax2 = o.sep_kmax2; taps1 = o.taps1; taps2 = o.taps2;
+        return *this;
+    }
+    ~ViewData() { if (ready) cudaEventDestroy(ready); }
     int plan1 = -1, plan2 = -1;
     std::unique_ptr<KernelSpectra> spec1, spec2;
     // direct path: kernel i is rank-1 separable and at most 31 wide (sep_kernels.cu)
@@ -147,6 +180,7 @@ struct mvdContext {
     float min_value = 1e-4f;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    cudaStream_t copy_stream = nullptr;  // uploads of mvdAddView (created on first use)
     float* psi = nullptr;
     float* quot = nullptr;
     std::vector<ViewData> views;
@@ -331,10 +365,7 @@ extern "C" int mvdDestroy(mvdContext* c) {
     return guarded([&] {
         cudaSetDevice(c->device);
         if (c->stream) cudaStreamSynchronize(c->stream);
-        for (auto& v : c->views) {
-            if (v.img) cudaFree(v.img);
-            if (v.weight) cudaFree(v.weight);
-        }
+        if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); c->copy_stream = nullptr; }
         c->views.clear();
         c->plans.clear();
         c->prof.reset();
@@ -371,45 +402,86 @@ extern "C" int mvdSynchronize(mvdContext* c) {
 }
 
 // ---- views ---------------------------------------------------------------------------------
+// `volDim` / `volOff` (both or neither): img and weight are x-fastest host volumes of extent volDim and the brick
+// sits at volOff inside them (the single-process multi-device API uploads bricks straight from the caller's
+// whole-volume arrays); otherwise they are dense brick-sized arrays.
+static void add_view(mvdContext* c, const float* img, const float* weight, float weightConst, const float* kernel1, const int k1[3],
+                     const float* kernel2, const int k2[3], int memKind, const int* volDim, const int* volOff, int* viewIndex) {
+    require(c && img && kernel1 && kernel2 && k1 && k2, "mvdAddView: null argument");
+    require((int)c->views.size() < kMaxViews, "mvdAddView: too many views");
+    c->activate();
+    for (int d = 0; d < 3; ++d) {
+        const int need1 = k1[d] - 1 - k1[d] / 2, need2 = k2[d] - 1 - k2[d] / 2;
+        const bool lo_nb = c->boff[d] > 0, hi_nb = c->boff[d] + c->bdim[d] < c->gdim[d];
+        if (lo_nb) require(c->glo[d] >= std::max(k1[d] / 2, need1) && c->glo[d] >= std::max(k2[d] / 2, need2),
+                           "mvdAddView: ghost layer narrower than the kernel halo");
+        if (hi_nb) require(c->ghi[d] >= std::max(k1[d] / 2, need1) && c->ghi[d] >= std::max(k2[d] / 2, need2),
+                           "mvdAddView: ghost layer narrower than the kernel halo");
+    }
+    require(memKind == MVD_MEM_HOST || memKind == MVD_MEM_DEVICE || memKind == MVD_MEM_HOST_IMG_DEVICE_WEIGHT || memKind == MVD_MEM_HOST_ASYNC,
+            "mvdAddView: bad memKind");
+    require(!volDim || memKind == MVD_MEM_HOST || memKind == MVD_MEM_HOST_ASYNC, "mvdAddView: volume slices are host arrays");
+    const cudaMemcpyKind kind = memKind == MVD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    const cudaMemcpyKind wkind = (memKind == MVD_MEM_HOST || memKind == MVD_MEM_HOST_ASYNC) ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+    if (!c->copy_stream) MVD_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    ViewData v;
+    const size_t bytes = c->brick_elems() * sizeof(float);
+    auto upload = [&](float* dst, const float* src, cudaMemcpyKind k) {
+        if (!volDim) {
+            MVD_CUDA(cudaMemcpyAsync(dst, src, bytes, k, c->copy_stream));
+            return;
+        }
+        cudaMemcpy3DParms p;
+        std::memset(&p, 0, sizeof(p));
+        p.srcPtr = make_cudaPitchedPtr(const_cast<float*>(src), (size_t)volDim[0] * sizeof(float), volDim[0], volDim[1]);
+        p.srcPos = make_cudaPos((size_t)volOff[0] * sizeof(float), volOff[1], volOff[2]);
+        p.dstPtr = make_cudaPitchedPtr(dst, (size_t)c->bdim[0] * sizeof(float), c->bdim[0], c->bdim[1]);
+        p.dstPos = make_cudaPos(0, 0, 0);
+        p.extent = make_cudaExtent((size_t)c->bdim[0] * sizeof(float), c->bdim[1], c->bdim[2]);
+        p.kind = k;
+        MVD_CUDA(cudaMemcpy3DAsync(&p, c->copy_stream));
+    };
+    v.img.alloc(bytes);
+    upload(v.img, img, kind);
+    if (weight) {
+        v.weight.alloc(bytes);
+        upload(v.weight, weight, wkind);
+    }
+    MVD_CUDA(cudaEventCreateWithFlags(&v.ready, cudaEventDisableTiming));
+    MVD_CUDA(cudaEventRecord(v.ready, c->copy_stream));
+    v.ready_pending = true;
+    v.weight_const = weightConst;
+    v.plan1 = c->plan_for(k1);
+    v.plan2 = c->plan_for(k2);
+    {   // on a stream of their own: the spectra are built while the image and the weights upload
+        StreamGuard aux;
+        v.spec1 = build_spectra(*c->dev, *c->plans[v.plan1], kernel1, aux.st);
+        v.spec2 = build_spectra(*c->dev, *c->plans[v.plan2], kernel2, aux.st);
+    }
+    v.sep_kmax1 = separate_kernel(kernel1, k1, v.taps1);
+    v.sep_kmax2 = separate_kernel(kernel2, k2, v.taps2);
+    // MVD_MEM_HOST_ASYNC: the caller keeps img / weight alive until the next mvdSynchronize / mvdRunIterations returns, so the
+    // upload of this view overlaps the caller's next calls (and the first steps of the loop); otherwise the buffers may go
+    // away after return
+    if (memKind != MVD_MEM_HOST_ASYNC) MVD_CUDA(cudaStreamSynchronize(c->copy_stream));
+    c->views.push_back(std::move(v));
+    if (viewIndex) *viewIndex = (int)c->views.size() - 1;
+}
+
 extern "C" int mvdAddView(mvdContext* c, const float* img, const float* weight, float weightConst, const float* kernel1,
                           const int k1[3], const float* kernel2, const int k2[3], int memKind, int* viewIndex) {
-    return guarded([&] {
-        require(c && img && kernel1 && kernel2 && k1 && k2, "mvdAddView: null argument");
-        require((int)c->views.size() < kMaxViews, "mvdAddView: too many views");
-        c->activate();
-        for (int d = 0; d < 3; ++d) {
-            const int need1 = k1[d] - 1 - k1[d] / 2, need2 = k2[d] - 1 - k2[d] / 2;
-            const bool lo_nb = c->boff[d] > 0, hi_nb = c->boff[d] + c->bdim[d] < c->gdim[d];
-            if (lo_nb) require(c->glo[d] >= std::max(k1[d] / 2, need1) && c->glo[d] >= std::max(k2[d] / 2, need2),
-                               "mvdAddView: ghost layer narrower than the kernel halo");
-            if (hi_nb) require(c->ghi[d] >= std::max(k1[d] / 2, need1) && c->ghi[d] >= std::max(k2[d] / 2, need2),
-                               "mvdAddView: ghost layer narrower than the kernel halo");
-        }
-        require(memKind == MVD_MEM_HOST || memKind == MVD_MEM_DEVICE || memKind == MVD_MEM_HOST_IMG_DEVICE_WEIGHT, "mvdAddView: bad memKind");
-        const cudaMemcpyKind kind = memKind == MVD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-        const cudaMemcpyKind wkind = memKind == MVD_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
-        ViewData v;
-        const size_t bytes = c->brick_elems() * sizeof(float);
-        MVD_CUDA(cudaMalloc(&v.img, bytes));
-        MVD_CUDA(cudaMemcpyAsync(v.img, img, bytes, kind, c->stream));
-        if (weight) {
-            MVD_CUDA(cudaMalloc(&v.weight, bytes));
-            MVD_CUDA(cudaMemcpyAsync(v.weight, weight, bytes, wkind, c->stream));
-        }
-        v.weight_const = weightConst;
-        v.plan1 = c->plan_for(k1);
-        v.plan2 = c->plan_for(k2);
-        {   // on a stream of their own: the spectra are built while the image and the weights upload
-            StreamGuard aux;
-            v.spec1 = build_spectra(*c->dev, *c->plans[v.plan1], kernel1, aux.st);
-            v.spec2 = build_spectra(*c->dev, *c->plans[v.plan2], kernel2, aux.st);
-        }
-        v.sep_kmax1 = separate_kernel(kernel1, k1, v.taps1);
-        v.sep_kmax2 = separate_kernel(kernel2, k2, v.taps2);
-        MVD_CUDA(cudaStreamSynchronize(c->stream));  // caller buffers may go away after return
-        c->views.push_back(std::move(v));
-        if (viewIndex) *viewIndex = (int)c->views.size() - 1;
-    });
+    return guarded([&] { add_view(c, img, weight, weightConst, kernel1, k1, kernel2, k2, memKind, nullptr, nullptr, viewIndex); });
+}
+
+// every kernel that reads a view's image or weights runs behind its upload
+static void wait_view(mvdContext* c, ViewData& vd) {
+    if (vd.ready_pending) {
+        MVD_CUDA(cudaStreamWaitEvent(c->stream, vd.ready, 0));
+        vd.ready_pending = false;
+    }
+}
+static void wait_all_views(mvdContext* c) {
+    for (auto& v : c->views) wait_view(c, v);
 }
 
 extern "C" int mvdNumViews(mvdContext* c) { return c ? (int)c->views.size() : -1; }
@@ -422,6 +494,7 @@ extern "C" int mvdFirstIterationSums(mvdContext* c, double* sum, long long* coun
         c->activate();
         MVD_CUDA(cudaMemsetAsync(c->d_fi_sum, 0, sizeof(double), c->stream));
         MVD_CUDA(cudaMemsetAsync(c->d_fi_count, 0, sizeof(unsigned long long), c->stream));
+        wait_all_views(c);
         MVD_CUDA(launch_first_iteration_sums(c->view_ptrs(), c->brick_elems(), c->d_fi_sum, c->d_fi_count, c->stream));
         ++g_kernel_launches;
         unsigned long long cnt = 0;
@@ -474,6 +547,7 @@ extern "C" int mvdGetPsi(mvdContext* c, float* psi, int memKind) {
 // ---- the loop ------------------------------------------------------------------------------
 static void step_quotient(mvdContext* c, int v) {
     ViewData& vd = c->views[v];
+    wait_view(c, vd);
     // conv1: psi extended by mirror-single (MVDeconFFTThreads.java:23,57), fused quotient (MVDeconvolution.java:473-525)
     const Volume src = c->ghosted_volume(c->psi, EXT_MIRROR_SINGLE, 0.f);
     EpilogueArgs ep = c->epilogue_base(c->quot);
@@ -488,6 +562,7 @@ static void step_quotient(mvdContext* c, int v) {
 
 static void step_update(mvdContext* c, int v, int slot) {
     ViewData& vd = c->views[v];
+    wait_view(c, vd);
     c->ensure_stats(slot + 1);
     MVD_CUDA(cudaMemsetAsync(c->d_sum + slot, 0, sizeof(double), c->stream));
     MVD_CUDA(cudaMemsetAsync(c->d_max + slot, 0, sizeof(unsigned int), c->stream));
@@ -615,8 +690,8 @@ extern "C" int mvdViewUsesDirectPath(mvdContext* c, int view, int* conv1, int* c
 
 // The reference's second native hook: in-place separable convolution of a whole image or block with
 // one kernel of diameter N per axis (CUDASeparableConvolution.java:13-17, called by
-// CUDASeparableConvolutionFunctions.gauss, :127-199).  N <= 31 runs the direct kernels, 63 the FFT
-// engine axis by axis; 127 exceeds the largest xy window and is refused.
+// CUDASeparableConvolutionFunctions.gauss, :127-199).  N <= 31 runs the direct kernels, 63 and 127 the FFT
+// engine axis by axis (127 taps along x or y use the 256-point windows).
 static int separable_hook(int N, float* image, const float* kx, const float* ky, const float* kz, int w, int h, int d, int cx, int cy,
                           int cz, int oob, float oobv, int dev_id) {
     const int rc = guarded([&] {
@@ -661,6 +736,7 @@ static int separable_hook(int N, float* image, const float* kx, const float* ky,
             MVD_CUDA(cudaMalloc(&B.t, sep_tmp_elems(v, dim) * sizeof(float)));
             MVD_CUDA(launch_separable(v, dim, taps, kmax, EPI_STORE, ep, B.t, B.st));
             g_kernel_launches += 2;
+            MVD_CUDA(cudaStreamSynchronize(B.st));  // the caller's array is only touched once everything has succeeded
             MVD_CUDA(cudaMemcpyAsync(image, B.b, n * sizeof(float), cudaMemcpyDeviceToHost, B.st));
         } else {
             float* srcp = B.a;
@@ -673,6 +749,7 @@ static int separable_hook(int N, float* image, const float* kx, const float* ky,
                 convolve_device(dev, srcp, dim, ks[ax], kd, ext, oobv, dstp, B.st);
                 std::swap(srcp, dstp);
             }
+            MVD_CUDA(cudaStreamSynchronize(B.st));
             MVD_CUDA(cudaMemcpyAsync(image, srcp, n * sizeof(float), cudaMemcpyDeviceToHost, B.st));
         }
         MVD_CUDA(cudaStreamSynchronize(B.st));
@@ -786,9 +863,340 @@ extern "C" int mvdMaskNeverUpdated(mvdContext* c) {
     return guarded([&] {
         require(c && !c->views.empty(), "mvdMaskNeverUpdated: no views");
         c->activate();
+        wait_all_views(c);
         MVD_CUDA(launch_mask_never_updated(c->view_ptrs(), c->bdim, c->psi, c->adim, c->glo, c->stream));
         ++g_kernel_launches;
         MVD_CUDA(cudaStreamSynchronize(c->stream));
+    });
+}
+
+// ---- several devices behind one handle, one process ------------------------------------------------
+// The reference drives N devices from one JVM with one thread per device (MVDeconFFT.java:426-445).  mvdMulti does the
+// same behind the C ABI: the volume is cut into one brick per device (power-of-two grid, longest axis first, x bricks
+// float4-aligned), every brick is an mvdContext with ghost layers, the bricks are attached to each other as
+// MVD_PEER_POINTER neighbours (peer access over NVLink: the step kernels store ghost voxels into the neighbours), and a
+// worker thread per device issues that device's launches.  Between two steps a brick's stream waits for the events its
+// neighbours recorded after the previous step (cudaStreamWaitEvent across devices) -- a neighbour-only barrier on the
+// devices, no collective, no host synchronisation of the streams; the host threads meet at a barrier per step only so
+// that an event is recorded before anybody waits for it.
+#include <condition_variable>
+#include <functional>
+#include <thread>
+
+namespace {
+struct HostBarrier {
+    std::mutex m;
+    std::condition_variable cv;
+    int n, waiting = 0;
+    long long gen = 0;
+    explicit HostBarrier(int n_) : n(n_) {}
+    void arrive_and_wait() {
+        std::unique_lock<std::mutex> lk(m);
+        const long long g = gen;
+        if (++waiting == n) { waiting = 0; ++gen; cv.notify_all(); }
+        else cv.wait(lk, [&] { return gen != g; });
+    }
+};
+}  // namespace
+
+struct mvdMulti {
+    int n = 0;
+    int gdim[3], grid[3], ghost[3];
+    std::vector<int> devices;
+    std::vector<mvdContext*> bricks;
+    std::vector<std::vector<int>> neighbours;
+    std::vector<cudaEvent_t> done[2];  // per brick, alternating by step
+    long long step = 0;                 // steps issued so far (decides which event of a pair is current)
+    bool attached = false;
+    int num_views = 0;
+    ~mvdMulti() {
+        for (size_t i = 0; i < bricks.size(); ++i) {
+            if (bricks[i]) {
+                cudaSetDevice(bricks[i]->device);
+                if (bricks[i]->stream) cudaStreamSynchronize(bricks[i]->stream);
+            }
+        }
+        for (size_t i = 0; i < bricks.size(); ++i) {
+            if (!bricks[i]) continue;
+            cudaSetDevice(bricks[i]->device);
+            for (int k = 0; k < 2; ++k)
+                if (i < done[k].size() && done[k][i]) cudaEventDestroy(done[k][i]);
+            mvdDestroy(bricks[i]);
+        }
+    }
+    // fn(brick index) on one thread per brick; the first exception (message) is rethrown on the caller's thread
+    void parallel(const std::function<void(int)>& fn) {
+        std::vector<std::thread> th;
+        std::vector<std::string> err(n);
+        std::vector<int> kind(n, 0);
+        for (int i = 0; i < n; ++i)
+            th.emplace_back([&, i] {
+                try { fn(i); }
+                catch (const CudaError& e) { err[i] = e.what(); kind[i] = 2; cudaGetLastError(); }
+                catch (const std::invalid_argument& e) { err[i] = e.what(); kind[i] = 1; }
+                catch (const std::exception& e) { err[i] = e.what(); kind[i] = 3; }
+            });
+        for (auto& t : th) t.join();
+        for (int i = 0; i < n; ++i) {
+            if (kind[i] == 1) throw std::invalid_argument("brick " + std::to_string(i) + ": " + err[i]);
+            if (kind[i]) throw CudaError("brick " + std::to_string(i) + " (device " + std::to_string(devices[i]) + "): " + err[i]);
+        }
+    }
+};
+
+// brick boundaries b_i = floor4(n i / g) (b_0 = 0, b_g = n): x bricks stay float4-aligned (same rule as parallel.brick_of)
+static int brick_bound(int i, int g, int n) { return i == 0 ? 0 : (i == g ? n : (int)((long long)n * i / g / 4 * 4)); }
+
+static void multi_attach(mvdMulti* m) {
+    if (m->attached || m->n == 1) { m->attached = true; return; }
+    for (int b = 0; b < m->n; ++b) {
+        mvdContext* c = m->bricks[b];
+        for (int r : m->neighbours[b]) {
+            mvdContext* p = m->bricks[r];
+            if (mvdAttachPeer(c, p->boff, p->bdim, p->psi, p->quot, MVD_PEER_POINTER, p->device) != 0) {
+                char buf[512];
+                mvdGetLastError(buf, sizeof(buf));
+                throw CudaError(std::string("mvdAttachPeer: ") + buf);
+            }
+        }
+    }
+    m->attached = true;
+}
+
+extern "C" int mvdCreateMulti(mvdMulti** out, const int* devices, int numDevices, const int globalDim[3], const int maxKernelDim[3],
+                              double lambda, float minValue) {
+    return guarded([&] {
+        require(out && devices && globalDim && maxKernelDim, "mvdCreateMulti: null argument");
+        *out = nullptr;
+        require(numDevices >= 1 && (numDevices & (numDevices - 1)) == 0, "mvdCreateMulti: the number of devices must be a power of two");
+        std::unique_ptr<mvdMulti> m(new mvdMulti);
+        m->n = numDevices;
+        m->devices.assign(devices, devices + numDevices);
+        for (int d = 0; d < 3; ++d) { m->gdim[d] = globalDim[d]; m->grid[d] = 1; }
+        for (int k = numDevices; k > 1; k /= 2) {  // split the longest axis, z before y before x on ties
+            int best = 2;
+            for (int d = 1; d >= 0; --d)
+                if ((double)m->gdim[d] / m->grid[d] > (double)m->gdim[best] / m->grid[best]) best = d;
+            m->grid[best] *= 2;
+        }
+        for (int d = 0; d < 3; ++d) {
+            require(maxKernelDim[d] >= 1, "mvdCreateMulti: bad kernel extent");
+            m->ghost[d] = m->grid[d] > 1 ? std::max(maxKernelDim[d] / 2, maxKernelDim[d] - 1 - maxKernelDim[d] / 2) : 0;
+        }
+        m->bricks.assign(numDevices, nullptr);
+        m->neighbours.resize(numDevices);
+        for (int k = 0; k < 2; ++k) m->done[k].assign(numDevices, nullptr);
+        std::vector<std::array<int, 3>> coords(numDevices);
+        for (int r = 0; r < numDevices; ++r) {
+            const int cx = r % m->grid[0], cy = (r / m->grid[0]) % m->grid[1], cz = r / (m->grid[0] * m->grid[1]);
+            coords[r] = {cx, cy, cz};
+            int off[3], dim[3];
+            for (int d = 0; d < 3; ++d) {
+                off[d] = brick_bound(coords[r][d], m->grid[d], m->gdim[d]);
+                dim[d] = brick_bound(coords[r][d] + 1, m->grid[d], m->gdim[d]) - off[d];
+                require(dim[d] >= std::max(1, m->ghost[d]), "mvdCreateMulti: bricks thinner than the kernel halo");
+            }
+            if (mvdCreate(&m->bricks[r], devices[r], m->gdim, off, dim, m->ghost, lambda, minValue) != 0) {
+                char buf[512];
+                mvdGetLastError(buf, sizeof(buf));
+                throw CudaError(std::string("mvdCreate: ") + buf);
+            }
+            MVD_CUDA(cudaSetDevice(devices[r]));
+            for (int k = 0; k < 2; ++k) MVD_CUDA(cudaEventCreateWithFlags(&m->done[k][r], cudaEventDisableTiming));
+        }
+        for (int r = 0; r < numDevices; ++r)
+            for (int q = 0; q < numDevices; ++q) {
+                if (q == r) continue;
+                bool nb = true;
+                for (int d = 0; d < 3; ++d) {
+                    const int delta = coords[q][d] - coords[r][d];
+                    nb = nb && delta >= -1 && delta <= 1 && (delta == 0 || m->ghost[d] > 0);
+                }
+                if (nb) m->neighbours[r].push_back(q);
+            }
+        *out = m.release();
+    });
+}
+
+extern "C" int mvdDestroyMulti(mvdMulti* m) {
+    if (!m) return 0;
+    return guarded([&] { delete m; });
+}
+
+extern "C" int mvdMultiNumBricks(mvdMulti* m) { return m ? m->n : -1; }
+
+extern "C" int mvdMultiBrickInfo(mvdMulti* m, int brick, int* device, int offset[3], int dim[3]) {
+    return guarded([&] {
+        require(m && brick >= 0 && brick < m->n, "mvdMultiBrickInfo: bad brick");
+        if (device) *device = m->devices[brick];
+        for (int d = 0; d < 3; ++d) {
+            if (offset) offset[d] = m->bricks[brick]->boff[d];
+            if (dim) dim[d] = m->bricks[brick]->bdim[d];
+        }
+    });
+}
+
+// img / weight: whole-volume host arrays (x fastest); every device uploads its brick from them
+extern "C" int mvdMultiAddView(mvdMulti* m, const float* img, const float* weight, float weightConst, const float* kernel1, const int k1[3],
+                               const float* kernel2, const int k2[3]) {
+    return guarded([&] {
+        require(m && img && kernel1 && kernel2 && k1 && k2, "mvdMultiAddView: null argument");
+        for (int d = 0; d < 3; ++d)
+            require(m->grid[d] == 1 || (std::max(k1[d], k2[d]) / 2 <= m->ghost[d] && std::max(k1[d], k2[d]) - 1 - std::max(k1[d], k2[d]) / 2 <= m->ghost[d]),
+                    "mvdMultiAddView: kernel larger than the maxKernelDim given to mvdCreateMulti");
+        m->parallel([&](int b) {
+            mvdContext* c = m->bricks[b];
+            add_view(c, img, weight, weightConst, kernel1, k1, kernel2, k2, MVD_MEM_HOST, m->gdim, c->boff, nullptr);
+        });
+        ++m->num_views;
+    });
+}
+
+extern "C" int mvdMultiSetDirectPath(mvdMulti* m, int enable) {
+    return guarded([&] {
+        require(m, "mvdMultiSetDirectPath: null handle");
+        for (auto* c : m->bricks) c->direct_enabled = enable != 0;
+    });
+}
+
+// psi = the average of MVDeconvolution.java:105-127 over the WHOLE volume, in every brick (ghost layers included)
+extern "C" int mvdMultiInitPsiAverage(mvdMulti* m, double* avgOut) {
+    return guarded([&] {
+        require(m && m->num_views > 0, "mvdMultiInitPsiAverage: no views");
+        std::vector<double> sums(m->n, 0.0);
+        std::vector<long long> counts(m->n, 0);
+        auto check = [](int rc, const char* what) {
+            if (rc != 0) {
+                char buf[512];
+                mvdGetLastError(buf, sizeof(buf));
+                throw CudaError(std::string(what) + ": " + buf);
+            }
+        };
+        m->parallel([&](int b) { check(mvdFirstIterationSums(m->bricks[b], &sums[b], &counts[b]), "mvdFirstIterationSums"); });
+        double s = 0.0;
+        long long n = 0;
+        for (int b = 0; b < m->n; ++b) { s += sums[b]; n += counts[b]; }
+        double avg = s / (double)n;
+        if (std::isnan(avg)) avg = 0.5;
+        if (avgOut) *avgOut = avg;
+        m->parallel([&](int b) {
+            check(mvdFillPsi(m->bricks[b], (float)avg), "mvdFillPsi");
+            check(mvdSynchronize(m->bricks[b]), "mvdSynchronize");
+        });
+    });
+}
+
+// whole-volume host array <-> the bricks' (ghosted) arrays; `ghosts`: also fill the ghost layers from the volume
+static void multi_copy_psi(mvdMulti* m, float* vol, bool to_device) {
+    m->parallel([&](int b) {
+        mvdContext* c = m->bricks[b];
+        c->activate();
+        int lo[3], n[3];  // volume box covered by the copy, clipped to the volume
+        for (int d = 0; d < 3; ++d) {
+            const int a0 = to_device ? c->boff[d] - c->glo[d] : c->boff[d];
+            const int a1 = to_device ? c->boff[d] + c->bdim[d] + c->ghi[d] : c->boff[d] + c->bdim[d];
+            lo[d] = std::max(0, a0);
+            n[d] = std::min(c->gdim[d], a1) - lo[d];
+        }
+        cudaMemcpy3DParms p;
+        std::memset(&p, 0, sizeof(p));
+        cudaPitchedPtr h = make_cudaPitchedPtr(vol, (size_t)c->gdim[0] * sizeof(float), c->gdim[0], c->gdim[1]);
+        cudaPitchedPtr g = make_cudaPitchedPtr(c->psi, (size_t)c->adim[0] * sizeof(float), c->adim[0], c->adim[1]);
+        const cudaPos hpos = make_cudaPos((size_t)lo[0] * sizeof(float), lo[1], lo[2]);
+        const cudaPos gpos = make_cudaPos((size_t)(lo[0] - (c->boff[0] - c->glo[0])) * sizeof(float), lo[1] - (c->boff[1] - c->glo[1]),
+                                          lo[2] - (c->boff[2] - c->glo[2]));
+        if (to_device) { p.srcPtr = h; p.srcPos = hpos; p.dstPtr = g; p.dstPos = gpos; p.kind = cudaMemcpyHostToDevice; }
+        else { p.srcPtr = g; p.srcPos = gpos; p.dstPtr = h; p.dstPos = hpos; p.kind = cudaMemcpyDeviceToHost; }
+        p.extent = make_cudaExtent((size_t)n[0] * sizeof(float), n[1], n[2]);
+        MVD_CUDA(cudaMemcpy3DAsync(&p, c->stream));
+        MVD_CUDA(cudaStreamSynchronize(c->stream));
+    });
+}
+
+extern "C" int mvdMultiSetPsi(mvdMulti* m, const float* psi) {
+    return guarded([&] {
+        require(m && psi, "mvdMultiSetPsi: null argument");
+        multi_copy_psi(m, const_cast<float*>(psi), true);  // ghost layers come straight from the caller's volume
+    });
+}
+
+extern "C" int mvdMultiGetPsi(mvdMulti* m, float* psi) {
+    return guarded([&] {
+        require(m && psi, "mvdMultiGetPsi: null argument");
+        multi_copy_psi(m, psi, false);
+    });
+}
+
+extern "C" int mvdMultiMaskNeverUpdated(mvdMulti* m) {
+    return guarded([&] {
+        require(m && m->num_views > 0, "mvdMultiMaskNeverUpdated: no views");
+        m->parallel([&](int b) {
+            if (mvdMaskNeverUpdated(m->bricks[b]) != 0) {
+                char buf[512];
+                mvdGetLastError(buf, sizeof(buf));
+                throw CudaError(std::string("mvdMaskNeverUpdated: ") + buf);
+            }
+        });
+    });
+}
+
+// numIterations passes over all views (MVDeconvolution.runIteration, :333-444) on all devices; sumChange / maxChange:
+// numIterations * numViews values each (sum over the bricks / maximum over the bricks), or NULL
+extern "C" int mvdMultiRunIterations(mvdMulti* m, int numIterations, double* sumChange, double* maxChange) {
+    return guarded([&] {
+        require(m && m->num_views > 0, "mvdMultiRunIterations: no views");
+        require(numIterations >= 0, "mvdMultiRunIterations: negative iteration count");
+        multi_attach(m);
+        const int nv = m->num_views, nslots = numIterations * nv;
+        HostBarrier barrier(m->n);
+        std::atomic<bool> failed{false};
+        std::vector<std::vector<double>> sums(m->n, std::vector<double>(std::max(nslots, 1))), maxs(m->n, std::vector<double>(std::max(nslots, 1)));
+        const long long step0 = m->step;
+        m->parallel([&](int b) {
+            mvdContext* c = m->bricks[b];
+            std::string err;
+            int kind = 0;
+            long long step = step0;
+            auto one_step = [&](const std::function<void()>& body) {
+                // every thread passes every barrier, whatever happens: a failing brick only stops issuing work
+                if (!failed.load()) {
+                    try {
+                        c->activate();
+                        if (step > 0)
+                            for (int r : m->neighbours[b]) MVD_CUDA(cudaStreamWaitEvent(c->stream, m->done[(step - 1) & 1][r], 0));
+                        body();
+                        MVD_CUDA(cudaEventRecord(m->done[step & 1][b], c->stream));
+                    } catch (const CudaError& e) { err = e.what(); kind = 2; failed.store(true); }
+                    catch (const std::exception& e) { err = e.what(); kind = 1; failed.store(true); }
+                }
+                ++step;
+                barrier.arrive_and_wait();  // all events of this step are recorded before anybody waits for them
+            };
+            try {
+                c->activate();
+                c->ensure_stats(nslots);
+            } catch (const std::exception& e) { err = e.what(); kind = 2; failed.store(true); }
+            for (int it = 0; it < numIterations; ++it)
+                for (int v = 0; v < nv; ++v) {
+                    one_step([&] { step_quotient(c, v); });
+                    one_step([&] { step_update(c, v, it * nv + v); });
+                }
+            if (!failed.load()) {
+                try {
+                    if (nslots > 0) read_stats(c, 0, nslots, sums[b].data(), maxs[b].data());
+                    else MVD_CUDA(cudaStreamSynchronize(c->stream));
+                } catch (const std::exception& e) { err = e.what(); kind = 2; failed.store(true); }
+            }
+            if (kind == 1) throw std::invalid_argument(err);
+            if (kind) throw CudaError(err);
+        });
+        m->step = step0 + 2LL * nslots;
+        for (int i = 0; i < nslots; ++i) {
+            double s = 0.0, mx = -1.0;
+            for (int b = 0; b < m->n; ++b) { s += sums[b][i]; mx = std::max(mx, maxs[b][i]); }
+            if (sumChange) sumChange[i] = s;
+            if (maxChange) maxChange[i] = mx;
+        }
     });
 }
 

@@ -23,12 +23,15 @@
 #include "row128.cuh"
 #include "z_items.cuh"
 #include "device_common.cuh"
+#include "inv_rows128.cuh"
 
 #include <algorithm>
 
 namespace mvd {
 
-static constexpr int NT = 256;  // threads per CTA of the xy kernels
+// threads per CTA of the xy kernels: 256, two or three CTAs per SM; windows with a 256-point side hold a plane of
+// > 113 KB, i.e. one CTA per SM, and run 512 threads
+template <int BX, int BY> struct XYThreads { static constexpr int NT = (BX > 128 || BY > 128) ? 512 : 256; };
 #ifndef MVD_XY_ZPC
 #define MVD_XY_ZPC 4  // planes per work item of the xy kernels (measured: 1 -> 32.1, 2 -> 31.9, 4 -> 31.5 ms per iteration)
 #endif
@@ -37,12 +40,12 @@ static constexpr int NT = 256;  // threads per CTA of the xy kernels
 #endif
 static constexpr int XY_ZPC = MVD_XY_ZPC;  // z-planes per CTA of the xy kernels
 
-// exp(-2 pi i n / 128): column twiddles of the xy kernels (the index is warp-uniform there)
-__constant__ float2 c_tw128[128];
+// exp(-2 pi i n / 256): column twiddles of the xy kernels (the index is warp-uniform there)
+__constant__ float2 c_tw256[256];
 
-struct ConstTw128 {
-    int shift;  // log2(128 / N)
-    __device__ __forceinline__ float2 operator[](int i) const { return c_tw128[i << shift]; }
+struct ConstTw256 {
+    int shift;  // log2(256 / N)
+    __device__ __forceinline__ float2 operator[](int i) const { return c_tw256[i << shift]; }
 };
 
 // shared-memory plane: BY rows of H = BX/2 packed complex columns.
@@ -69,6 +72,7 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 
 template <int BX, int BY> struct XYCfg {
     using L = PlaneLayout<BX>;
+    static constexpr int NT = XYThreads<BX, BY>::NT;
     static constexpr int H = BX / 2;
     static constexpr int TX = H / 8;            // threads per row, 8 packed complex each
     static constexpr int RPR = NT / TX;         // rows per round
@@ -84,7 +88,7 @@ template <int BX, int BY> struct XYCfg {
     static constexpr size_t SMEM_INV = PLANE + (size_t)(2 * H) * sizeof(float2);
     static_assert(BX != 128 || 2 * H >= 96, "fast-row tables need 96 float2");
     // 228 KB per SM, 1 KB reserved per resident CTA (+ the inverse kernel's static reduction arrays)
-    static constexpr int MIN_CTAS = (SMEM_FWD + 1024 + 128) * 3 <= 233472 ? 3 : ((SMEM_FWD + 1024 + 128) * 2 <= 233472 ? 2 : 1);
+    static constexpr int MIN_CTAS = NT > 256 ? 1 : ((SMEM_FWD + 1024 + 128) * 3 <= 233472 ? 3 : ((SMEM_FWD + 1024 + 128) * 2 <= 233472 ? 2 : 1));
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -96,16 +100,17 @@ template <int BX, int BY> struct XYCfg {
 #endif
 // the up-front loads of the 128 x 128 kernel need 126 registers: two CTAs per SM (measured equal to three at 77 registers without them)
 template <int BX, int BY> struct FwdCfg {
-    static constexpr bool PIPE = MVD_FWD_PIPE != 0 && BX == 128 && BY == 2 * (NT / 4);
+    static constexpr bool PIPE = MVD_FWD_PIPE != 0 && BX == 128 && BY == 2 * (XYThreads<BX, BY>::NT / 4);
     static constexpr int WANT = PIPE ? 2 : MVD_FWD_MINCTAS;
     static constexpr int MIN_CTAS = XYCfg<BX, BY>::MIN_CTAS < WANT ? XYCfg<BX, BY>::MIN_CTAS : WANT;
 };
 template <int BX, int BY>
-__global__ void __launch_bounds__(NT, FwdCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Volume src, const Tile* __restrict__ tiles,
+__global__ void __launch_bounds__((XYThreads<BX, BY>::NT), FwdCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Volume src, const Tile* __restrict__ tiles,
                                                                            float2* __restrict__ scratch, size_t tile_stride, int bz,
                                                                            int n_items, Twiddles tw) {
     using C = XYCfg<BX, BY>;
     using L = PlaneLayout<BX>;
+    constexpr int NT = C::NT;
     constexpr int H = C::H, P = L::P, TX = C::TX, RPR = C::RPR, TY = C::TY, CPR = C::CPR;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float2* plane = reinterpret_cast<float2*>(smem_raw);
@@ -148,7 +153,7 @@ __global__ void __launch_bounds__(NT, FwdCfg<BX, BY>::MIN_CTAS) fwd_xy_kernel(Vo
     // column phase thread mapping
     const int cc = tid % CPR;
     const int cu = tid / CPR;
-    const ConstTw128 twc{7 - ilog2<BY>()};
+    const ConstTw256 twc{8 - ilog2<BY>()};
 
 #pragma unroll 1
     for (int zi = 0; zi < XY_ZPC; ++zi) {
@@ -521,58 +526,16 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
     if constexpr (C::ASYNC) cp_async_wait_all();
 }
 
-// ---------------------------------------------------------------------------------------------
-// Fused ghost-layer exchange: a run of N freshly computed output voxels starting at brick
-// coordinate (x0, y, z) is also stored into the ghost layers of every neighbouring brick that
-// needs it (PeerTarget, conv_types.h) -- peer memory over NVLink, written by the same kernel
-// that produced the values.  `peers` is the tile's candidate list in shared memory and `pm` the
-// subset whose y/z range contains the row (push_row_mask), so interior tiles never get here.
-// also returns the x range [xlo, xhi) covered by the matching neighbours, so that runs outside it skip the call
-__device__ __forceinline__ unsigned push_row_mask(const PeerTarget* peers, int n, int y, int z, int& xlo, int& xhi) {
-    unsigned m = 0;
-    xlo = 0x7fffffff;
-    xhi = -0x7fffffff;
-    for (int i = 0; i < n; ++i) {
-        const PeerTarget& t = peers[i];
-        if (y >= t.lo[1] && y < t.hi[1] && z >= t.lo[2] && z < t.hi[2]) {
-            m |= 1u << i;
-            xlo = min(xlo, t.lo[0]);
-            xhi = max(xhi, t.hi[0]);
-        }
-    }
-    return m;
-}
-
-template <int N>
-__device__ __noinline__ void push_run(const PeerTarget* __restrict__ peers, unsigned pm, int x0, int y, int z, float4 r) {
-    const float rv[4] = {r.x, r.y, r.z, r.w};
-    for (; pm; pm &= pm - 1) {
-        const PeerTarget& t = peers[__ffs(pm) - 1];
-        if (x0 + N <= t.lo[0] || x0 >= t.hi[0]) continue;
-        const long long idx = ((long long)(z + t.shift[2]) * t.dim[1] + (y + t.shift[1])) * (long long)t.dim[0] + (x0 + t.shift[0]);
-        float* __restrict__ p = t.base + idx;
-        const bool inside = x0 >= t.lo[0] && x0 + N <= t.hi[0];
-        if (N == 4 && inside && (idx & 3) == 0) {
-            *reinterpret_cast<float4*>(p) = r;
-        } else if (N == 2 && inside && (idx & 1) == 0) {
-            *reinterpret_cast<float2*>(p) = make_float2(r.x, r.y);
-        } else {
-#pragma unroll
-            for (int i = 0; i < N; ++i)
-                if (x0 + i >= t.lo[0] && x0 + i < t.hi[0]) p[i] = rv[i];
-        }
-    }
-}
-
 #ifndef MVD_INV_MINCTAS
 #define MVD_INV_MINCTAS 2  // 2 x 256 threads at <= 128 registers beat 3 x 256 at 80 with spills (measured)
 #endif
 template <int BX, int BY, int EPI, bool PUSH>
-__global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS ? XYCfg<BX, BY>::MIN_CTAS : MVD_INV_MINCTAS)) inv_xy_kernel(const float2* __restrict__ scratch, size_t tile_stride,
+__global__ void __launch_bounds__((XYThreads<BX, BY>::NT), (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS ? XYCfg<BX, BY>::MIN_CTAS : MVD_INV_MINCTAS)) inv_xy_kernel(const float2* __restrict__ scratch, size_t tile_stride,
                                                                            const Tile* __restrict__ tiles, EpilogueArgs ep, int chunks,
                                                                            int n_items, Twiddles tw) {
     using C = XYCfg<BX, BY>;
     using L = PlaneLayout<BX>;
+    constexpr int NT = C::NT;
     constexpr int H = C::H, P = L::P, TX = C::TX, RPR = C::RPR, TY = C::TY, CPR = C::CPR;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float2* plane = reinterpret_cast<float2*>(smem_raw);
@@ -596,7 +559,7 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
     const int rrow = tid / TX;
     const int cc = tid % CPR;
     const int cu = tid / CPR;
-    const ConstTw128 twc{7 - ilog2<BY>()};
+    const ConstTw256 twc{8 - ilog2<BY>()};
     const bool use_tik = ep.lambda > 0.0;
     const TikhonovConst tik = make_tikhonov(ep.lambda);
     double lsum = 0.0;
@@ -694,122 +657,7 @@ __global__ void __launch_bounds__(NT, (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS
         // ---- phase 2: inverse rows (C2R through the packed half-length transform) + epilogue.
         // Only the rows of the effective region are transformed; the others would be discarded.
         if constexpr (BX == 128) {
-            const int q = tid & 3;
-#pragma unroll 1
-            for (int yl0 = 0; yl0 < n1; yl0 += NT / 4) {
-                const int yl = yl0 + (tid >> 2);
-                // rows of the effective region come in multiples of 4, a warp holds 8 of them
-                const unsigned wmask = __ballot_sync(0xffffffffu, yl < n1);
-                if (yl >= n1) continue;
-                float2 e[8], f[8];
-                float rsum = 0.f;  // |change| of this thread's <= 32 voxels of the row, added to the double sum once
-                int pxlo = 0, pxhi = 0;  // brick x range any neighbour wants from this row
-                const unsigned pm = PUSH && s_npeer ? push_row_mask(s_peer, s_npeer, tile.e[1] + yl, zv, pxlo, pxhi) : 0u;
-                const size_t rowbase = ((size_t)(zv + ep.out_off[2]) * ep.out_dim[1] + (tile.e[1] + yl + ep.out_off[1])) * (size_t)ep.out_dim[0] +
-                                       tile.e[0] + ep.out_off[0];
-                const size_t auxbase = ((size_t)zv * ep.aux_dim[1] + (tile.e[1] + yl)) * (size_t)ep.aux_dim[0] + tile.e[0];
-                const bool vec = ((rowbase | auxbase) & 3) == 0 && ((reinterpret_cast<uintptr_t>(ep.out) | reinterpret_cast<uintptr_t>(ep.img) |
-                                                                      reinterpret_cast<uintptr_t>(ep.weight)) & 15) == 0;
-                const int xq = 4 * q - lx;  // first sample of the thread's quad m = 0, in region coordinates
-                unsigned full4 = 0, part4 = 0;
-#pragma unroll
-                for (int m = 0; m < 8; ++m) {
-                    const int xl = xq + 16 * m;
-                    if (xl >= 0 && xl + 3 < n0) full4 |= 1u << m;
-                    else if (xl + 3 >= 0 && xl < n0) part4 |= 1u << m;
-                }
-                float* __restrict__ outp = ep.out + rowbase + xq;
-                const float* __restrict__ imgp = ep.img + auxbase + xq;
-                const float* __restrict__ wp = ep.weight + auxbase + xq;
-                // epilogue operands of quads h .. h+3 (the first half is requested before the row transform,
-                // the second half before the first half is consumed: two batches of loads in flight)
-                auto load_half = [&](int h, float4 (&a)[4], float4 (&b)[4]) {
-#pragma unroll
-                    for (int i4 = 0; i4 < 4; ++i4) {
-                        const int m = h + i4;
-                        a[i4] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        b[i4] = make_float4(ep.weight_const, ep.weight_const, ep.weight_const, ep.weight_const);
-                        if (vec && (full4 >> m & 1)) {
-                            if constexpr (EPI == EPI_QUOTIENT) a[i4] = __ldg(reinterpret_cast<const float4*>(imgp + 16 * m));
-                            if constexpr (EPI == EPI_UPDATE) {
-                                a[i4] = *reinterpret_cast<const float4*>(outp + 16 * m);
-                                if (ep.weight) b[i4] = __ldg(reinterpret_cast<const float4*>(wp + 16 * m));
-                            }
-                        }
-                    }
-                };
-                auto finish_half = [&](int h, const float4 (&a)[4], const float4 (&b)[4]) {
-#pragma unroll
-                    for (int i4 = 0; i4 < 4; ++i4) {
-                        const int m = h + i4;
-                        if (full4 >> m & 1) {
-                            const float c[4] = {e[m].x + ep.add_const, e[m].y + ep.add_const, f[m].x + ep.add_const, f[m].y + ep.add_const};
-                            const float av[4] = {a[i4].x, a[i4].y, a[i4].z, a[i4].w};
-                            const float bv[4] = {b[i4].x, b[i4].y, b[i4].z, b[i4].w};
-                            float r[4];
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                if constexpr (EPI == EPI_STORE) r[i] = c[i];
-                                else if constexpr (EPI == EPI_QUOTIENT) r[i] = quotient_value(av[i], c[i]);
-                                else {
-                                    r[i] = next_psi_value(av[i], c[i], bv[i], use_tik, tik, ep.min_value);
-                                    const float ch = fabsf(__fsub_rn(r[i], av[i]));
-                                    rsum += ch;
-                                    lmax = fmaxf(lmax, ch);  // fmaxf drops NaN
-                                }
-                            }
-                            *reinterpret_cast<float4*>(outp + 16 * m) = make_float4(r[0], r[1], r[2], r[3]);
-                            if constexpr (PUSH) {
-                                const int px = tile.e[0] + xq + 16 * m;
-                                if (pm && px + 4 > pxlo && px < pxhi) push_run<4>(s_peer, pm, px, tile.e[1] + yl, zv, make_float4(r[0], r[1], r[2], r[3]));
-                            }
-                        }
-                    }
-                };
-                float4 a0[4], b0[4];
-                load_half(0, a0, b0);
-                row128_inverse(e, f, plane + (ly + yl) * P, twr, twu, q, wmask);
-                // (e[m].x, e[m].y, f[m].x, f[m].y) = samples x = 16 m + 4 q .. + 3 of the window
-                if (vec) {
-                    float4 a1[4], b1[4];
-                    load_half(4, a1, b1);
-                    finish_half(0, a0, b0);
-                    finish_half(4, a1, b1);
-                } else {
-                    part4 |= full4;
-                }
-                if (part4) {  // quads straddling the region border, or unaligned rows
-#pragma unroll
-                    for (int m = 0; m < 8; ++m) {
-                        if (!(part4 >> m & 1)) continue;
-                        const float c[4] = {e[m].x + ep.add_const, e[m].y + ep.add_const, f[m].x + ep.add_const, f[m].y + ep.add_const};
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const int x = xq + 16 * m + i;
-                            if (x < 0 || x >= n0) continue;
-                            const size_t idx = rowbase + x, aidx = auxbase + x;
-                            float nv;
-                            if constexpr (EPI == EPI_STORE) {
-                                nv = c[i];
-                            } else if constexpr (EPI == EPI_QUOTIENT) {
-                                nv = quotient_value(__ldg(ep.img + aidx), c[i]);
-                            } else {
-                                const float last = ep.out[idx];
-                                const float w = ep.weight ? __ldg(ep.weight + aidx) : ep.weight_const;
-                                nv = next_psi_value(last, c[i], w, use_tik, tik, ep.min_value);
-                                const float ch = fabsf(__fsub_rn(nv, last));
-                                rsum += ch;
-                                lmax = fmaxf(lmax, ch);
-                            }
-                            ep.out[idx] = nv;
-                            if constexpr (PUSH) {
-                                if (pm && tile.e[0] + x >= pxlo && tile.e[0] + x < pxhi) push_run<1>(s_peer, pm, tile.e[0] + x, tile.e[1] + yl, zv, make_float4(nv, 0.f, 0.f, 0.f));
-                            }
-                        }
-                    }
-                }
-                if constexpr (EPI == EPI_UPDATE) lsum += (double)rsum;
-            }
+            inv_rows128<EPI, PUSH, NT>(plane, twr, twu, tile, zv, ep, s_peer, s_npeer, tid, use_tik, tik, lsum, lmax);
         } else {
 #pragma unroll 1
         for (int yl0 = 0; yl0 < n1; yl0 += RPR) {
@@ -952,6 +800,8 @@ int g_num_sms = 148;  // set by configure_conv_kernels
 void set_grid_caps(int xy_cap, int z_cap) { g_xy_grid_cap = xy_cap; g_z_grid_cap = z_cap; }
 
 bool xy_size_supported(int b) { return b == 32 || b == 64 || b == 128; }
+bool y_size_supported(int b) { return xy_size_supported(b) || b == 256; }
+bool xy_pair_supported(int bx, int by) { return y_size_supported(bx) && y_size_supported(by) && !(bx == 256 && by == 256); }
 bool z_size_supported(int b) { return b == 16 || b == 32 || b == 64 || b == 128 || b == 256 || b == 512; }
 size_t plane_elems(int bx, int by) { return (size_t)(bx / 2 + 1) * by; }
 size_t tile_scratch_elems(int bx, int by, int bz) { return plane_elems(bx, by) * bz; }
@@ -968,7 +818,11 @@ static inline Twiddles to_dev(const TwiddleTables& t) {
         else if (bx == 32 && by == 128) { F(32, 128); } else if (bx == 64 && by == 32) { F(64, 32); } \
         else if (bx == 64 && by == 64) { F(64, 64); } else if (bx == 64 && by == 128) { F(64, 128); } \
         else if (bx == 128 && by == 32) { F(128, 32); } else if (bx == 128 && by == 64) { F(128, 64); } \
-        else if (bx == 128 && by == 128) { F(128, 128); } else return cudaErrorInvalidValue;      \
+        else if (bx == 128 && by == 128) { F(128, 128); } else if (bx == 32 && by == 256) { F(32, 256); }  \
+        else if (bx == 64 && by == 256) { F(64, 256); } else if (bx == 128 && by == 256) { F(128, 256); } \
+        else if (bx == 256 && by == 32) { F(256, 32); } else if (bx == 256 && by == 64) { F(256, 64); }   \
+        else if (bx == 256 && by == 128) { F(256, 128); }                                                 \
+        else return cudaErrorInvalidValue;      \
     } while (0)
 
 #define MVD_Z_DISPATCH(bz, F)                                                               \
@@ -989,13 +843,13 @@ cudaError_t configure_conv_kernels() {
     }
     // column twiddles in the constant bank
     {
-        float2 h[128];
+        float2 h[256];
         const double two_pi = 6.283185307179586476925286766559;
-        for (int i = 0; i < 128; ++i) {
-            const double a = -two_pi * (double)i / 128.0;
+        for (int i = 0; i < 256; ++i) {
+            const double a = -two_pi * (double)i / 256.0;
             h[i] = make_float2((float)cos(a), (float)sin(a));
         }
-        e = cudaMemcpyToSymbol(c_tw128, h, sizeof(h));
+        e = cudaMemcpyToSymbol(c_tw256, h, sizeof(h));
     }
 #define CFG_XY(BX, BY)                                                                                                           \
     {                                                                                                                            \
@@ -1008,6 +862,7 @@ cudaError_t configure_conv_kernels() {
         if (e == cudaSuccess) e = cudaFuncSetAttribute(inv_xy_kernel<BX, BY, EPI_UPDATE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm); \
     }
     CFG_XY(32, 32) CFG_XY(32, 64) CFG_XY(32, 128) CFG_XY(64, 32) CFG_XY(64, 64) CFG_XY(64, 128) CFG_XY(128, 32) CFG_XY(128, 64) CFG_XY(128, 128)
+    CFG_XY(32, 256) CFG_XY(64, 256) CFG_XY(128, 256) CFG_XY(256, 32) CFG_XY(256, 64) CFG_XY(256, 128)
 #undef CFG_XY
 #define CFG_Z(BZ)                                                                                                                 \
     {                                                                                                                             \
@@ -1025,7 +880,7 @@ cudaError_t launch_fwd_xy(int bx, int by, int bz, const Volume& src, const Tile*
     const size_t stride = tile_scratch_elems(bx, by, bz);
     const int n_items = ((bz + XY_ZPC - 1) / XY_ZPC) * n_tiles;
     const int grid = g_xy_grid_cap > 0 ? std::min(n_items, g_xy_grid_cap) : n_items;
-#define F(BX, BY) fwd_xy_kernel<BX, BY><<<grid, NT, XYCfg<BX, BY>::SMEM_FWD, st>>>(src, d_tiles, scratch, stride, bz, n_items, to_dev(tw))
+#define F(BX, BY) fwd_xy_kernel<BX, BY><<<grid, XYCfg<BX, BY>::NT, XYCfg<BX, BY>::SMEM_FWD, st>>>(src, d_tiles, scratch, stride, bz, n_items, to_dev(tw))
     MVD_XY_DISPATCH(bx, by, F);
 #undef F
     return cudaGetLastError();
@@ -1062,11 +917,11 @@ cudaError_t launch_inv_xy(int bx, int by, int bz, int epilogue, const float2* sc
     {                                                                                                                    \
         constexpr size_t sm = XYCfg<BX, BY>::SMEM_INV;                                                                       \
         const bool push = ep.peers != nullptr && ep.n_peers > 0;                                                         \
-        if (epilogue == EPI_STORE) inv_xy_kernel<BX, BY, EPI_STORE, false><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
-        else if (epilogue == EPI_QUOTIENT && !push) inv_xy_kernel<BX, BY, EPI_QUOTIENT, false><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
-        else if (epilogue == EPI_QUOTIENT) inv_xy_kernel<BX, BY, EPI_QUOTIENT, true><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
-        else if (!push) inv_xy_kernel<BX, BY, EPI_UPDATE, false><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
-        else inv_xy_kernel<BX, BY, EPI_UPDATE, true><<<grid, NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        if (epilogue == EPI_STORE) inv_xy_kernel<BX, BY, EPI_STORE, false><<<grid, XYCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else if (epilogue == EPI_QUOTIENT && !push) inv_xy_kernel<BX, BY, EPI_QUOTIENT, false><<<grid, XYCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else if (epilogue == EPI_QUOTIENT) inv_xy_kernel<BX, BY, EPI_QUOTIENT, true><<<grid, XYCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else if (!push) inv_xy_kernel<BX, BY, EPI_UPDATE, false><<<grid, XYCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else inv_xy_kernel<BX, BY, EPI_UPDATE, true><<<grid, XYCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
     }
     MVD_XY_DISPATCH(bx, by, F);
 #undef F

@@ -12,6 +12,9 @@ struct TwiddleTables {
 
 // true when (bx,by) / bz are sizes the kernels are instantiated for
 bool xy_size_supported(int b);
+bool y_size_supported(int b);
+// windows with a 256-point side exist for kernels too wide for 128 (one 512-thread CTA per SM); 256 x 256 planes do not fit one SM
+bool xy_pair_supported(int bx, int by);
 bool z_size_supported(int b);
 
 size_t plane_elems(int bx, int by);                 // (bx/2+1)*by complex per z-plane
@@ -30,6 +33,11 @@ bool z_tma_supported(int bz);
 cudaError_t configure_z_tma_kernels();
 cudaError_t launch_z_pass_tma(int bx, int by, int bz, float2* scratch, const float2* kspec, int n_tiles, int zlo, int max_nz, int num_sms,
                               const TwiddleTables& tw, cudaStream_t st);
+// inverse xy pass for 128 x 128 windows fed by bulk copies into a shared-memory ring (inv_ring_kernels.cu)
+bool inv_ring_supported(int bx, int by);
+cudaError_t configure_inv_ring_kernels();
+cudaError_t launch_inv_ring(int bz, int epilogue, const float2* scratch, const Tile* d_tiles, int n_tiles, int max_nz, const EpilogueArgs& ep,
+                            int num_sms, const TwiddleTables& tw, cudaStream_t st);
 void set_grid_caps(int xy_cap, int z_cap);  // persistent-grid sizes, 0 = one CTA per work item
 cudaError_t configure_conv_kernels();  // opt in to > 48 KB dynamic shared memory
 

@@ -16,6 +16,7 @@ static int env_flag(const char* name, int dflt) {
     return s ? std::atoi(s) : dflt;
 }
 std::atomic<int> g_use_z_tma{env_flag("MVD_Z_TMA", 0)};
+std::atomic<int> g_use_inv_ring{env_flag("MVD_INV_RING", 1)};
 
 void cuda_check(cudaError_t e, const char* what) {
     if (e != cudaSuccess) throw CudaError(std::string(what) + ": " + cudaGetErrorString(e));
@@ -83,12 +84,24 @@ bool same_plan(const ConvPlan& p, const int dim[3], const int k[3]) {
     return true;
 }
 
-static const int kXYSizes[] = {32, 64, 128};
+static const int kXYSizes[] = {32, 64, 128, 256};
 static const int kZSizes[] = {16, 32, 64, 128, 256, 512};
 
+// x, y: windows up to 128 points (two 256-thread CTAs per SM: measured faster per output voxel than 256-point
+// windows at one 512-thread CTA per SM in spite of their smaller halo share, 31.35 vs 31.43 ms per iteration at
+// K = 31); 256-point windows only for kernels that do not fit 128, or on request (MVD_XMAX / MVD_YMAX = 256).
 static std::vector<AxisTile> plan_axes(const int dim[3], const int k[3], int d) {
-    if (d == 0) return plan_axis(dim[0], k[0], 4, kXYSizes, 3);
-    if (d == 1) return plan_axis(dim[1], k[1], 4, kXYSizes, 3);  // multiples of 4 rows: whole row rounds in inv_xy
+    if (d < 2) {
+        int n = 3;
+        if (const char* s = std::getenv(d == 0 ? "MVD_XMAX" : "MVD_YMAX")) {
+            const int mx = std::atoi(s);
+            n = 4;
+            while (n > 1 && mx > 0 && kXYSizes[n - 1] > mx) --n;
+        }
+        std::vector<AxisTile> t = plan_axis(dim[d], k[d], 4, kXYSizes, n);  // multiples of 4 rows: whole row rounds in inv_xy
+        if (t.empty() && n < 4) t = plan_axis(dim[d], k[d], 4, kXYSizes, 4);
+        return t;
+    }
     // MVD_ZMAX (tuning): largest z window.  Shorter windows make tiles small enough for a batch's
     // scratch to stay in L2 between the three kernels, at the price of more halo planes.
     int nz = 6;
@@ -111,6 +124,11 @@ std::unique_ptr<ConvPlan> make_plan(const int dim[3], const int k[3]) {
             throw std::invalid_argument("make_plan: kernel size " + std::to_string(k[d]) + " in dimension " + std::to_string(d) +
                                         " exceeds the largest supported FFT window");
     }
+    for (const auto& ty : ax[1])
+        for (const auto& tx : ax[0])
+            if (!xy_pair_supported(tx.b, ty.b))
+                throw std::invalid_argument("make_plan: kernel needs 256-point FFT windows in x and y at once (" + std::to_string(k[0]) + " x " +
+                                            std::to_string(k[1]) + "); a 256 x 256 plane exceeds the FFT window one SM can hold");
     std::map<std::vector<int>, size_t> index;
     for (const auto& tz : ax[2])
         for (const auto& ty : ax[1])
@@ -173,6 +191,7 @@ Device::Device(int id) : id_(id) {
                         std::to_string(prop.major) + std::to_string(prop.minor));
     MVD_CUDA(configure_conv_kernels());
     MVD_CUDA(configure_z_tma_kernels());
+    MVD_CUDA(configure_inv_ring_kernels());
     const double two_pi = 6.283185307179586476925286766559;
     for (int l = 0; l < 11; ++l) {
         const int n = 1 << l;
@@ -345,6 +364,13 @@ void partition_for_peers(ConvPlan& plan, const PeerTarget* peers, int n) {
 }
 
 // ---- convolution -----------------------------------------------------------------------
+static cudaError_t launch_inv(Device& dev, int bx, int by, int bz, int epilogue, const float2* buf, const Tile* d_tiles, int n_tiles, int max_nz,
+                              const EpilogueArgs& ep, cudaStream_t st) {
+    if (g_use_inv_ring.load() && inv_ring_supported(bx, by))
+        return launch_inv_ring(bz, epilogue, buf, d_tiles, n_tiles, max_nz, ep, dev.sm_count(), dev.twiddles(), st);
+    return launch_inv_xy(bx, by, bz, epilogue, buf, d_tiles, n_tiles, max_nz, ep, dev.twiddles(), st);
+}
+
 void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spec, const Volume& src, int epilogue,
                      const EpilogueArgs& ep, Scratch& scratch, cudaStream_t st, Profiler* prof) {
     const double epi_bytes = epilogue == EPI_STORE ? 4.0 : (epilogue == EPI_QUOTIENT ? 8.0 : (ep.weight ? 12.0 : 8.0));
@@ -421,16 +447,16 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
                 plain.peers = nullptr;
                 plain.n_peers = 0;
                 if (a > 0) {
-                    MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, buf, c.d_tiles + s, a, c.max_nz, plain, dev.twiddles(), ls));
+                    MVD_CUDA(launch_inv(dev, bx, by, bz, epilogue, buf, c.d_tiles + s, a, c.max_nz, plain, ls));
                     ++g_kernel_launches;
                 }
                 if (cnt - a > 0) {
-                    MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, buf + (size_t)a * te, c.d_tiles + s + a, cnt - a, c.max_nz, ep, dev.twiddles(), ls));
+                    MVD_CUDA(launch_inv(dev, bx, by, bz, epilogue, buf + (size_t)a * te, c.d_tiles + s + a, cnt - a, c.max_nz, ep, ls));
                     ++g_kernel_launches;
                 }
                 g_kernel_launches += 2;
             } else {
-                MVD_CUDA(launch_inv_xy(bx, by, bz, epilogue, buf, c.d_tiles + s, cnt, c.max_nz, ep, dev.twiddles(), ls));
+                MVD_CUDA(launch_inv(dev, bx, by, bz, epilogue, buf, c.d_tiles + s, cnt, c.max_nz, ep, ls));
                 g_kernel_launches += 3;
             }
             if (prof) prof->end(ls);

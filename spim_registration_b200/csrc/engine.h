@@ -23,6 +23,7 @@ void cuda_check(cudaError_t e, const char* what);
 extern std::atomic<long long> g_kernel_launches;
 // run-time switches between kernel generations (A/B measurements; mvdSetTuning / environment MVD_Z_TMA, MVD_INV_TMA)
 extern std::atomic<int> g_use_z_tma;
+extern std::atomic<int> g_use_inv_ring;
 
 // ---- planner ---------------------------------------------------------------------------
 struct AxisTile {

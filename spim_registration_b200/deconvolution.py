@@ -190,6 +190,12 @@ class MVDeconvolution:
             views.init(iterationType, numThreads)
         dev = self.data[0].device0 if device is None else device
         shape = self.data[0].getImage().shape
+        devs = list(self.data[0].deviceList) if device is None else [device]
+        if len(devs) > 1:
+            # several devices (MVDeconFFT.java:426-445: one thread per device): the volume is sharded over them behind
+            # one handle of the C ABI, one process (include/mvdecon.h, mvdCreateMulti)
+            self._run_multi(lib, devs, shape, numIterations, initialImage, directPath, debug, debugInterval)
+            return
         self._ctx = C.c_void_p()
         _lib.check(lib.mvdCreate(C.byref(self._ctx), dev, _lib.int3(shape[::-1]), None, None, None, self.lam, float(self.minValue)),
                    "mvdCreate")
@@ -241,6 +247,61 @@ class MVDeconvolution:
         finally:
             lib.mvdDestroy(self._ctx)
             self._ctx = None
+
+    def _run_multi(self, lib, devs, shape, numIterations, initialImage, directPath, debug, debugInterval):
+        kmax = [1, 1, 1]
+        for v in self.data:
+            for k in (v.getKernel1(), v.getKernel2()):
+                kmax = [max(a, b) for a, b in zip(kmax, k.shape[::-1])]
+        h = C.c_void_p()
+        _lib.check(lib.mvdCreateMulti(C.byref(h), (C.c_int * len(devs))(*devs), len(devs), _lib.int3(shape[::-1]), _lib.int3(kmax), self.lam,
+                                      float(self.minValue)), "mvdCreateMulti")
+        try:
+            for v in self.data:
+                w = v.getWeight()
+                wp, wc = (None, float(w)) if isinstance(w, float) else (w.ctypes.data_as(C.c_void_p), 1.0)
+                k1, k2 = v.getKernel1(), v.getKernel2()
+                _lib.check(lib.mvdMultiAddView(h, v.getImage().ctypes.data_as(C.c_void_p), wp, wc, k1.ctypes.data_as(_lib.c_float_p),
+                                               _lib.int3(k1.shape[::-1]), k2.ctypes.data_as(_lib.c_float_p), _lib.int3(k2.shape[::-1])), "mvdMultiAddView")
+            _lib.check(lib.mvdMultiSetDirectPath(h, int(bool(directPath))), "mvdMultiSetDirectPath")
+            self.directPath = None
+            self.bricks = []
+            for b in range(lib.mvdMultiNumBricks(h)):
+                d, off, dim = C.c_int(), (C.c_int * 3)(), (C.c_int * 3)()
+                _lib.check(lib.mvdMultiBrickInfo(h, b, C.byref(d), off, dim), "mvdMultiBrickInfo")
+                self.bricks.append((d.value, tuple(off), tuple(dim)))
+            if initialImage is not None:
+                init = np.ascontiguousarray(initialImage, dtype=F32)
+                _lib.check(lib.mvdMultiSetPsi(h, init.ctypes.data_as(C.c_void_p)), "mvdMultiSetPsi")
+                self.avg = None
+            else:
+                avg = C.c_double()
+                _lib.check(lib.mvdMultiInitPsiAverage(h, C.byref(avg)), "mvdMultiInitPsiAverage")
+                self.avg = avg.value
+            nv = self.numViews
+            n = numIterations * nv
+            s, m = (C.c_double * max(n, 1))(), (C.c_double * max(n, 1))()
+            self.debugStack = []
+            if debug:
+                for it in range(numIterations):
+                    s1, m1 = (C.c_double * nv)(), (C.c_double * nv)()
+                    _lib.check(lib.mvdMultiRunIterations(h, 1, s1, m1), "mvdMultiRunIterations")
+                    s[it * nv:(it + 1) * nv] = s1[:]
+                    m[it * nv:(it + 1) * nv] = m1[:]
+                    if it % max(1, debugInterval) == 0:
+                        snap = np.empty(shape, dtype=F32)
+                        _lib.check(lib.mvdMultiGetPsi(h, snap.ctypes.data_as(C.c_void_p)), "mvdMultiGetPsi")
+                        self.debugStack.append((it, snap))
+            else:
+                _lib.check(lib.mvdMultiRunIterations(h, numIterations, s, m), "mvdMultiRunIterations")
+            self.sumChange = np.array(s[:n]).reshape(numIterations, nv)
+            self.maxChange = np.array(m[:n]).reshape(numIterations, nv)
+            self.i = numIterations
+            _lib.check(lib.mvdMultiMaskNeverUpdated(h), "mvdMultiMaskNeverUpdated")
+            self.psi = np.empty(shape, dtype=F32)
+            _lib.check(lib.mvdMultiGetPsi(h, self.psi.ctypes.data_as(C.c_void_p)), "mvdMultiGetPsi")
+        finally:
+            lib.mvdDestroyMulti(h)
 
     def getPsi(self):
         return self.psi

@@ -57,6 +57,11 @@ def _kernel(shape, seed):
     ((96, 200, 260), (31, 31, 31)),
     ((300, 36, 40), (31, 5, 7)),     # z needs the 512-point window
     ((530, 20, 24), (15, 3, 3)),     # z = 512-point window + a short one
+    ((80, 150, 170), (63, 63, 63)),  # transformed PSFs grow with the view's affine (ExtractPSF.java:331-345)
+    ((120, 60, 200), (95, 31, 95)),
+    ((20, 40, 300), (5, 7, 151)),    # wider than a 128-point window allows: 256-point windows along x
+    ((24, 280, 60), (3, 201, 9)),    # ... along y
+    ((300, 30, 40), (255, 3, 5)),    # ... 512 points along z
 ])
 @pytest.mark.parametrize("mode", ["zero", "const", "mirror"])
 def test_convolution_matches_oracle(m, o, shape, ks, mode):
@@ -124,8 +129,8 @@ def test_legacy_failure_leaves_block_untouched(m, lib):
     code, msg = L.last_error()
     assert code != 0 and "device" in msg
     np.testing.assert_array_equal(f, before)
-    kbig = np.ones((3, 3, 200), np.float32)  # x kernel wider than the largest xy window
-    kd3 = (C.c_int * 3)(3, 3, 200)
+    kbig = np.ones((3, 3, 300), np.float32)  # x kernel wider than the largest xy window
+    kd3 = (C.c_int * 3)(3, 3, 300)
     lib.convolution3DfftCUDAInPlace(f.ctypes.data_as(L.c_float_p), dim, kbig.ctypes.data_as(L.c_float_p), kd3, 0)
     code, msg = L.last_error()
     assert code != 0 and "window" in msg
@@ -426,10 +431,11 @@ def test_fused_ghost_exchange_is_bit_identical_to_copies(m, o, direct):
 
 
 # ---- direct separable path and the separable-convolution hook -------------------------------------
-@pytest.mark.parametrize("size,shape", [(7, (20, 33, 150)), (15, (40, 70, 260)), (31, (35, 66, 140)), (63, (70, 80, 90))])
+@pytest.mark.parametrize("size,shape", [(7, (20, 33, 150)), (15, (40, 70, 260)), (31, (35, 66, 140)), (63, (70, 80, 90)), (127, (140, 150, 160))])
 @pytest.mark.parametrize("oob", [0, 1, 2])
 def test_separable_hook_matches_oracle(m, o, size, shape, oob):
-    """convolve_N (CUDASeparableConvolution.java:13-17): N <= 31 direct kernels, 63 through the FFT engine."""
+    """convolve_N (CUDASeparableConvolution.java:13-17; convolve_127 is called at CUDASeparableConvolutionFunctions.java:191):
+    N <= 31 direct kernels, 63 and 127 through the FFT engine axis by axis."""
     rng = np.random.default_rng(size + oob)
     f = rng.random(shape, dtype=np.float32) + np.float32(0.1)
     ks = [np.zeros(size, np.float32) for _ in range(3)]
@@ -465,8 +471,6 @@ def test_separable_hook_partial_axes_gauss_and_refusals(m, o):
     assert rel_l2(got2, o.separable_convolve(img2[None], k2[0], k2[1], None, "clamp")[0]) <= CONV_TOL
     # refusals leave the image untouched and return false
     before = f.copy()
-    big = np.full(127, 1 / 127, np.float32)
-    assert not cuda.convolve(127, f, big, big, big, 50, 40, 30, True, True, True, 2, 0.0, 0)
     assert not cuda.convolve(7, f, k[:7].copy(), None, None, 50, 40, 30, True, False, False, 5, 0.0, 0)  # bad out-of-bounds code
     assert not cuda.convolve(7, f, k[:7].copy(), None, None, 50, 40, 30, True, False, False, 0, 0.0, 99)  # bad device
     np.testing.assert_array_equal(f, before)
@@ -666,3 +670,68 @@ def test_extract_and_transform_psf_match_oracle(m, o):
         np.testing.assert_allclose(t, rt, rtol=0, atol=2e-7)
     psf = e.extractNextImg(img, _registration(45.0, 2.0, (0, 0, 0)), locs, size)
     assert psf.shape == e.pointSpreadFunctions[0].shape and len(e.originalPSFs) == 1
+
+
+# ---- several devices behind one handle of the C ABI (mvdCreateMulti), one process ------------------------------------
+def _multi_dataset(o):
+    from spim_registration_b200 import synthetic
+    shape, V = (44, 56, 72), 3
+    ds = _dataset(o, shape, V, (9, 7, 11), seed=9)
+    weights = synthetic.blending_weights(shape, V)
+    return shape, V, ds, weights
+
+
+@pytest.mark.parametrize("ndev", [2, 4, 8])
+def test_multi_device_handle_on_one_gpu_equals_single_context(m, o, ndev):
+    """mvdCreateMulti with the same device named several times: bricks, peer attachment, the per-device worker threads
+    and the event-based neighbour barrier are exactly what several GPUs run (MVDeconFFT.java:426-445 drives its devices
+    from one process too); the result must equal the oracle and the single-context run, statistics included."""
+    shape, V, ds, weights = _multi_dataset(o)
+    k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
+    ref, stats, avg = o.run_deconvolution(ds["imgs"], weights, k1, k2, 3, 0.006)
+    single = m.MVDeconvolution(_views(m, ds["imgs"], weights, ds["psfs"]), "EFFICIENT_BAYESIAN", 3, 0.006)
+    inp = m.MVDeconInput()
+    for img, w, p in zip(ds["imgs"], weights, ds["psfs"]):
+        inp.add(m.MVDeconFFT(img, w, p, deviceList=[0] * ndev))
+    multi = m.MVDeconvolution(inp, "EFFICIENT_BAYESIAN", 3, 0.006)
+    assert len(multi.bricks) == ndev
+    assert abs(multi.avg - avg) <= 1e-9 * abs(avg)
+    assert rel_l2(multi.getPsi(), ref) <= LOOP_TOL
+    assert rel_l2(multi.getPsi(), single.getPsi()) <= 2e-6
+    rs = np.array([[s for s, _ in row] for row in stats])
+    np.testing.assert_allclose(multi.sumChange, rs, rtol=STAT_SUM_TOL)
+    np.testing.assert_allclose(multi.maxChange, np.array([[x for _, x in row] for row in stats]), rtol=STAT_MAX_TOL)
+
+
+def test_multi_device_handle_initial_image_and_debug_stack(m, o):
+    """mvdMultiSetPsi fills the bricks' ghost layers from the caller's volume; stepping one iteration at a time
+    (debug stack) keeps the neighbour events consistent across calls."""
+    shape, V, ds, weights = _multi_dataset(o)
+    k1, k2 = o.init_kernels(ds["psfs"], "INDEPENDENT", 8)
+    psi0 = (np.random.default_rng(4).random(shape, dtype=np.float32) + np.float32(0.2))
+    ref_it = []
+    ref, _, _ = o.run_deconvolution(ds["imgs"], weights, k1, k2, 3, 0.006, psi0=psi0, on_iteration=lambda i, p: ref_it.append(p.copy()))
+    inp = m.MVDeconInput()
+    for img, w, p in zip(ds["imgs"], weights, ds["psfs"]):
+        inp.add(m.MVDeconFFT(img, w, p, deviceList=[0, 0, 0, 0]))
+    multi = m.MVDeconvolution(inp, "INDEPENDENT", 3, 0.006, initialImage=psi0, debug=True)
+    for it, snap in multi.debugStack:
+        assert rel_l2(snap, ref_it[it]) <= LOOP_TOL
+    assert rel_l2(multi.getPsi(), ref) <= LOOP_TOL
+
+
+def test_multi_device_handle_on_real_devices(m, o, lib):
+    """The same through 2 (4, 8) distinct GPUs when the box has them; skipped on a single-GPU box."""
+    n = lib.getNumDevicesCUDA()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    ndev = 8 if n >= 8 else (4 if n >= 4 else 2)
+    shape, V, ds, weights = _multi_dataset(o)
+    k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
+    ref, stats, avg = o.run_deconvolution(ds["imgs"], weights, k1, k2, 3, 0.006)
+    inp = m.MVDeconInput()
+    for img, w, p in zip(ds["imgs"], weights, ds["psfs"]):
+        inp.add(m.MVDeconFFT(img, w, p, deviceList=list(range(ndev))))
+    multi = m.MVDeconvolution(inp, "EFFICIENT_BAYESIAN", 3, 0.006)
+    assert sorted(b[0] for b in multi.bricks) == list(range(ndev))
+    assert rel_l2(multi.getPsi(), ref) <= LOOP_TOL
