@@ -34,6 +34,8 @@ CONFIGS = {
             shape=(512, 1024, 1024), k=31, psftype="EFFICIENT_BAYESIAN", kind="blob", extracted=False, dense_weights=True),
     4: dict(name="cfg4: 6-view 1024x1024x512 independent RL with per-view weight images", views=6, shape=(512, 1024, 1024), k=31,
             psftype="INDEPENDENT", kind="blob", extracted=False, dense_weights=True),
+    5: dict(name="cfg5: 8-view 2048x2048x1024 volume sharded by bricks across 8 GPUs (2x2x2), PSF 31^3, efficient Bayesian, per-view blending weights",
+            views=8, shape=(1024, 2048, 2048), k=31, psftype="EFFICIENT_BAYESIAN", kind="blob", extracted=False, dense_weights=True, min_gpus=8),
     # debugging size
     0: dict(name="cfg0: 3-view 96x160x192 debug volume, PSF 15^3", views=3, shape=(96, 160, 192), k=15,
             psftype="EFFICIENT_BAYESIAN", kind="blob", extracted=False, dense_weights=True),
@@ -144,7 +146,7 @@ def device_convolve(lib, t_src, kernel, mode, value=0.0):
     return out
 
 
-def gen_dataset_device(cfg, lib, psfs, sub=None):
+def gen_dataset_device(cfg, lib, psfs, sub=None, seed_offset=0):
     """Synthetic views generated on the device (not timed, not the product): sparse sources blurred
     into blobs/beads, blurred by every view's PSF, Poisson-like noise, a no-data slab per view,
     cosine blending weights normalised over the views.  `sub` = (offset_zyx, dim_zyx) of a brick."""
@@ -152,8 +154,17 @@ def gen_dataset_device(cfg, lib, psfs, sub=None):
     from spim_registration_b200 import synthetic
     dev = torch.device("cuda", local_device())
     Z, Y, X = cfg["shape"]
+    if sub is not None and float(Z) * Y * X > 2.0e9:
+        # a volume that does not fit one GPU (cfg5): every rank generates its own brick as a small volume of the same
+        # statistics (sources, blur, noise); the bricks are not continuous across their faces, which a throughput
+        # measurement does not need
+        (oz, oy, ox), (dz, dy, dx) = sub
+        local = dict(cfg, shape=(dz, dy, dx))
+        imgs, _ = gen_dataset_device(dict(local, dense_weights=False), lib, psfs, None, seed_offset=1 + ox + 7 * oy + 13 * oz)
+        weights = virtual_weights_device(cfg, lib, sub) if cfg["dense_weights"] else [None] * cfg["views"]
+        return imgs, weights
     g = torch.Generator(device=dev)
-    g.manual_seed(synthetic.SEED0 + 3)
+    g.manual_seed(synthetic.SEED0 + 3 + seed_offset)
     dens = 1.0 / 4096 if cfg["kind"] == "blob" else 1.0 / 32768
     src = (torch.rand((Z, Y, X), generator=g, device=dev) < dens).float() * (0.2 + 0.8 * torch.rand((Z, Y, X), generator=g, device=dev))
     sig = 2.5 if cfg["kind"] == "blob" else 0.8
@@ -454,84 +465,145 @@ def run_ours(args, cfg):
     if parity is not None:
         line["parity_multi_gpu"] = parity
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_sample(cfg, k1, k2, budget_s=args.cpu_seconds)
+        line["cpu_baseline"] = cpu_sample(cfg, k1, k2)
     emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
 # ------------------------------------------------------------------------------------------
-def cpu_sample(cfg, k1, k2, budget_s=20.0, steps=1):
-    """CPU port of the reference's CPU path (oracle/cpu_baseline.py) on a bounded sample: a crop of
-    the workload with the reference's 256^3 blocks (64^3 for tiny configs), all views, `steps`
-    iterations; throughput scaled per voxel.  numpy-generated inputs of the same statistics."""
+def run_single_process(args, cfg):
+    """--single-process: N GPUs of the box driven from ONE process through the multi-device handle of the C ABI
+    (mvdCreateMulti: worker thread per device, event-based neighbour barrier, no torch.distributed / NCCL) -- how
+    the reference's Java host would use several devices (MVDeconFFT.java:426-445).  Host buffers in, host buffers out."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import torch
+    import spim_registration_b200 as m
+    from spim_registration_b200 import _lib as L
+    lib = m.load()
+    n = args.gpus
+    torch.cuda.set_device(0)
+    Z, Y, X = cfg["shape"]
+    V = cfg["views"]
+    nvox = float(X) * Y * Z
+    psfs, k1, k2 = prepare_kernels(cfg)
+    imgs, weights = gen_dataset_device(cfg, lib, psfs, None)
+    h_imgs = [i.cpu().numpy() for i in imgs]
+    h_w = [w.cpu().numpy() if w is not None else None for w in weights]
+    del imgs, weights
+    torch.cuda.empty_cache()
+    kmax = [max(max(k.shape[::-1][d] for k in k1), max(k.shape[::-1][d] for k in k2)) for d in range(3)]
+    t0 = time.perf_counter()
+    h = C.c_void_p()
+    L.check(lib.mvdCreateMulti(C.byref(h), (C.c_int * n)(*range(n)), n, L.int3((X, Y, Z)), L.int3(kmax), LAMBDA, 1e-4), "mvdCreateMulti")
+    for v in range(V):
+        wp, wc = (h_w[v].ctypes.data_as(C.c_void_p), 1.0) if h_w[v] is not None else (None, 1.0 / V)
+        L.check(lib.mvdMultiAddView(h, h_imgs[v].ctypes.data_as(C.c_void_p), wp, wc, k1[v].ctypes.data_as(L.c_float_p), L.int3(k1[v].shape[::-1]),
+                                    k2[v].ctypes.data_as(L.c_float_p), L.int3(k2[v].shape[::-1])), "mvdMultiAddView")
+    avg = C.c_double()
+    L.check(lib.mvdMultiInitPsiAverage(h, C.byref(avg)), "mvdMultiInitPsiAverage")
+    t1 = time.perf_counter()
+    L.check(lib.mvdMultiRunIterations(h, args.warmup, None, None), "mvdMultiRunIterations")
+    launches0 = lib.mvdKernelLaunchCount()
+    t2 = time.perf_counter()
+    L.check(lib.mvdMultiRunIterations(h, args.steps, None, None), "mvdMultiRunIterations")   # returns when every device has finished
+    t3 = time.perf_counter()
+    launches = lib.mvdKernelLaunchCount() - launches0
+    L.check(lib.mvdMultiMaskNeverUpdated(h), "mvdMultiMaskNeverUpdated")
+    psi = np.empty((Z, Y, X), np.float32)
+    L.check(lib.mvdMultiGetPsi(h, psi.ctypes.data_as(C.c_void_p)), "mvdMultiGetPsi")
+    t4 = time.perf_counter()
+    lib.mvdDestroyMulti(h)
+    ms = (t3 - t2) * 1e3
+    e2e_s = (t1 - t0) + (t3 - t2) + (t4 - t3)
+    emit({"metric": "Gvoxel-iterations/sec (all views)", "value": nvox * args.steps / (ms * 1e-3) / 1e9, "unit": "Gvoxel-iterations/s", "n_gpus": n,
+          "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+          "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "single-process C ABI (mvdCreateMulti)",
+          "config": {"workload": cfg["name"], "views": V, "volume_xyz": [X, Y, Z], "psf": cfg["k"], "iteration_type": cfg["psftype"], "lambda": LAMBDA,
+                     "step": "one iteration over all views", "halo": "epilogue stores into peer ghost layers (NVLink) + per-step neighbour events",
+                     "timing": "host clock around mvdMultiRunIterations, which returns after every device's stream has drained"},
+          "e2e": {"value": nvox * args.steps / e2e_s / 1e9, "unit": "Gvoxel-iterations/s", "h2d_bytes_per_step": sum(a.nbytes for a in h_imgs + [w for w in h_w if w is not None]) / args.steps,
+                  "d2h_bytes_per_step": psi.nbytes / args.steps, "seconds": e2e_s, "includes": "context creation, H2D of views and weights from pageable host arrays, spectra, psi init, iterations, mask, D2H"},
+          "gpu_launches": int(launches), "psi_mean": float(psi.mean(dtype=np.float64))})
+
+
+# ------------------------------------------------------------------------------------------
+def reference_crop(cfg, blocks_xyz=(2, 2, 1)):
+    """The bounded sample of the workload the CPU arm runs: a crop of blocks_xyz effective regions of the reference's
+    256^3 blocks (64^3 for tiny configs) -- 452 x 452 x 226 voxels at K = 31 -- the same at every N and in every step."""
+    Z, Y, X = cfg["shape"]
+    block = [256, 256, 256] if min(cfg["shape"]) >= 256 else [64, 64, 64]
+    e = block[0] - cfg["k"] + 1
+    crop = [min(n, e * b) for n, b in zip((Z, Y, X), blocks_xyz[::-1])]
+    return block, crop
+
+
+def cpu_sample(cfg, k1, k2, budget_s=20.0, steps=1, crop=None):
+    """CPU port of the reference's CPU path (oracle/cpu_baseline.py) on a bounded sample: a fixed crop of the workload
+    (reference_crop) in the reference's blocks, all views, `steps` iterations; throughput per voxel.  numpy-generated
+    inputs of the same statistics.  `crop` = (z, y, x) overrides the sample (the whole volume for --full-iteration)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import cpu_baseline as cb
     V = cfg["views"]
-    Z, Y, X = cfg["shape"]
     cores = cb.host_threads()
-    block = [256, 256, 256] if min(cfg["shape"]) >= 256 else [64, 64, 64]
-    e = block[0] - cfg["k"] + 1
-    # sample = a whole number of effective blocks; grow while the estimated time fits the budget
-    crop = [min(n, e) for n in (Z, Y, X)]
+    block, default_crop = reference_crop(cfg)
+    crop = list(crop or default_crop)
     rng = np.random.default_rng(7)
-    def make(c):
-        imgs = [(rng.random(c, dtype=np.float32) * 0.9 + 0.05) for _ in range(V)]
-        w = [np.full(c, 1.0 / V, np.float32) if cfg["dense_weights"] else np.float32(1.0 / V) for _ in range(V)]
-        return imgs, w
-    imgs, w = make(crop)
+    imgs = [(rng.random(crop, dtype=np.float32) * 0.9 + 0.05) for _ in range(V)]
+    w = [np.full(crop, 1.0 / V, np.float32) if cfg["dense_weights"] else np.float32(1.0 / V) for _ in range(V)]
     psi = np.full(crop, 0.3, np.float32)
-    _, t = cb.run_iterations(imgs, w, k1, k2, 1, LAMBDA, block, psi, cores)  # also warms the FFT plans
-    vox = float(np.prod(crop))
-    nblk = max(1, int(budget_s / max(t, 1e-3)))
-    if nblk >= 2:
-        mult = [1, 1, 1]
-        ax = 2
-        while np.prod(mult) * 2 <= nblk and any(crop[a] * mult[a] * 2 <= (Z, Y, X)[a] for a in range(3)):
-            for _ in range(3):
-                if crop[ax] * mult[ax] * 2 <= (Z, Y, X)[ax]:
-                    mult[ax] *= 2
-                    break
-                ax = (ax - 1) % 3
-            ax = (ax - 1) % 3
-        crop = [crop[a] * mult[a] for a in range(3)]
-        imgs, w = make(crop)
-        psi = np.full(crop, 0.3, np.float32)
-        _, t = cb.run_iterations(imgs, w, k1, k2, steps, LAMBDA, block, psi, cores)
-        vox = float(np.prod(crop)) * steps
+    _, t = cb.run_iterations(imgs, w, k1, k2, steps, LAMBDA, block, psi, cores)
+    vox = float(np.prod(crop)) * steps
     return {"value": vox / t / 1e9, "unit": "Gvoxel-iterations/s", "cores": cores, "kind": "port",
             "sample": "%d view(s), crop %dx%dx%d (xyz) of the workload in %d^3 blocks, %d iteration(s), %.1f s, scipy pocketfft float32 with %d workers"
                       % (V, crop[2], crop[1], crop[0], block[0], steps, t, cores), "seconds": t}
 
 
 def run_reference(args, cfg):
-    """--impl reference: the CPU port on the host cores (rank 0 only)."""
+    """--impl reference: the CPU port on the host cores (rank 0 only; the other ranks leave at once).  Every step runs
+    the same fixed crop with all host threads -- thread count and affinity are set here, so that the figure does not
+    depend on how the process was launched (torchrun exports OMP_NUM_THREADS=1 to its workers)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
+    ncpu = os.cpu_count() or 1
+    try:
+        os.sched_setaffinity(0, range(ncpu))
+    except (AttributeError, OSError):
+        pass
+    for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[var] = str(ncpu)
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle_np as o
     from spim_registration_b200 import synthetic
     psfs = synthetic.make_psfs(cfg["views"], (cfg["k"],) * 3, cfg["extracted"])
     k1, k2 = o.init_kernels(psfs, cfg["psftype"], 8)
-    per_step = max(5.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
     vals, secs, sample = [], [], None
     for i in range(args.warmup + args.steps):
-        r = cpu_sample(cfg, k1, k2, budget_s=per_step)
+        r = cpu_sample(cfg, k1, k2)
         if i >= args.warmup:
             vals.append(r["value"])
             secs.append(r["seconds"])
         sample = r
     value = float(np.mean(vals))
     Z, Y, X = cfg["shape"]
+    full = None
+    if args.full_iteration:   # one iteration of the WHOLE workload, once, beside the crop figure
+        r = cpu_sample(cfg, k1, k2, crop=(Z, Y, X))
+        full = {"value": r["value"], "seconds": r["seconds"], "sample": r["sample"]}
     line = {"impl": "reference", "metric": "Gvoxel-iterations/sec (all views)", "value": value, "unit": "Gvoxel-iterations/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": float(X) * Y * Z / (value * 1e9) * 1e3, "higher_is_better": True, "scaling": "strong",
+            "ms_per_step": float(np.mean(secs)) * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": cfg["name"], "views": cfg["views"], "volume_xyz": [X, Y, Z], "psf": cfg["k"],
-                       "iteration_type": cfg["psftype"], "lambda": LAMBDA, "step": "bounded sample of one iteration over all views, scaled per voxel"},
+                       "iteration_type": cfg["psftype"], "lambda": LAMBDA,
+                       "step": "one iteration over all views on a fixed crop of the workload (see cpu_baseline.sample); value = crop voxels / time, ms_per_step = the time of the crop",
+                       "spread": {"min": float(np.min(vals)), "max": float(np.max(vals))}},
             "cpu_baseline": {"value": value, "unit": "Gvoxel-iterations/s", "cores": sample["cores"], "kind": "port", "sample": sample["sample"]},
             "e2e": {"value": value, "unit": "Gvoxel-iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    if full:
+        line["full_iteration"] = full
     emit(line)
 
 
@@ -543,13 +615,21 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--single-process", action="store_true", help="drive --gpus N devices from one process through mvdCreateMulti")
     ap.add_argument("--no-parity", action="store_true", help="skip the multi-GPU parity leg (world > 1)")
     ap.add_argument("--cpu-seconds", type=float, default=20.0)
+    ap.add_argument("--full-iteration", action="store_true", help="--impl reference: also time one iteration of the whole workload")
     args = ap.parse_args()
     cfg = CONFIGS[args.config]
     quiet_stdout()
+    if cfg.get("min_gpus", 1) > max(args.gpus, int(os.environ.get("WORLD_SIZE", "1"))) and args.impl == "ours":
+        if int(os.environ.get("RANK", "0")) == 0:
+            emit({"error": "%s needs %d GPUs (%.0f GB resident)" % (cfg["name"], cfg["min_gpus"], (2 * cfg["views"] + 2) * float(np.prod(cfg["shape"])) * 4 / 1e9)})
+        sys.exit(2)
     if args.impl == "reference":
         run_reference(args, cfg)
+    elif args.single_process:
+        run_single_process(args, cfg)
     else:
         run_ours(args, cfg)
 

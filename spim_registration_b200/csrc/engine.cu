@@ -16,7 +16,7 @@ static int env_flag(const char* name, int dflt) {
     return s ? std::atoi(s) : dflt;
 }
 std::atomic<int> g_use_z_tma{env_flag("MVD_Z_TMA", 0)};
-std::atomic<int> g_use_inv_ring{env_flag("MVD_INV_RING", 1)};
+std::atomic<int> g_use_inv_ring{env_flag("MVD_INV_RING", 0)};
 
 void cuda_check(cudaError_t e, const char* what) {
     if (e != cudaSuccess) throw CudaError(std::string(what) + ": " + cudaGetErrorString(e));
@@ -364,10 +364,12 @@ void partition_for_peers(ConvPlan& plan, const PeerTarget* peers, int n) {
 }
 
 // ---- convolution -----------------------------------------------------------------------
-static cudaError_t launch_inv(Device& dev, int bx, int by, int bz, int epilogue, const float2* buf, const Tile* d_tiles, int n_tiles, int max_nz,
-                              const EpilogueArgs& ep, cudaStream_t st) {
-    if (g_use_inv_ring.load() && inv_ring_supported(bx, by))
-        return launch_inv_ring(bz, epilogue, buf, d_tiles, n_tiles, max_nz, ep, dev.sm_count(), dev.twiddles(), st);
+static cudaError_t launch_inv(Device& dev, int bx, int by, int bz, int epilogue, const float2* buf, const Tile* d_tiles, int n_tiles, int zlo,
+                              int max_nz, const EpilogueArgs& ep, cudaStream_t st) {
+    if (g_use_inv_ring.load() && inv_ring_supported(bx, by)) {
+        const cudaError_t e = launch_inv_ring(bz, epilogue, buf, d_tiles, n_tiles, zlo, max_nz, ep, dev.sm_count(), dev.twiddles(), st);
+        if (e != cudaErrorNotSupported) return e;
+    }
     return launch_inv_xy(bx, by, bz, epilogue, buf, d_tiles, n_tiles, max_nz, ep, dev.twiddles(), st);
 }
 
@@ -433,8 +435,9 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
             if (prof) prof->begin(0, cnt * ((double)bx * by * bz * 4.0 + pe * bz * 8.0), ls);
             MVD_CUDA(launch_fwd_xy(bx, by, bz, src, c.d_tiles + s, cnt, buf, dev.twiddles(), ls));
             if (prof) { prof->end(ls); prof->begin(1, cnt * pe * bz * 8.0 + pe * bz * 8.0 + nz_sum * pe * 8.0, ls); }
+            const int zlo = c.tiles[s].e[2] - c.tiles[s].o[2];  // the same for every tile of a plan
             if (g_use_z_tma.load() && z_tma_supported(bz))
-                MVD_CUDA(launch_z_pass_tma(bx, by, bz, buf, spec.per_class[ci], cnt, c.tiles[s].e[2] - c.tiles[s].o[2], c.max_nz, dev.sm_count(),
+                MVD_CUDA(launch_z_pass_tma(bx, by, bz, buf, spec.per_class[ci], cnt, zlo, c.max_nz, dev.sm_count(),
                                            dev.twiddles(), ls));
             else
                 MVD_CUDA(launch_z_pass(bx, by, bz, 1, buf, spec.per_class[ci], c.d_tiles + s, cnt, 1.f, dev.twiddles(), ls));
@@ -447,16 +450,16 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
                 plain.peers = nullptr;
                 plain.n_peers = 0;
                 if (a > 0) {
-                    MVD_CUDA(launch_inv(dev, bx, by, bz, epilogue, buf, c.d_tiles + s, a, c.max_nz, plain, ls));
+                    MVD_CUDA(launch_inv(dev, bx, by, bz, epilogue, buf, c.d_tiles + s, a, zlo, c.max_nz, plain, ls));
                     ++g_kernel_launches;
                 }
                 if (cnt - a > 0) {
-                    MVD_CUDA(launch_inv(dev, bx, by, bz, epilogue, buf + (size_t)a * te, c.d_tiles + s + a, cnt - a, c.max_nz, ep, ls));
+                    MVD_CUDA(launch_inv(dev, bx, by, bz, epilogue, buf + (size_t)a * te, c.d_tiles + s + a, cnt - a, zlo, c.max_nz, ep, ls));
                     ++g_kernel_launches;
                 }
                 g_kernel_launches += 2;
             } else {
-                MVD_CUDA(launch_inv(dev, bx, by, bz, epilogue, buf, c.d_tiles + s, cnt, c.max_nz, ep, ls));
+                MVD_CUDA(launch_inv(dev, bx, by, bz, epilogue, buf, c.d_tiles + s, cnt, zlo, c.max_nz, ep, ls));
                 g_kernel_launches += 3;
             }
             if (prof) prof->end(ls);

@@ -735,3 +735,29 @@ def test_multi_device_handle_on_real_devices(m, o, lib):
     multi = m.MVDeconvolution(inp, "EFFICIENT_BAYESIAN", 3, 0.006)
     assert sorted(b[0] for b in multi.bricks) == list(range(ndev))
     assert rel_l2(multi.getPsi(), ref) <= LOOP_TOL
+
+
+# ---- the TMA kernel generations (off by default: measured slower) stay correct ---------------------
+@pytest.mark.parametrize("switch", ["z_tma", "inv_ring"])
+def test_tma_kernels_match_oracle_and_default_kernels(m, o, lib, switch):
+    """z pass with bulk-tensor loads / stores and the inverse xy ring kernel fed by bulk-tensor loads: same results as
+    the register-loading kernels (the arithmetic is the same, only the data movement differs) and as the oracle."""
+    from spim_registration_b200 import synthetic
+    f, k = _rand((300, 150, 260), 31), _kernel((31, 31, 31), 32)       # 512-point z window, two 128-windows in x and y
+    ref = o.convolve_extended(f, k, "mirror")
+    base = m.convolve(f, k, "mirror")
+    shape, V = (140, 112, 120), 2
+    ds = _dataset(o, shape, V, (15, 15, 15), seed=11)
+    weights = synthetic.blending_weights(shape, V)
+    k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
+    loop_ref, _, _ = o.run_deconvolution(ds["imgs"], weights, k1, k2, 2, 0.006)
+    prev = lib.mvdSetTuning(switch.encode(), 1)
+    try:
+        assert prev in (0, 1)
+        got = m.convolve(f, k, "mirror")
+        dec = m.MVDeconvolution(_views(m, ds["imgs"], weights, ds["psfs"]), "EFFICIENT_BAYESIAN", 2, 0.006, directPath=False)
+    finally:
+        lib.mvdSetTuning(switch.encode(), prev)
+    assert rel_l2(got, ref) <= CONV_TOL
+    assert rel_l2(got, base) <= 1e-7
+    assert rel_l2(dec.getPsi(), loop_ref) <= LOOP_TOL
