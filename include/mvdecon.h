@@ -308,8 +308,9 @@ long long mvdDivideIntoBlocks(const long long* imgSize, const long long* kernelS
 long long mvdKernelLaunchCount(void);
 
 /* Process-wide switches between kernel generations, for A/B measurements and tests (defaults: the faster one).
- *   "z_tma"   1 = z pass with TMA bulk-tensor loads / stores (z_tma_kernels.cu), 0 = register-loading z pass
- *   "inv_tma" 1 = inverse xy pass fed by bulk copies into a shared-memory ring, 0 = register-loading kernel
+ *   "z_tma"   1 = z pass with TMA bulk-tensor loads / stores (z_tma_kernels.cu), 0 = register-loading z pass (default)
+ *   "inv_ring" 1 = inverse xy pass fed by bulk-tensor loads into a shared-memory ring, 0 = register-loading kernel (default)
+ *   "z_warp"  1 = z pass with warp-local 512-point lines behind swizzled bulk-tensor loads / stores (default), 0 = off
  * Returns the previous value, or -1 for an unknown name. */
 int mvdSetTuning(const char* name, int value);
 

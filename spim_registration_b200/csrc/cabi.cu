@@ -94,6 +94,7 @@ extern "C" int mvdSetTuning(const char* name, int value) {
     if (!name) return -1;
     if (std::strcmp(name, "z_tma") == 0) return g_use_z_tma.exchange(value);
     if (std::strcmp(name, "inv_ring") == 0) return g_use_inv_ring.exchange(value);
+    if (std::strcmp(name, "z_warp") == 0) return g_use_z_warp.exchange(value);
     return -1;
 }
 

@@ -17,6 +17,7 @@ static int env_flag(const char* name, int dflt) {
 }
 std::atomic<int> g_use_z_tma{env_flag("MVD_Z_TMA", 0)};
 std::atomic<int> g_use_inv_ring{env_flag("MVD_INV_RING", 0)};
+std::atomic<int> g_use_z_warp{env_flag("MVD_Z_WARP", 1)};
 
 void cuda_check(cudaError_t e, const char* what) {
     if (e != cudaSuccess) throw CudaError(std::string(what) + ": " + cudaGetErrorString(e));
@@ -160,6 +161,8 @@ std::unique_ptr<ConvPlan> make_plan(const int dim[3], const int k[3]) {
 KernelSpectra::~KernelSpectra() {
     for (auto* p : per_class)
         if (p) cudaFree(p);
+    for (auto* p : per_class_t)
+        if (p) cudaFree(p);
 }
 
 // ---- device ----------------------------------------------------------------------------
@@ -192,6 +195,7 @@ Device::Device(int id) : id_(id) {
     MVD_CUDA(configure_conv_kernels());
     MVD_CUDA(configure_z_tma_kernels());
     MVD_CUDA(configure_inv_ring_kernels());
+    MVD_CUDA(configure_z_warp_kernels());
     const double two_pi = 6.283185307179586476925286766559;
     for (int l = 0; l < 11; ++l) {
         const int n = 1 << l;
@@ -312,6 +316,15 @@ std::unique_ptr<KernelSpectra> build_spectra(Device& dev, const ConvPlan& plan, 
         const float scale = (float)(1.0 / (4.0 * (double)bx * (double)by * (double)bz));
         MVD_CUDA(launch_z_pass(bx, by, bz, 0, d_spec, nullptr, d_tile + ci, 1, scale, dev.twiddles(), st));
         g_kernel_launches += 3;
+        float2* d_spec_t = nullptr;
+        if (z_warp_supported(bz) && plane_elems(bx, by) % 16 == 0) {
+            MVD_CUDA(cudaMalloc(&d_spec_t, tile_scratch_elems(bx, by, bz) * sizeof(float2)));
+            spec->per_class_t.push_back(d_spec_t);
+            MVD_CUDA(launch_transpose_spectrum(d_spec, d_spec_t, (int)plane_elems(bx, by), bz, st));
+            ++g_kernel_launches;
+        } else {
+            spec->per_class_t.push_back(nullptr);
+        }
     }
     MVD_CUDA(cudaStreamSynchronize(st));  // kernel_host and `tiles` may go away on return
     return spec;
@@ -436,7 +449,16 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
             MVD_CUDA(launch_fwd_xy(bx, by, bz, src, c.d_tiles + s, cnt, buf, dev.twiddles(), ls));
             if (prof) { prof->end(ls); prof->begin(1, cnt * pe * bz * 8.0 + pe * bz * 8.0 + nz_sum * pe * 8.0, ls); }
             const int zlo = c.tiles[s].e[2] - c.tiles[s].o[2];  // the same for every tile of a plan
-            if (g_use_z_tma.load() && z_tma_supported(bz))
+            bool z_done = false;
+            if (g_use_z_warp.load() && z_warp_supported(bz) && spec.per_class_t[ci]) {
+                const cudaError_t e = launch_z_pass_warp(bx, by, bz, buf, spec.per_class_t[ci], cnt, zlo, c.max_nz, dev.sm_count(), dev.twiddles(), ls);
+                if (e != cudaErrorNotSupported) {
+                    MVD_CUDA(e);
+                    z_done = true;
+                }
+            }
+            if (z_done) {
+            } else if (g_use_z_tma.load() && z_tma_supported(bz))
                 MVD_CUDA(launch_z_pass_tma(bx, by, bz, buf, spec.per_class[ci], cnt, zlo, c.max_nz, dev.sm_count(),
                                            dev.twiddles(), ls));
             else

@@ -24,6 +24,7 @@ extern std::atomic<long long> g_kernel_launches;
 // run-time switches between kernel generations (A/B measurements; mvdSetTuning / environment MVD_Z_TMA, MVD_INV_TMA)
 extern std::atomic<int> g_use_z_tma;
 extern std::atomic<int> g_use_inv_ring;
+extern std::atomic<int> g_use_z_warp;
 
 // ---- planner ---------------------------------------------------------------------------
 struct AxisTile {
@@ -66,6 +67,7 @@ void partition_for_peers(ConvPlan& plan, const PeerTarget* peers, int n);
 // Spectra of one kernel for every tile class of a plan (resident in HBM).
 struct KernelSpectra {
     std::vector<float2*> per_class;
+    std::vector<float2*> per_class_t;  // transposed copy [position][z] for the warp-local z pass (512-point classes), else nullptr
     double kernel_sum = 0.0;
     ~KernelSpectra();
     KernelSpectra() = default;

@@ -79,5 +79,8 @@ __device__ __forceinline__ void group_sync(int id, int threads) { asm volatile("
 // dims / box in elements (float32), strides in bytes for dimensions 1 .. rank-1.  Throws nothing: returns false on failure.
 bool encode_tensor_map_f32(CUtensorMap* out, const void* base, int rank, const unsigned long long* dims, const unsigned long long* strides_bytes,
                            const unsigned* box);
+// the same with the 128-byte shared-memory swizzle (inner box extent 128 bytes, destination 1024-byte aligned)
+bool encode_tensor_map_f32_swizzle128(CUtensorMap* out, const void* base, int rank, const unsigned long long* dims,
+                                      const unsigned long long* strides_bytes, const unsigned* box);
 
 }  // namespace mvd

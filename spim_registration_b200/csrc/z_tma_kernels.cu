@@ -134,8 +134,8 @@ __global__ void __launch_bounds__(ZT<BZ>::THREADS, ZT<BZ>::MIN_CTAS)
 }
 
 // ---------------------------------------------------------------------------------------------
-bool encode_tensor_map_f32(CUtensorMap* out, const void* base, int rank, const unsigned long long* dims, const unsigned long long* strides_bytes,
-                           const unsigned* box) {
+static bool encode_tensor_map(CUtensorMap* out, const void* base, int rank, const unsigned long long* dims, const unsigned long long* strides_bytes,
+                              const unsigned* box, bool swizzle128) {
     typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
     static EncodeFn fn = nullptr;
@@ -155,7 +155,17 @@ bool encode_tensor_map_f32(CUtensorMap* out, const void* base, int rank, const u
         if (i + 1 < rank) gs[i] = strides_bytes[i];
     }
     return fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bd, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+              swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+bool encode_tensor_map_f32(CUtensorMap* out, const void* base, int rank, const unsigned long long* dims, const unsigned long long* strides_bytes,
+                           const unsigned* box) {
+    return encode_tensor_map(out, base, rank, dims, strides_bytes, box, false);
+}
+// 128-byte swizzle: the box's inner extent must be 128 bytes and the shared-memory destination 1024-byte aligned
+bool encode_tensor_map_f32_swizzle128(CUtensorMap* out, const void* base, int rank, const unsigned long long* dims,
+                                      const unsigned long long* strides_bytes, const unsigned* box) {
+    return encode_tensor_map(out, base, rank, dims, strides_bytes, box, true);
 }
 
 bool z_tma_supported(int bz) { return bz == 128 || bz == 256 || bz == 512; }

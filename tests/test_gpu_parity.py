@@ -738,10 +738,11 @@ def test_multi_device_handle_on_real_devices(m, o, lib):
 
 
 # ---- the TMA kernel generations (off by default: measured slower) stay correct ---------------------
-@pytest.mark.parametrize("switch", ["z_tma", "inv_ring"])
-def test_tma_kernels_match_oracle_and_default_kernels(m, o, lib, switch):
-    """z pass with bulk-tensor loads / stores and the inverse xy ring kernel fed by bulk-tensor loads: same results as
-    the register-loading kernels (the arithmetic is the same, only the data movement differs) and as the oracle."""
+@pytest.mark.parametrize("switch,value", [("z_tma", 1), ("inv_ring", 1), ("z_warp", 0)])
+def test_tma_kernels_match_oracle_and_default_kernels(m, o, lib, switch, value):
+    """Every kernel generation against the default one and the oracle: the z pass with bulk-tensor loads / stores, the inverse
+    xy ring kernel fed by bulk-tensor loads, and (z_warp = 0) the register-loading z pass against the default warp-local z
+    pass.  The arithmetic is the same, only the data movement differs."""
     from spim_registration_b200 import synthetic
     f, k = _rand((300, 150, 260), 31), _kernel((31, 31, 31), 32)       # 512-point z window, two 128-windows in x and y
     ref = o.convolve_extended(f, k, "mirror")
@@ -751,7 +752,7 @@ def test_tma_kernels_match_oracle_and_default_kernels(m, o, lib, switch):
     weights = synthetic.blending_weights(shape, V)
     k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
     loop_ref, _, _ = o.run_deconvolution(ds["imgs"], weights, k1, k2, 2, 0.006)
-    prev = lib.mvdSetTuning(switch.encode(), 1)
+    prev = lib.mvdSetTuning(switch.encode(), value)
     try:
         assert prev in (0, 1)
         got = m.convolve(f, k, "mirror")
@@ -761,3 +762,39 @@ def test_tma_kernels_match_oracle_and_default_kernels(m, o, lib, switch):
     assert rel_l2(got, ref) <= CONV_TOL
     assert rel_l2(got, base) <= 1e-7
     assert rel_l2(dec.getPsi(), loop_ref) <= LOOP_TOL
+
+
+# ---- known-answer programs of the reference through the DEVICE code ------------------------------------------------------
+def test_tikhonov_table_through_the_device_epilogue(m, o):
+    """MVDeconvolution.main (MVDeconvolution.java:707-714) prints tikhonov(d * 10000, 0.0006) and tikhonov(d, 0.0006)
+    for d = 0, 0.1, ... < 10.  The same 200 values go through the update epilogue of the device: psi = 1, delta kernels
+    (conv1(psi) = 1, conv2(q) = q exactly on the direct path), so value = img and psi' = 1 + (tikhonov(img) - 1)."""
+    d = np.arange(0, 100, dtype=np.float64) * 0.1
+    vals = np.concatenate([d * 10000.0, d]).astype(np.float32).reshape(1, 10, 20)
+    lam = 0.0006
+    one = np.ones((1, 1, 1), np.float32)
+    view = m.MVDeconFFT(vals, 1.0, one)
+    view.kernel2 = one.copy()
+    inp = m.MVDeconInput()
+    inp.add(view)
+    psi0 = np.ones(vals.shape, np.float32)
+    dec = m.MVDeconvolution(inp, "INDEPENDENT", 1, lam, initialImage=psi0, prepared=True)
+    assert dec.directPath == [(7, 7)]
+    integral = np.where(vals > 0, vals, np.float32(1))            # no data -> quotient 1
+    want, _, _ = o.compute_final_values(psi0, integral, np.float32(1.0), lam)
+    want = np.where(vals > 0, want, np.float32(0))                # never-updated voxels are masked
+    got = dec.getPsi()
+    np.testing.assert_allclose(got, want, rtol=1.5e-7, atol=0)    # <= 1 ulp: the epilogue evaluates the term in two-float arithmetic
+    assert (got == want).mean() >= 0.95
+
+
+def test_blending_image_of_the_reference_main_program_on_the_device(m, o):
+    """BlendingRealRandomAccess.main (:251-270): 500 x 500, border {100, 0}, blending {12, 150} -- rendered by the device's
+    blending code (mvdTransformView) and compared bit for bit with the restated image."""
+    n = 500
+    img = np.ones((3, n, n), np.float32)
+    _, w = m.transformInputAndWeights(img, np.eye(4), (0, 0, 1), (n, n, 1), (100.0, 0.0, -10.0), (12.0, 150.0, 1.0))
+    yy, xx = np.meshgrid(np.arange(n, dtype=np.float32), np.arange(n, dtype=np.float32), indexing="ij")
+    ref = o.blending_weight(np.stack([xx, yy, np.ones_like(xx)], axis=-1), (n, n, 3), (100.0, 0.0, -10.0), (12.0, 150.0, 1.0))
+    np.testing.assert_array_equal(w[0], ref)
+    assert (w[0][150:350, 112:388] == 1).all() and (w[0][:, :101] == 0).all()

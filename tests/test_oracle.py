@@ -492,3 +492,25 @@ def test_cpp_loop_equals_numpy_oracle():
     assert rel_l2(got, ref) <= 2e-6
     np.testing.assert_allclose(np.array(gstats)[:, :, 0], np.array([[s for s, _ in r] for r in stats]), rtol=2e-5)
     np.testing.assert_allclose(np.array(gstats)[:, :, 1], np.array([[m for _, m in r] for r in stats]), rtol=1e-4)
+
+
+def test_blending_image_of_the_reference_main_program():
+    """BlendingRealRandomAccess.main (BlendingRealRandomAccess.java:251-270) renders a 500 x 500 image with border
+    {100, 0} and blending {12, 150}.  The image is not stored in the reference, but it is fully determined: zero up to
+    the border, the 1001-entry cosine table along the ramp, one on the plateau, product of the two axes, symmetric."""
+    n = 500
+    yy, xx = np.meshgrid(np.arange(n, dtype=np.float32), np.arange(n, dtype=np.float32), indexing="ij")
+    t = np.stack([xx, yy, np.ones_like(xx)], axis=-1)
+    # a third axis that never blends (negative border, range 1) turns the 3-d restatement into the 2-d program
+    w = o.blending_weight(t, (n, n, 3), (100.0, 0.0, -10.0), (12.0, 150.0, 1.0))
+    lut = o.blending_lookup()
+    assert (w[:, :101] == 0).all() and (w[:, 399:] == 0).all() and (w[0] == 0).all() and (w[-1] == 0).all()
+    assert (w[150:350, 112:388] == 1).all()                                  # plateau: 12 px behind the x border, 150 px in y
+    np.testing.assert_array_equal(w, w[::-1, :])                             # symmetric in both axes
+    np.testing.assert_array_equal(w, w[:, ::-1])
+    for d in range(1, 12):                                                   # the ramp along x on a plateau row
+        assert w[200, 100 + d] == np.float32(lut[int(np.floor(np.float32(d) / np.float32(12.0) * 1000.0 + 0.5))])
+    for d in (1, 30, 75, 149):                                               # ... along y on a plateau column
+        assert w[d, 250] == np.float32(lut[int(np.floor(np.float32(d) / np.float32(150.0) * 1000.0 + 0.5))])
+    assert w[30, 105] == np.float32(np.float64(np.float32(lut[int(np.floor(np.float32(5) / np.float32(12.0) * 1000.0 + 0.5))])) *
+                                    lut[int(np.floor(np.float32(30) / np.float32(150.0) * 1000.0 + 0.5))])   # product of the axes
