@@ -307,6 +307,22 @@ long long mvdDivideIntoBlocks(const long long* imgSize, const long long* kernelS
 /* Counters for bench.py: kernels launched by this library in the calling process. */
 long long mvdKernelLaunchCount(void);
 
+/* Allocation-free separable convolution.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  out = the three in-place 1-D passes of convolve_7 / 15 / 31 (same kernels, same arithmetic),
+ * with DEVICE arrays dSrc -> dOut (dSrc != dOut, x fastest, dim = {x, y, z}); a NULL kernel leaves that axis alone;
+ * kernelX/Y/Z are HOST arrays of kernelLen <= 31 taps; outofbounds 0 zero, 1 outofboundsvalue, 2 extend last pixel.
+ * The call launches two kernels on cudaStream (a cudaStream_t, NULL = legacy default stream) and returns without
+ * synchronising; it calls no cudaMalloc / cudaFree and no allocating library routine.  The intermediate lives in a
+ * static device array of MVD_NOALLOC_MAX_VOXELS floats (32 MiB, held by every GPU that loads the library until the
+ * process exits): volumes with more voxels are rejected with an error (mvdGetLastError).  Every call shares that
+ * array -- calls that overlap on the GPU (other streams, other host threads on the same device) race; serialise them.
+ * The first call on a device resolves the array's device address (cudaGetSymbolAddress): make it before a capture. */
+#define MVD_NOALLOC_MAX_VOXELS 8388608 /* 8 Mi voxels, e.g. 256 x 256 x 128 */
+int mvdSeparableConvolveNoAlloc(int device, const float* dSrc, float* dOut, const int dim[3], const float* kernelX,
+                                const float* kernelY, const float* kernelZ, int kernelLen, int outofbounds,
+                                float outofboundsvalue, void* cudaStream);
+
 /* Process-wide switches between kernel generations, for A/B measurements and tests (defaults: the faster one).
  *   "z_tma"   1 = z pass with TMA bulk-tensor loads / stores (z_tma_kernels.cu), 0 = register-loading z pass (default)
  *   "inv_ring" 1 = inverse xy pass fed by bulk-tensor loads into a shared-memory ring, 0 = register-loading kernel (default)

@@ -72,6 +72,8 @@ PROTOTYPES = {
     "mvdDivideIntoBlocks": (C.c_longlong, [c_ll_p, c_ll_p, c_ll_p, C.c_int, c_ll_p, C.c_longlong]),
     "mvdKernelLaunchCount": (C.c_longlong, []),
     "mvdSetTuning": (C.c_int, [C.c_char_p, C.c_int]),
+    "mvdSeparableConvolveNoAlloc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, c_int_p, c_float_p, c_float_p, c_float_p, C.c_int, C.c_int, C.c_float,
+                                              C.c_void_p]),
     "mvdCreateMulti": (C.c_int, [C.POINTER(C.c_void_p), c_int_p, C.c_int, c_int_p, c_int_p, C.c_double, C.c_float]),
     "mvdDestroyMulti": (C.c_int, [C.c_void_p]),
     "mvdMultiNumBricks": (C.c_int, [C.c_void_p]),

@@ -1793,3 +1793,78 @@ extern "C" float* convolution3DfftCUDA(float* im, int* imDim, float* kernel, int
     if (legacy_convolve(im, imDim, kernel, kernelDim, devCUDA, out) != 0) { std::free(out); return nullptr; }
     return out;
 }
+
+// ---- allocation-free separable convolution ----------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot allocate
+// device memory (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same kernels as
+// convolve_7 / 15 / 31 (sep_xy_kernel -> sep_z_kernel, sep_kernels.cu); the intermediate of the fused x / y pass lives
+// in the file-scope array below instead of a cudaMalloc'ed buffer.  Every GPU that loads the library holds the array
+// (MVD_NOALLOC_MAX_VOXELS floats = 32 MiB) until the process exits.
+//
+// In host code `g_noalloc_scratch` is a host-side stand-in, NOT a device address: the address the kernels get comes
+// from cudaGetSymbolAddress, resolved once per device with that device current (noalloc_scratch_ptr).
+// Every call shares the array and it keeps the previous call's contents.  Nothing in it has to start at zero: the x / y
+// pass writes every element the z pass reads (all dim[0] * dim[1] * dim[2] of them) before the z pass starts, in stream
+// order.  Calls that overlap on the GPU (different streams, or different host threads on the same device) RACE on it.
+static __device__ __align__(256) float g_noalloc_scratch[MVD_NOALLOC_MAX_VOXELS];
+
+static float* noalloc_scratch_ptr(int device) {
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static float* ptrs[kMaxDev] = {};
+    require(device >= 0 && device < kMaxDev, "mvdSeparableConvolveNoAlloc: device index out of range");
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptrs[device]) {
+        int cur = -1;
+        MVD_CUDA(cudaGetDevice(&cur));
+        require(cur == device, "mvdSeparableConvolveNoAlloc: internal error, the device is not current");
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            throw CudaError(std::string("cudaGetSymbolAddress(g_noalloc_scratch) on device ") + std::to_string(device) + ": " + cudaGetErrorString(e));
+        ptrs[device] = static_cast<float*>(p);
+    }
+    return ptrs[device];
+}
+
+extern "C" int mvdSeparableConvolveNoAlloc(int device, const float* dSrc, float* dOut, const int dim[3], const float* kernelX,
+                                           const float* kernelY, const float* kernelZ, int kernelLen, int outofbounds,
+                                           float outofboundsvalue, void* cudaStream) {
+    return guarded([&] {
+        require(dSrc && dOut && dim, "mvdSeparableConvolveNoAlloc: null argument");
+        require(dSrc != dOut, "mvdSeparableConvolveNoAlloc: dSrc and dOut must be different arrays");
+        require(dim[0] > 0 && dim[1] > 0 && dim[2] > 0, "mvdSeparableConvolveNoAlloc: bad image size");
+        require(kernelLen >= 1 && kernelLen <= kSepMaxTaps, "mvdSeparableConvolveNoAlloc: kernelLen must be 1 .. 31 (direct kernels only)");
+        require(outofbounds >= 0 && outofbounds <= 2, "mvdSeparableConvolveNoAlloc: outofbounds must be 0 (zero), 1 (value) or 2 (extend last pixel)");
+        const unsigned long long vox = (unsigned long long)dim[0] * (unsigned long long)dim[1] * (unsigned long long)dim[2];
+        if (vox > (unsigned long long)MVD_NOALLOC_MAX_VOXELS)
+            throw std::invalid_argument("mvdSeparableConvolveNoAlloc: " + std::to_string(vox) + " voxels exceed the maximum of " +
+                                        std::to_string((unsigned long long)MVD_NOALLOC_MAX_VOXELS) +
+                                        " (MVD_NOALLOC_MAX_VOXELS, the size of the library's static scratch array); use convolve_N or mvdConvolveDevice");
+        int n_dev = 0;
+        MVD_CUDA(cudaGetDeviceCount(&n_dev));
+        require(device >= 0 && device < n_dev, "mvdSeparableConvolveNoAlloc: no such CUDA device (this library has no CPU path)");
+        MVD_CUDA(cudaSetDevice(device));
+        float* tmp = noalloc_scratch_ptr(device);
+        Volume v;
+        v.data = dSrc;
+        for (int i = 0; i < 3; ++i) { v.dim[i] = dim[i]; v.off[i] = 0; v.gmin[i] = 0; v.gdim[i] = dim[i]; }
+        v.ext = outofbounds == 0 ? EXT_ZERO : (outofbounds == 1 ? EXT_CONST : EXT_CLAMP);
+        v.ext_value = outofboundsvalue;
+        const float one = 1.f;
+        SepTaps taps;
+        std::memset(&taps, 0, sizeof(taps));
+        const int kmax = sep_kmax_for(kernelLen, kernelLen, kernelLen);
+        make_window_taps(kernelX ? kernelX : &one, kernelX ? kernelLen : 1, kmax, taps.x);
+        make_window_taps(kernelY ? kernelY : &one, kernelY ? kernelLen : 1, kmax, taps.y);
+        make_window_taps(kernelZ ? kernelZ : &one, kernelZ ? kernelLen : 1, kmax, taps.z);
+        taps.per_pass_fill = 1;  // three 1-D passes, each with the plain outside value, like convolve_N
+        EpilogueArgs ep;
+        std::memset(&ep, 0, sizeof(ep));
+        ep.out = dOut;
+        for (int i = 0; i < 3; ++i) { ep.out_dim[i] = dim[i]; ep.aux_dim[i] = dim[i]; }
+        // two launches on the caller's stream, nothing else: no allocation, no copy, no synchronisation
+        MVD_CUDA(launch_separable(v, dim, taps, kmax, EPI_STORE, ep, tmp, static_cast<cudaStream_t>(cudaStream)));
+        g_kernel_launches += 2;
+    });
+}
