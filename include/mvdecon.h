@@ -93,6 +93,7 @@ const char* mvdVersion(void);
 #define MVD_MEM_HOST_ASYNC 3 /* mvdAddView only: host arrays (pinned for a real overlap) that the caller keeps alive until the next
                               * mvdSynchronize / mvdRunIterations / mvdInitPsiAverage returns: the call does not wait for the upload, the
                               * first step that reads the view does (on the device) */
+#define MVD_MEM_HOST_ASYNC_IMG_DEVICE_WEIGHT 4 /* mvdAddView only: img as MVD_MEM_HOST_ASYNC, weight on the device (copied before return) */
 
 /* Create a context on CUDA device `device` for one brick of the deconvolved volume.
  *   globalDim   (x,y,z) size of the whole deconvolved volume psi.
@@ -325,7 +326,8 @@ int mvdSeparableConvolveNoAlloc(int device, const float* dSrc, float* dOut, cons
 
 /* Process-wide switches between kernel generations, for A/B measurements and tests (defaults: the faster one).
  *   "z_tma"   1 = z pass with TMA bulk-tensor loads / stores (z_tma_kernels.cu), 0 = register-loading z pass (default)
- *   "inv_ring" 1 = inverse xy pass fed by bulk-tensor loads into a shared-memory ring, 0 = register-loading kernel (default)
+ *   "inv_ring" inverse xy pass fed by bulk-tensor loads into a shared-memory ring: 2 = for the quotient / store epilogues
+ *             (default; the update epilogue keeps the register-loading kernel, which is faster there), 1 = always, 0 = never
  *   "z_warp"  1 = z pass with warp-local 512-point lines behind swizzled bulk-tensor loads / stores (default), 0 = off
  * Returns the previous value, or -1 for an unknown name. */
 int mvdSetTuning(const char* name, int value);

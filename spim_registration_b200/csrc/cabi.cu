@@ -419,8 +419,10 @@ static void add_view(mvdContext* c, const float* img, const float* weight, float
         if (hi_nb) require(c->ghi[d] >= std::max(k1[d] / 2, need1) && c->ghi[d] >= std::max(k2[d] / 2, need2),
                            "mvdAddView: ghost layer narrower than the kernel halo");
     }
-    require(memKind == MVD_MEM_HOST || memKind == MVD_MEM_DEVICE || memKind == MVD_MEM_HOST_IMG_DEVICE_WEIGHT || memKind == MVD_MEM_HOST_ASYNC,
+    require(memKind == MVD_MEM_HOST || memKind == MVD_MEM_DEVICE || memKind == MVD_MEM_HOST_IMG_DEVICE_WEIGHT || memKind == MVD_MEM_HOST_ASYNC ||
+                memKind == MVD_MEM_HOST_ASYNC_IMG_DEVICE_WEIGHT,
             "mvdAddView: bad memKind");
+    const bool async_img = memKind == MVD_MEM_HOST_ASYNC || memKind == MVD_MEM_HOST_ASYNC_IMG_DEVICE_WEIGHT;
     require(!volDim || memKind == MVD_MEM_HOST || memKind == MVD_MEM_HOST_ASYNC, "mvdAddView: volume slices are host arrays");
     const cudaMemcpyKind kind = memKind == MVD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     const cudaMemcpyKind wkind = (memKind == MVD_MEM_HOST || memKind == MVD_MEM_HOST_ASYNC) ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
@@ -446,7 +448,14 @@ static void add_view(mvdContext* c, const float* img, const float* weight, float
     upload(v.img, img, kind);
     if (weight) {
         v.weight.alloc(bytes);
-        upload(v.weight, weight, wkind);
+        if (memKind == MVD_MEM_HOST_ASYNC_IMG_DEVICE_WEIGHT) {
+            // device -> device on the context's own stream (ordered before every step) and complete on return: the caller may
+            // free the weight array at once, while the image upload is still in flight on the copy stream
+            MVD_CUDA(cudaMemcpyAsync(v.weight, weight, bytes, cudaMemcpyDeviceToDevice, c->stream));
+            MVD_CUDA(cudaStreamSynchronize(c->stream));
+        } else {
+            upload(v.weight, weight, wkind);
+        }
     }
     MVD_CUDA(cudaEventCreateWithFlags(&v.ready, cudaEventDisableTiming));
     MVD_CUDA(cudaEventRecord(v.ready, c->copy_stream));
@@ -464,7 +473,7 @@ static void add_view(mvdContext* c, const float* img, const float* weight, float
     // MVD_MEM_HOST_ASYNC: the caller keeps img / weight alive until the next mvdSynchronize / mvdRunIterations returns, so the
     // upload of this view overlaps the caller's next calls (and the first steps of the loop); otherwise the buffers may go
     // away after return
-    if (memKind != MVD_MEM_HOST_ASYNC) MVD_CUDA(cudaStreamSynchronize(c->copy_stream));
+    if (!async_img) MVD_CUDA(cudaStreamSynchronize(c->copy_stream));
     c->views.push_back(std::move(v));
     if (viewIndex) *viewIndex = (int)c->views.size() - 1;
 }
@@ -974,11 +983,40 @@ extern "C" int mvdCreateMulti(mvdMulti** out, const int* devices, int numDevices
         m->n = numDevices;
         m->devices.assign(devices, devices + numDevices);
         for (int d = 0; d < 3; ++d) { m->gdim[d] = globalDim[d]; m->grid[d] = 1; }
-        for (int k = numDevices; k > 1; k /= 2) {  // split the longest axis, z before y before x on ties
-            int best = 2;
-            for (int d = 1; d >= 0; --d)
-                if ((double)m->gdim[d] / m->grid[d] > (double)m->gdim[best] / m->grid[best]) best = d;
-            m->grid[best] *= 2;
+        // the grid whose largest brick needs the least FFT-window volume (bricks that sit badly on the windows cost up to 20 % more
+        // work); ties prefer fewer cuts along x (long rows), then along y -- the same rule as parallel.brick_grid
+        {
+            static const int xy_sizes[] = {32, 64, 128}, z_sizes[] = {16, 32, 64, 128, 256, 512};
+            auto axis_cost = [&](int n, int k, int d) {
+                const std::vector<AxisTile> t = d < 2 ? plan_axis(n, k, 4, xy_sizes, 3) : plan_axis(n, k, 1, z_sizes, 6);
+                if (t.empty()) return 1e300;
+                double c = 0;
+                for (const auto& a : t) c += a.b + 6;
+                return c;
+            };
+            double best = 1e300;
+            for (int gx = 1; gx <= numDevices; gx *= 2)
+                for (int gy = 1; gx * gy <= numDevices; gy *= 2) {
+                    const int g[3] = {gx, gy, numDevices / (gx * gy)};
+                    double cost = 1.0;
+                    bool ok = true;
+                    for (int d = 0; d < 3 && ok; ++d) {
+                        require(maxKernelDim[d] >= 1, "mvdCreateMulti: bad kernel extent");
+                        const int ghost = g[d] > 1 ? std::max(maxKernelDim[d] / 2, maxKernelDim[d] - 1 - maxKernelDim[d] / 2) : 0;
+                        double worst = 0;
+                        for (int i = 0; i < g[d]; ++i) {
+                            const int n = brick_bound(i + 1, g[d], m->gdim[d]) - brick_bound(i, g[d], m->gdim[d]);
+                            if (n < std::max(1, ghost)) { ok = false; break; }
+                            worst = std::max(worst, axis_cost(n, maxKernelDim[d], d));
+                        }
+                        cost *= worst;
+                    }
+                    if (ok && cost < best) {  // strict: the first grid in (gx, gy) order wins ties
+                        best = cost;
+                        for (int d = 0; d < 3; ++d) m->grid[d] = g[d];
+                    }
+                }
+            require(best < 1e299, "mvdCreateMulti: no brick grid fits the kernel halo");
         }
         for (int d = 0; d < 3; ++d) {
             require(maxKernelDim[d] >= 1, "mvdCreateMulti: bad kernel extent");

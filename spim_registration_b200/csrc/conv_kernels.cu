@@ -769,6 +769,12 @@ __global__ void __launch_bounds__((XYThreads<BX, BY>::NT), (XYCfg<BX, BY>::MIN_C
         }
         }
         __syncthreads();  // rows are done with the plane before the next plane's columns scatter into it
+        if constexpr (PUSH && BX == 128) {
+            if (s_npeer) {  // the same for every thread of the CTA (written behind a barrier): interior tiles pay nothing
+                push_plane128<NT>(plane, tile, zv, s_peer, s_npeer, tid);
+                __syncthreads();
+            }
+        }
     }
     }  // items
     if constexpr (EPI == EPI_UPDATE) {

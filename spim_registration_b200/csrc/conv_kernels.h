@@ -44,7 +44,7 @@ bool inv_ring_supported(int bx, int by);
 cudaError_t configure_inv_ring_kernels();
 // zlo = first plane of a tile that is handed on; cudaErrorNotSupported: use launch_inv_xy
 cudaError_t launch_inv_ring(int bz, int epilogue, const float2* scratch, const Tile* d_tiles, int n_tiles, int zlo, int max_nz,
-                            const EpilogueArgs& ep, int num_sms, const TwiddleTables& tw, cudaStream_t st);
+                            const EpilogueArgs& ep, int num_sms, int interleave, const TwiddleTables& tw, cudaStream_t st);
 void set_grid_caps(int xy_cap, int z_cap);  // persistent-grid sizes, 0 = one CTA per work item
 cudaError_t configure_conv_kernels();  // opt in to > 48 KB dynamic shared memory
 

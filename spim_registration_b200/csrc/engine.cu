@@ -16,7 +16,7 @@ static int env_flag(const char* name, int dflt) {
     return s ? std::atoi(s) : dflt;
 }
 std::atomic<int> g_use_z_tma{env_flag("MVD_Z_TMA", 0)};
-std::atomic<int> g_use_inv_ring{env_flag("MVD_INV_RING", 0)};
+std::atomic<int> g_use_inv_ring{env_flag("MVD_INV_RING", 2)};
 std::atomic<int> g_use_z_warp{env_flag("MVD_Z_WARP", 1)};
 
 void cuda_check(cudaError_t e, const char* what) {
@@ -379,8 +379,11 @@ void partition_for_peers(ConvPlan& plan, const PeerTarget* peers, int n) {
 // ---- convolution -----------------------------------------------------------------------
 static cudaError_t launch_inv(Device& dev, int bx, int by, int bz, int epilogue, const float2* buf, const Tile* d_tiles, int n_tiles, int zlo,
                               int max_nz, const EpilogueArgs& ep, cudaStream_t st) {
-    if (g_use_inv_ring.load() && inv_ring_supported(bx, by)) {
-        const cudaError_t e = launch_inv_ring(bz, epilogue, buf, d_tiles, n_tiles, zlo, max_nz, ep, dev.sm_count(), dev.twiddles(), st);
+    // inv_ring: 0 = off, 1 = every epilogue, 2 = quotient / store epilogues only; MVD_RING_ORDER: 0 contiguous runs of planes per CTA, 1 round-robin
+    const int ring = g_use_inv_ring.load();
+    static const int ring_order = env_flag("MVD_RING_ORDER", 2);  // 2 = round-robin + L2 prefetch of the epilogue operands
+    if (ring && (ring == 1 || epilogue != EPI_UPDATE) && inv_ring_supported(bx, by)) {
+        const cudaError_t e = launch_inv_ring(bz, epilogue, buf, d_tiles, n_tiles, zlo, max_nz, ep, dev.sm_count(), ring_order, dev.twiddles(), st);
         if (e != cudaErrorNotSupported) return e;
     }
     return launch_inv_xy(bx, by, bz, epilogue, buf, d_tiles, n_tiles, max_nz, ep, dev.twiddles(), st);
@@ -464,7 +467,11 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
             else
                 MVD_CUDA(launch_z_pass(bx, by, bz, 1, buf, spec.per_class[ci], c.d_tiles + s, cnt, 1.f, dev.twiddles(), ls));
             if (prof) { prof->end(ls); prof->begin(2, nz_sum * pe * 8.0 + out_vox * epi_bytes, ls); }
-            if (ep.n_peers > 0 && c.n_interior >= 0) {
+            // MVD_PUSH_SPLIT=1: interior tiles with the plain kernel, tiles at the brick faces with the PUSH kernel (two launches
+            // per batch: what paid while the push sat inside the per-voxel epilogue).  Default: one launch of the PUSH kernel --
+            // with the staged push (push_plane128) it costs interior tiles nothing, and whole batches have shorter tails.
+            static const int push_split = env_flag("MVD_PUSH_SPLIT", 0);
+            if (push_split && ep.n_peers > 0 && c.n_interior >= 0) {
                 // interior tiles with the plain epilogue, tiles at the brick faces with the one that also
                 // stores into the neighbours' ghost layers
                 const int a = std::max(0, std::min(cnt, c.n_interior - s));

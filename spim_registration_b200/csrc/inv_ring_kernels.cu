@@ -48,7 +48,7 @@ constexpr size_t SMEM = OFF_BAR + 64;
 template <int EPI, bool PUSH>
 __global__ void __launch_bounds__(ring::THREADS, 1)
     inv_ring_kernel(const __grid_constant__ CUtensorMap map_plane, const __grid_constant__ CUtensorMap map_nyq, const Tile* __restrict__ tiles,
-                    EpilogueArgs ep, int bz, int zlo, int max_nz, int n_planes, int planes_per_cta, Twiddles tw) {
+                    EpilogueArgs ep, int bz, int zlo, int max_nz, int n_planes, int planes_per_cta, int interleave, Twiddles tw) {
     using namespace ring;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     float2* slots = reinterpret_cast<float2*>(smem_raw);
@@ -74,12 +74,15 @@ __global__ void __launch_bounds__(ring::THREADS, 1)
     if (tid < G) s_npeer[tid] = 0;
     __syncthreads();
 
-    const int q0 = blockIdx.x * planes_per_cta;
-    const int count = min(planes_per_cta, n_planes - q0);  // planes of this CTA (<= 0: nothing to do)
+    // plane k of this CTA = (tile, effective plane) pair q; slot k % S; group k % G.  interleave = 0: every CTA a contiguous
+    // run of pairs; 1: pairs dealt round-robin, so that the CTAs in flight work on neighbouring planes of the same tile
+    // (their epilogue rows share DRAM pages and the cache lines at tile seams)
+    const int q0 = interleave ? (int)blockIdx.x : (int)blockIdx.x * planes_per_cta;
+    const int qstep = interleave ? (int)gridDim.x : 1;  // interleave >= 2: additionally L2-prefetch the epilogue operands
+    const int count = interleave ? (n_planes > q0 ? (n_planes - q0 + qstep - 1) / qstep : 0) : min(planes_per_cta, n_planes - q0);
 
-    // plane k of this CTA = (tile, effective plane) pair q0 + k; slot k % S; group k % G
     auto plane_of = [&](int k, int& ti, int& zr) {
-        const int q = q0 + k;
+        const int q = q0 + k * qstep;
         ti = q / max_nz;
         zr = q - ti * max_nz;
     };
@@ -144,6 +147,24 @@ __global__ void __launch_bounds__(ring::THREADS, 1)
         const float2* __restrict__ nyq = plane + BY * P;
         const int zv = tile.e[2] + zr;  // plane inside the volume
 
+        if (valid && EPI != EPI_STORE && interleave >= 2) {
+            // the epilogue's operand rows of this plane towards L2 while the plane's spectrum is still in flight / being
+            // transformed: one 128-byte line per thread and step, 4 lines cover a 98-float row
+            const int n0p = tile.n[0], n1p = tile.n[1];
+            for (int i = lt; i < 4 * n1p; i += GT) {
+                const int yl = i >> 2, seg = i & 3;
+                if (32 * seg < n0p) {
+                    const size_t ob = ((size_t)(zv + ep.out_off[2]) * ep.out_dim[1] + (tile.e[1] + yl + ep.out_off[1])) * (size_t)ep.out_dim[0] +
+                                      tile.e[0] + ep.out_off[0] + 32 * seg;
+                    const size_t ab = ((size_t)zv * ep.aux_dim[1] + (tile.e[1] + yl)) * (size_t)ep.aux_dim[0] + tile.e[0] + 32 * seg;
+                    if constexpr (EPI == EPI_QUOTIENT) asm volatile("prefetch.global.L2 [%0];" ::"l"(ep.img + ab));
+                    if constexpr (EPI == EPI_UPDATE) {
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(ep.out + ob));
+                        if (ep.weight) asm volatile("prefetch.global.L2 [%0];" ::"l"(ep.weight + ab));
+                    }
+                }
+            }
+        }
         tma::mbar_wait(&full[s], (unsigned)(k / S) & 1u);
         if (valid) {
         // ---- phase 1: inverse columns, in place, warp-local; column 0 re-packs DC + i*Nyquist
@@ -203,6 +224,12 @@ __global__ void __launch_bounds__(ring::THREADS, 1)
         // ---- phase 2: inverse rows of the effective region + epilogue
         inv_rows128<EPI, PUSH, GT>(plane, twr, twu, tile, zv, ep, s_peer, PUSH ? s_npeer[g] : 0, lt, use_tik, tik, lsum, lmax);
         }
+        if constexpr (PUSH) {
+            if (valid && s_npeer[g]) {  // the same for every thread of the group: interior tiles pay nothing
+                gsync();  // the plane's rows hold the results
+                push_plane128<GT>(plane, tile, zv, s_peer, s_npeer[g], lt);
+            }
+        }
         tma::fence_proxy_async();  // this thread's accesses to the slot are ordered before the bulk copies that refill it
         gsync();  // the slot is consumed: refill it with the plane three ahead
         if (lt == 0) issue_load(k + S);
@@ -246,7 +273,7 @@ cudaError_t configure_inv_ring_kernels() {
 }
 
 cudaError_t launch_inv_ring(int bz, int epilogue, const float2* scratch, const Tile* d_tiles, int n_tiles, int zlo, int max_nz,
-                            const EpilogueArgs& ep, int num_sms, const TwiddleTables& tw, cudaStream_t st) {
+                            const EpilogueArgs& ep, int num_sms, int interleave, const TwiddleTables& tw, cudaStream_t st) {
     if (n_tiles <= 0 || max_nz <= 0) return cudaSuccess;
     if (ep.n_peers > kMaxPeers || zlo + max_nz > bz) return cudaErrorInvalidValue;
     const long long total = (long long)n_tiles * max_nz;
@@ -265,7 +292,7 @@ cudaError_t launch_inv_ring(int bz, int epilogue, const float2* scratch, const T
     const int grid = std::max(1, std::min(num_sms, (n_planes + 5) / 6));
     const int per = (n_planes + grid - 1) / grid;
     const bool push = ep.peers != nullptr && ep.n_peers > 0;
-#define L(EPI, PUSH) inv_ring_kernel<EPI, PUSH><<<grid, ring::THREADS, ring::SMEM, st>>>(mp, mn, d_tiles, ep, bz, zlo, max_nz, n_planes, per, to_dev(tw))
+#define L(EPI, PUSH) inv_ring_kernel<EPI, PUSH><<<grid, ring::THREADS, ring::SMEM, st>>>(mp, mn, d_tiles, ep, bz, zlo, max_nz, n_planes, per, interleave, to_dev(tw))
     if (epilogue == EPI_STORE) L(EPI_STORE, false);
     else if (epilogue == EPI_QUOTIENT && !push) L(EPI_QUOTIENT, false);
     else if (epilogue == EPI_QUOTIENT) L(EPI_QUOTIENT, true);
