@@ -359,7 +359,13 @@ Profiler::~Profiler() {
     for (auto& r : recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
 }
 
+bool push_split_enabled() {
+    static const int v = env_flag("MVD_PUSH_SPLIT", 0);
+    return v != 0;
+}
+
 void partition_for_peers(ConvPlan& plan, const PeerTarget* peers, int n) {
+    if (!push_split_enabled() && n > 0) return;  // one PUSH launch over all tiles: their order does not matter
     for (TileClass& c : plan.classes) {
         auto interior = [&](const Tile& t) {
             for (int p = 0; p < n; ++p) {
@@ -470,8 +476,7 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
             // MVD_PUSH_SPLIT=1: interior tiles with the plain kernel, tiles at the brick faces with the PUSH kernel (two launches
             // per batch: what paid while the push sat inside the per-voxel epilogue).  Default: one launch of the PUSH kernel --
             // with the staged push (push_plane128) it costs interior tiles nothing, and whole batches have shorter tails.
-            static const int push_split = env_flag("MVD_PUSH_SPLIT", 0);
-            if (push_split && ep.n_peers > 0 && c.n_interior >= 0) {
+            if (push_split_enabled() && ep.n_peers > 0 && c.n_interior >= 0) {
                 // interior tiles with the plain epilogue, tiles at the brick faces with the one that also
                 // stores into the neighbours' ghost layers
                 const int a = std::max(0, std::min(cnt, c.n_interior - s));

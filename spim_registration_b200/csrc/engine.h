@@ -63,6 +63,7 @@ bool same_plan(const ConvPlan& p, const int dim[3], const int k[3]);
 // Orders the tiles of every class interior first (stable) with respect to the neighbours' boxes and
 // uploads them again; n = 0 removes the partition.  No kernel using the plan may be in flight.
 void partition_for_peers(ConvPlan& plan, const PeerTarget* peers, int n);
+bool push_split_enabled();  // MVD_PUSH_SPLIT=1: interior / boundary tiles in separate launches (run_convolution)
 
 // Spectra of one kernel for every tile class of a plan (resident in HBM).
 struct KernelSpectra {
