@@ -54,9 +54,8 @@ void convolution3DfftCUDAInPlace(float* im, int* imDim, float* kernel, int* kern
  * CUDASeparableConvolutionFunctions.java:127-199): in-place separable convolution with one kernel of
  * diameter N per axis, image x fastest.  outofbounds 0 = zero, 1 = outofboundsvalue, 2 = extend the
  * last pixel.  Java `boolean` arguments and results are C ints (JNA).  Returns 1 on success, 0 on
- * failure (mvdGetLastError).  N <= 31 runs the direct separable kernels, 63 the FFT engine axis by
- * axis, 127 is refused (wider than the largest xy window).  The interface's convolutionCPU is not
- * exported: this library has no CPU path. */
+ * failure (mvdGetLastError).  N <= 31 runs the direct separable kernels, 63 and 127 the FFT engine axis by
+ * axis (127 taps along x or y use the 256-point windows; called at CUDASeparableConvolutionFunctions.java:191). */
 int convolve_7(float* image, float* kernelX, float* kernelY, float* kernelZ, int imageW, int imageH, int imageD, int convolveX,
                int convolveY, int convolveZ, int outofbounds, float outofboundsvalue, int devCUDA);
 int convolve_15(float* image, float* kernelX, float* kernelY, float* kernelZ, int imageW, int imageH, int imageD, int convolveX,
@@ -67,6 +66,11 @@ int convolve_63(float* image, float* kernelX, float* kernelY, float* kernelZ, in
                 int convolveY, int convolveZ, int outofbounds, float outofboundsvalue, int devCUDA);
 int convolve_127(float* image, float* kernelX, float* kernelY, float* kernelZ, int imageW, int imageH, int imageD, int convolveX,
                  int convolveY, int convolveZ, int outofbounds, float outofboundsvalue, int devCUDA);
+/* CUDASeparableConvolution.convolutionCPU (CUDASeparableConvolution.java:19-21; declared by the reference's interface, called
+ * nowhere in it): in-place separable convolution with kernels of RADIUS kernelR* (2 R + 1 taps, NULL = leave the axis alone),
+ * outofbounds as above.  This library has no CPU code: the result is computed on device 0 by the kernels behind convolve_N. */
+void convolutionCPU(float* image, float* kernelX, float* kernelY, float* kernelZ, int kernelRX, int kernelRY, int kernelRZ, int imageW,
+                    int imageH, int imageD, int outofbounds, float outofboundsvalue);
 
 /* CUDAFourierConvolution.java:9 -- declared by the reference, never called.  Returns a
  * malloc()ed array with the result (caller frees) or NULL on failure. */
@@ -170,7 +174,11 @@ int mvdArrayInfo(mvdContext* ctx, int which, void** devicePtr, int dim[3], int o
  * (sum |K - a(z) b(y) c(x)| <= 1e-6 sum |K|, each extent <= 31); such convolutions run as direct
  * separable passes with the same fused epilogues instead of through the FFT engine (Gaussian PSFs
  * and the compound kernels built from them qualify, extracted bead PSFs do not).  Enabled by
- * default; contexts with attached peers use the FFT engine.  mvdViewUsesDirectPath reports the tap
+ * default, also for bricks with attached peers (the z kernel's epilogue pushes ghost voxels like the FFT path's).  The
+ * substitution is an approximation the reference does not make: the factors are the kernel's marginal sums, the
+ * replaced kernel differs from the given one by at most 1e-6 of its L1 norm, i.e. the convolution result by at most
+ * 1e-6 relative -- two orders of magnitude inside the 1e-4 parity bound; mvdSetDirectPath(ctx, 0) switches it off
+ * (every convolution then runs the FFT engine on the kernel as given).  mvdViewUsesDirectPath reports the tap
  * count class (0 = FFT, else 7 / 15 / 31) chosen for conv1 and conv2 of a view. */
 int mvdSetDirectPath(mvdContext* ctx, int enable);
 int mvdViewUsesDirectPath(mvdContext* ctx, int view, int* conv1, int* conv2);
@@ -281,6 +289,35 @@ int mvdMultiSetPsi(mvdMulti* multi, const float* psi);
 int mvdMultiRunIterations(mvdMulti* multi, int numIterations, double* sumChange, double* maxChange);
 int mvdMultiMaskNeverUpdated(mvdMulti* multi);
 int mvdMultiGetPsi(mvdMulti* multi, float* psi);
+
+/* Kernel preparation behind the C ABI: MVDeconInput.init / MVDeconFFT.init
+ * (MVDeconInput.java:43-49, MVDeconFFT.java:162-333) with AdjustInput.normImg (AdjustInput.java:29-100, its sumImg
+ * double-count included), Mirror.mirror (Mirror.java:31-108, even-size quirk included) and the compound kernels of
+ * the four PSFTYPEs; the small zero-extended convolutions run through the device engine.  The Java host keeps its own
+ * MVDeconFFT.init; this entry is for hosts without it.
+ *   psfs[v]      host array, extent psfDims[3 v .. 3 v + 2] = (x, y, z), x fastest; views are initialised in order
+ *   psfType      0 OPTIMIZATION_II, 1 OPTIMIZATION_I, 2 EFFICIENT_BAYESIAN, 3 INDEPENDENT (order of MVDeconFFT.PSFTYPE, :28)
+ *   numThreads   the thread count that decides sumImg's portions (the reference: Threads.numThreads())
+ *   kernel1[v], kernel2[v]  host outputs of the extent of psfs[v] */
+int mvdPrepareKernels(int device, int numViews, const float* const* psfs, const int* psfDims, int psfType, int numThreads,
+                      float* const* kernel1, float* const* kernel2);
+
+/* Neighbour-only barrier of the fused exchange, in peer memory (one process per GPU: events cannot be shared, and a
+ * collective over all ranks costs ~25 us per step).  Every context owns a small flag array; after a step a rank stores the
+ * step number into its slot of every neighbour's array, before the next step it waits until all its neighbours have done
+ * the same (ld.acquire.sys spin, bounded to ~10 s: on expiry the next mvdSynchronize / mvdGetStats fails).
+ *   mvdExportFlags      the CUDA IPC handle and / or the device pointer of this context's flag array
+ *   mvdAttachPeerFlags  one neighbour's array (MVD_PEER_IPC handle or MVD_PEER_POINTER), the slot (0 .. 31) of THIS brick in
+ *                       the neighbour's array and the slot of the neighbour in this brick's array (e.g. the 3 x 3 x 3 offset code)
+ *   mvdPeerSignal / mvdPeerWait / mvdPeerBarrier(ctx, value)  enqueue on the context's stream; values must increase by at most
+ *                       2^31 per call.  mvdPeerBarrier = signal + wait in one kernel: only when every brick has its OWN GPU --
+ *                       kernels of several bricks on one GPU that wait for one another may never run at the same time; there,
+ *                       signal for all bricks first and wait afterwards. */
+int mvdExportFlags(mvdContext* ctx, unsigned char flagsHandle[64], void** flagsPointer);
+int mvdAttachPeerFlags(mvdContext* ctx, const void* peerFlags, int kind, int theirSlotForMe, int mySlotForThem);
+int mvdPeerSignal(mvdContext* ctx, unsigned int value);
+int mvdPeerWait(mvdContext* ctx, unsigned int value);
+int mvdPeerBarrier(mvdContext* ctx, unsigned int value);
 
 /* Stand-alone resident convolution with the engine used by the loop: out = conv(ext(src), kernel)
  * restricted to the volume, src/out dim (x,y,z) host arrays.  extMode 0 zero, 1 constant

@@ -72,6 +72,13 @@ PROTOTYPES = {
     "mvdDivideIntoBlocks": (C.c_longlong, [c_ll_p, c_ll_p, c_ll_p, C.c_int, c_ll_p, C.c_longlong]),
     "mvdKernelLaunchCount": (C.c_longlong, []),
     "mvdSetTuning": (C.c_int, [C.c_char_p, C.c_int]),
+    "mvdExportFlags": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "mvdAttachPeerFlags": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "mvdPeerSignal": (C.c_int, [C.c_void_p, C.c_uint]),
+    "mvdPeerWait": (C.c_int, [C.c_void_p, C.c_uint]),
+    "mvdPeerBarrier": (C.c_int, [C.c_void_p, C.c_uint]),
+    "mvdPrepareKernels": (C.c_int, [C.c_int, C.c_int, C.POINTER(c_float_p), c_int_p, C.c_int, C.c_int, C.POINTER(c_float_p), C.POINTER(c_float_p)]),
+    "convolutionCPU": (None, [c_float_p, c_float_p, c_float_p, c_float_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float]),
     "mvdSeparableConvolveNoAlloc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, c_int_p, c_float_p, c_float_p, c_float_p, C.c_int, C.c_int, C.c_float,
                                               C.c_void_p]),
     "mvdCreateMulti": (C.c_int, [C.POINTER(C.c_void_p), c_int_p, C.c_int, c_int_p, c_int_p, C.c_double, C.c_float]),

@@ -199,6 +199,14 @@ struct mvdContext {
     PeerTarget* d_peers_psi = nullptr;
     PeerTarget* d_peers_quot = nullptr;
     std::vector<void*> ipc_mappings;
+    // neighbour-only barrier in peer memory (mvdExportFlags / mvdAttachPeerFlags / mvdPeerSignal / mvdPeerWait)
+    unsigned int* d_flags = nullptr;  // slots 0 .. 31: written by the neighbours; slot 32: status of the bounded spin
+    PeerFlags peer_flags{};
+    void ensure_flags() {
+        if (d_flags) return;
+        MVD_CUDA(cudaMalloc(&d_flags, 64 * sizeof(unsigned int)));
+        MVD_CUDA(cudaMemset(d_flags, 0, 64 * sizeof(unsigned int)));
+    }
     // direct separable path
     bool direct_enabled = true;
     float* sep_tmp = nullptr;
@@ -359,6 +367,7 @@ static void detach_peers(mvdContext* c) {
     c->d_peers_psi = c->d_peers_quot = nullptr;
     for (void* p : c->ipc_mappings) cudaIpcCloseMemHandle(p);
     c->ipc_mappings.clear();
+    c->peer_flags.n = 0;
 }
 
 extern "C" int mvdDestroy(mvdContext* c) {
@@ -374,6 +383,7 @@ extern "C" int mvdDestroy(mvdContext* c) {
         if (c->sep_tmp) cudaFree(c->sep_tmp);
         if (c->psi) cudaFree(c->psi);
         if (c->quot) cudaFree(c->quot);
+        if (c->d_flags) cudaFree(c->d_flags);
         if (c->d_sum) cudaFree(c->d_sum);
         if (c->d_max) cudaFree(c->d_max);
         if (c->d_fi_sum) cudaFree(c->d_fi_sum);
@@ -394,11 +404,14 @@ extern "C" int mvdSetStream(mvdContext* c, void* s) {
     });
 }
 
+static void check_peer_status(mvdContext* c);
+
 extern "C" int mvdSynchronize(mvdContext* c) {
     return guarded([&] {
         require(c, "mvdSynchronize: null context");
         c->activate();
         MVD_CUDA(cudaStreamSynchronize(c->stream));
+        check_peer_status(c);
     });
 }
 
@@ -592,6 +605,7 @@ static void step_update(mvdContext* c, int v, int slot) {
 }
 
 static void read_stats(mvdContext* c, int first, int n, double* sum, double* mx) {
+    check_peer_status(c);
     if (n <= 0) return;
     require(first >= 0 && first + n <= c->stat_capacity, "statistics slot out of range");
     std::vector<unsigned int> bits(n);
@@ -859,6 +873,69 @@ extern "C" int mvdAttachPeer(mvdContext* c, const int peerBrickOffset[3], const 
         MVD_CUDA(cudaMemcpy(c->d_peers_quot, c->peers_quot.data(), c->peers_quot.size() * sizeof(PeerTarget), cudaMemcpyHostToDevice));
         for (auto& plan : c->plans) partition_for_peers(*plan, c->peers_psi.data(), (int)c->peers_psi.size());
     });
+}
+
+// ---- neighbour-only barrier of the fused exchange -----------------------------------------------------
+extern "C" int mvdExportFlags(mvdContext* c, unsigned char flagsHandle[64], void** flagsPointer) {
+    return guarded([&] {
+        require(c, "mvdExportFlags: null context");
+        c->activate();
+        c->ensure_flags();
+        if (flagsHandle) {
+            cudaIpcMemHandle_t h;
+            MVD_CUDA(cudaIpcGetMemHandle(&h, c->d_flags));
+            std::memcpy(flagsHandle, &h, 64);
+        }
+        if (flagsPointer) *flagsPointer = c->d_flags;
+    });
+}
+
+extern "C" int mvdAttachPeerFlags(mvdContext* c, const void* peerFlags, int kind, int theirSlotForMe, int mySlotForThem) {
+    return guarded([&] {
+        require(c && peerFlags, "mvdAttachPeerFlags: null argument");
+        require(kind == MVD_PEER_POINTER || kind == MVD_PEER_IPC, "mvdAttachPeerFlags: bad kind");
+        require(theirSlotForMe >= 0 && theirSlotForMe < 32 && mySlotForThem >= 0 && mySlotForThem < 32, "mvdAttachPeerFlags: slots are 0 .. 31");
+        require(c->peer_flags.n < kMaxPeers, "mvdAttachPeerFlags: too many neighbours");
+        c->activate();
+        c->ensure_flags();
+        unsigned int* p = nullptr;
+        if (kind == MVD_PEER_IPC) {
+            cudaIpcMemHandle_t h;
+            void* m = nullptr;
+            std::memcpy(&h, peerFlags, 64);
+            MVD_CUDA(cudaIpcOpenMemHandle(&m, h, cudaIpcMemLazyEnablePeerAccess));
+            c->ipc_mappings.push_back(m);
+            p = static_cast<unsigned int*>(m);
+        } else {
+            p = const_cast<unsigned int*>(static_cast<const unsigned int*>(peerFlags));
+        }
+        const int i = c->peer_flags.n++;
+        c->peer_flags.theirs[i] = p;
+        c->peer_flags.their_slot[i] = theirSlotForMe;
+        c->peer_flags.my_slot[i] = mySlotForThem;
+    });
+}
+
+static int peer_barrier(mvdContext* c, unsigned int value, int phase, const char* what) {
+    return guarded([&] {
+        require(c, what);
+        require(c->peer_flags.n > 0 && c->d_flags, "peer barrier: no neighbour flags attached (mvdAttachPeerFlags)");
+        c->activate();
+        MVD_CUDA(launch_peer_barrier(c->peer_flags, c->d_flags, value, c->d_flags + 32, phase, c->stream));
+        ++g_kernel_launches;
+    });
+}
+extern "C" int mvdPeerSignal(mvdContext* c, unsigned int value) { return peer_barrier(c, value, 0, "mvdPeerSignal: null context"); }
+extern "C" int mvdPeerWait(mvdContext* c, unsigned int value) { return peer_barrier(c, value, 1, "mvdPeerWait: null context"); }
+extern "C" int mvdPeerBarrier(mvdContext* c, unsigned int value) { return peer_barrier(c, value, 2, "mvdPeerBarrier: null context"); }
+
+// after a synchronisation: did a bounded spin of the peer barrier expire?
+static void check_peer_status(mvdContext* c) {
+    if (!c->d_flags || c->peer_flags.n == 0) return;
+    unsigned int st = 0;
+    MVD_CUDA(cudaMemcpyAsync(&st, c->d_flags + 32, sizeof(st), cudaMemcpyDeviceToHost, c->stream));
+    MVD_CUDA(cudaStreamSynchronize(c->stream));
+    if (st != 0) throw CudaError("peer barrier timed out: a neighbouring brick did not signal within ~10 s (crashed rank, or the ranks' step sequences differ)");
 }
 
 extern "C" int mvdDetachPeers(mvdContext* c) {
@@ -1905,4 +1982,171 @@ extern "C" int mvdSeparableConvolveNoAlloc(int device, const float* dSrc, float*
         MVD_CUDA(launch_separable(v, dim, taps, kmax, EPI_STORE, ep, tmp, static_cast<cudaStream_t>(cudaStream)));
         g_kernel_launches += 2;
     });
+}
+
+// ---- kernel preparation behind the C ABI ------------------------------------------
+// MVDeconInput.init / MVDeconFFT.init (MVDeconInput.java:43-49, MVDeconFFT.java:162-333) for callers without the Java
+// (or Python) host: kernel1 = normImg(psf), kernel2 by PSFTYPE.  Host arithmetic as in the reference, statement by
+// statement; the small zero-extended convolutions of the compound kernels run through the device engine.
+namespace {
+// correctly rounded sum of doubles (Shewchuk's exact partials; what the oracle's math.fsum computes).  The reference
+// accumulates in mpicbg.util.RealSum, a cascaded compensated sum that is exact for these sizes as well.
+double exact_sum(const std::vector<double>& x) {
+    std::vector<double> partials;
+    for (double v : x) {
+        size_t i = 0;
+        for (double y : partials) {
+            if (std::fabs(v) < std::fabs(y)) std::swap(v, y);
+            const double hi = v + y;
+            const double lo = y - (hi - v);
+            if (lo != 0.0) partials[i++] = lo;
+            v = hi;
+        }
+        partials.resize(i);
+        partials.push_back(v);
+    }
+    // sum the partials from the top, correcting the final rounding (as CPython's math.fsum does)
+    double hi = 0.0;
+    int n = (int)partials.size();
+    if (n > 0) {
+        hi = partials[--n];
+        double lo = 0.0;
+        while (n > 0) {
+            const double x1 = hi, y = partials[--n];
+            hi = x1 + y;
+            const double yr = hi - x1;
+            lo = y - yr;
+            if (lo != 0.0) break;
+        }
+        if (n > 0 && ((lo < 0.0 && partials[n - 1] < 0.0) || (lo > 0.0 && partials[n - 1] > 0.0))) {
+            const double y = lo * 2.0, x1 = hi + y;
+            if (y == x1 - hi) hi = x1;
+        }
+    }
+    return hi;
+}
+// AdjustInput.sumImg (AdjustInput.java:44-100): 2 * numThreads portions (FusionHelper.divideIntoPortions,
+// FusionHelper.java:236-260); the partial sum of the first portion is counted twice (:93-97) -- kept.
+double sum_img_quirk(const std::vector<float>& img, int num_threads) {
+    const size_t n = img.size(), parts = (size_t)num_threads * 2, chunk = n / parts, mod = n % parts;
+    std::vector<double> sums;
+    for (size_t i = 0; i < parts; ++i) {
+        const size_t start = i * chunk, len = chunk + (i == parts - 1 ? mod : 0);
+        std::vector<double> v(len);
+        for (size_t j = 0; j < len; ++j) v[j] = (double)img[start + j];
+        sums.push_back(exact_sum(v));
+    }
+    std::vector<double> all;
+    all.push_back(sums[0]);
+    all.insert(all.end(), sums.begin(), sums.end());
+    return exact_sum(all);
+}
+void norm_img(std::vector<float>& img, int num_threads) {  // AdjustInput.java:29-36: t = (float)((double) t / sum)
+    const double s = sum_img_quirk(img, num_threads);
+    for (float& t : img) t = (float)((double)t / s);
+}
+// Mirror.mirror along every dimension (Mirror.java:31-108, MVDeconFFT.java:315-323); for an even extent the two middle
+// positions are swapped twice, i.e. stay where they are (Mirror.java:72)
+std::vector<float> inverted_kernel(const std::vector<float>& k, const int d[3]) {
+    std::vector<float> cur = k, nxt(k.size());
+    for (int ax = 0; ax < 3; ++ax) {
+        const int n = d[ax];
+        std::vector<int> idx(n);
+        for (int i = 0; i < n; ++i) idx[i] = n - 1 - i;
+        if (n % 2 == 0) { idx[n / 2 - 1] = n / 2 - 1; idx[n / 2] = n / 2; }
+        for (int z = 0; z < d[2]; ++z)
+            for (int y = 0; y < d[1]; ++y)
+                for (int x = 0; x < d[0]; ++x) {
+                    const int c[3] = {x, y, z};
+                    int s[3] = {x, y, z};
+                    s[ax] = idx[c[ax]];
+                    nxt[((size_t)z * d[1] + y) * d[0] + x] = cur[((size_t)s[2] * d[1] + s[1]) * d[0] + s[0]];
+                }
+        cur.swap(nxt);
+    }
+    return cur;
+}
+}  // namespace
+
+static void convolve_host(int device, const float* src, const int dim[3], const float* kernel, const int k[3], int ext, float ext_value,
+                          float* out);
+
+extern "C" int mvdPrepareKernels(int device, int numViews, const float* const* psfs, const int* psfDims, int psfType, int numThreads,
+                                 float* const* kernel1, float* const* kernel2) {
+    return guarded([&] {
+        require(numViews >= 1 && psfs && psfDims && kernel1 && kernel2, "mvdPrepareKernels: null argument");
+        require(psfType >= 0 && psfType <= 3, "mvdPrepareKernels: psfType must be 0 OPTIMIZATION_II, 1 OPTIMIZATION_I, 2 EFFICIENT_BAYESIAN, 3 INDEPENDENT");
+        require(numThreads >= 1, "mvdPrepareKernels: numThreads must be positive");
+        const int V = numViews;
+        std::vector<std::vector<float>> k1(V);
+        for (int v = 0; v < V; ++v) {
+            const int* d = psfDims + 3 * v;
+            require(psfs[v] && kernel1[v] && kernel2[v] && d[0] > 0 && d[1] > 0 && d[2] > 0, "mvdPrepareKernels: bad view");
+            k1[v].assign(psfs[v], psfs[v] + (size_t)d[0] * d[1] * d[2]);
+        }
+        auto conv0 = [&](const std::vector<float>& in, const int* din, const std::vector<float>& k, const int* dk) {
+            // FFTConvolution(Views.extendZero(input), input, Views.extendZero(kernel), kernel, output): same extent as the input
+            std::vector<float> out(in.size());
+            convolve_host(device, in.data(), din, k.data(), dk, EXT_ZERO, 0.f, out.data());
+            return out;
+        };
+        // views are initialised in order: the kernels of later views are still un-normalised when an earlier view combines
+        // them (MVDeconInput.java:43-49)
+        for (int v = 0; v < V; ++v) {
+            const int* dv = psfDims + 3 * v;
+            norm_img(k1[v], numThreads);                                           // MVDeconFFT.java:165
+            std::vector<float> k2;
+            if (V == 1 || psfType == 3) {                                          // :174-180
+                k2 = inverted_kernel(k1[v], dv);
+            } else if (psfType == 2) {                                             // EFFICIENT_BAYESIAN :181-244
+                std::vector<float> tmp = inverted_kernel(k1[v], dv);
+                for (int w = 0; w < V; ++w) {
+                    if (w == v) continue;
+                    const int* dw = psfDims + 3 * w;
+                    std::vector<float> out = conv0(inverted_kernel(k1[v], dv), dv, k1[w], dw);
+                    out = conv0(out, dv, inverted_kernel(k1[w], dw), dw);
+                    for (size_t i = 0; i < tmp.size(); ++i) tmp[i] = out[i] * tmp[i];
+                }
+                norm_img(tmp, numThreads);
+                k2 = tmp;
+            } else if (psfType == 1) {                                             // OPTIMIZATION_I :245-291
+                std::vector<float> tmp = k1[v];
+                for (int w = 0; w < V; ++w) {
+                    if (w == v) continue;
+                    const int* dw = psfDims + 3 * w;
+                    const std::vector<float> out = conv0(k1[v], dv, inverted_kernel(k1[w], dw), dw);
+                    for (size_t i = 0; i < tmp.size(); ++i) tmp[i] = out[i] * tmp[i];
+                }
+                norm_img(tmp, numThreads);
+                k2 = inverted_kernel(tmp, dv);
+            } else {                                                               // OPTIMIZATION_II :292-302
+                std::vector<float> e = k1[v];
+                for (int i = 1; i < V; ++i)                                        // computeExponentialKernel :305-333
+                    for (size_t j = 0; j < e.size(); ++j) e[j] = e[j] * k1[v][j];
+                norm_img(e, numThreads);
+                k2 = inverted_kernel(e, dv);
+            }
+            std::memcpy(kernel1[v], k1[v].data(), k1[v].size() * sizeof(float));
+            std::memcpy(kernel2[v], k2.data(), k2.size() * sizeof(float));
+        }
+    });
+}
+
+// CUDASeparableConvolution.convolutionCPU (CUDASeparableConvolution.java:19-21; declared by the reference, never called):
+// in-place separable convolution with kernels of RADIUS kernelR* (2 R + 1 taps; a null kernel leaves its axis alone).  This
+// library has no CPU code: the same result is computed on device 0 by the kernels behind convolve_N.
+static int separable_hook(int N, float* image, const float* kx, const float* ky, const float* kz, int w, int h, int d, int cx, int cy,
+                          int cz, int oob, float oobv, int dev_id);
+extern "C" void convolutionCPU(float* image, float* kernelX, float* kernelY, float* kernelZ, int kernelRX, int kernelRY, int kernelRZ,
+                               int imageW, int imageH, int imageD, int outofbounds, float outofboundsvalue) {
+    if (kernelRX < 0 || kernelRY < 0 || kernelRZ < 0) { latch(1, "convolutionCPU: negative kernel radius"); return; }
+    const int r = std::max(kernelRX, std::max(kernelRY, kernelRZ)), N = 2 * r + 1;
+    auto centred = [&](const float* k, int rk) {  // kernels shorter than N are centred, like getFloatKernelPadded does for convolve_N
+        std::vector<float> p(N, 0.f);
+        if (k) std::memcpy(p.data() + (r - rk), k, (size_t)(2 * rk + 1) * sizeof(float));
+        return p;
+    };
+    const std::vector<float> px = centred(kernelX, kernelRX), py = centred(kernelY, kernelRY), pz = centred(kernelZ, kernelRZ);
+    separable_hook(N, image, px.data(), py.data(), pz.data(), imageW, imageH, imageD, kernelX != nullptr, kernelY != nullptr, kernelZ != nullptr,
+                   outofbounds, outofboundsvalue, 0);
 }

@@ -70,9 +70,9 @@ __device__ __forceinline__ int opaque(int x) {
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
-template <int BX, int BY> struct XYCfg {
+template <int BX, int BY, int NT_> struct XYCfgT {
     using L = PlaneLayout<BX>;
-    static constexpr int NT = XYThreads<BX, BY>::NT;
+    static constexpr int NT = NT_;
     static constexpr int H = BX / 2;
     static constexpr int TX = H / 8;            // threads per row, 8 packed complex each
     static constexpr int RPR = NT / TX;         // rows per round
@@ -90,6 +90,19 @@ template <int BX, int BY> struct XYCfg {
     // 228 KB per SM, 1 KB reserved per resident CTA (+ the inverse kernel's static reduction arrays)
     static constexpr int MIN_CTAS = NT > 256 ? 1 : ((SMEM_FWD + 1024 + 128) * 3 <= 233472 ? 3 : ((SMEM_FWD + 1024 + 128) * 2 <= 233472 ? 2 : 1));
 };
+#ifndef MVD_INV_MINCTAS
+#define MVD_INV_MINCTAS 2  // 2 x 256 threads at <= 128 registers beat 3 x 256 at 80 with spills (measured)
+#endif
+template <int BX, int BY> using XYCfg = XYCfgT<BX, BY, XYThreads<BX, BY>::NT>;
+// the inverse kernel's own thread count: MVD_INV_NT128 = three 128-thread CTAs per SM for 128 x 128 windows (experiment)
+#ifndef MVD_INV_NT128
+#define MVD_INV_NT128 1  // measured: inv_xy 11.17 -> 10.99 ms per four convolutions (168 registers, 20 B of spills instead of 176)
+#endif
+template <int BX, int BY> struct InvThreads {
+    static constexpr int NT = (MVD_INV_NT128 != 0 && BX == 128 && BY == 128) ? 128 : XYThreads<BX, BY>::NT;
+    static constexpr int MIN_CTAS_WANT = NT == 128 ? 3 : MVD_INV_MINCTAS;
+};
+template <int BX, int BY> using InvCfg = XYCfgT<BX, BY, InvThreads<BX, BY>::NT>;
 
 // ---------------------------------------------------------------------------------------------
 #ifndef MVD_FWD_MINCTAS
@@ -331,48 +344,24 @@ template <int BZ> struct ZCfg {
     // elements per thread: 512 = 16 x 16 x 2 (two exchanges), 256 = 16 x 16, 128 = 16 x 8, 64 = 8 x 8 (one exchange)
     static constexpr int EPT = BZ >= 512 ? MVD_Z_EPT512 : (BZ >= 128 ? 16 : 8);
     static constexpr int TZ = BZ / EPT;
-#ifndef MVD_Z_ASYNC
-#define MVD_Z_ASYNC 0  // measured on B200 (cfg3): 12.5 ms per iteration without, 14.0 - 17.4 ms with
-#endif
 #ifndef MVD_Z_PW
-#define MVD_Z_PW (MVD_Z_ASYNC ? 8 : 16)
+#define MVD_Z_PW 16
 #endif
-    static constexpr int PW = MVD_Z_PW;  // 8 (16): 64 (128) contiguous bytes per z index
+    static constexpr int PW = MVD_Z_PW;  // 16: 128 contiguous bytes per z index (32 / 64 / 128 / 256 bytes: 16.4 / 14.8 / 11.1 / 12.8 ms)
     static constexpr int THREADS = PW * TZ;
-    static constexpr bool ASYNC = MVD_Z_ASYNC != 0;
-#ifndef MVD_Z_PIPE
-#define MVD_Z_PIPE 0
-#endif
-    // PIPE: persistent grid, software-pipelined through registers -- the loads of the CTA's next item are
-    // issued before the current item is transformed (and land in a second register set), the kernel
-    // spectrum of the current item is staged in thread-private shared-memory slots by cp.async while the
-    // forward transform runs.  Needs 2 x EPT float2 registers per thread: fewer, fatter CTAs.
-    static constexpr bool PIPE = MVD_Z_PIPE != 0 && !ASYNC && BZ >= MVD_Z_PIPE;
-    // exchange buffer | twiddles | (ASYNC, PIPE) staging, EPT thread-private slots per thread
-    static constexpr size_t SMEM = (size_t)PW * BZ * sizeof(float2) * (ASYNC || PIPE ? 2 : 1) + (size_t)BZ * sizeof(float2);
+    // exchange buffer | twiddles
+    static constexpr size_t SMEM = (size_t)PW * BZ * sizeof(float2) + (size_t)BZ * sizeof(float2);
 #ifndef MVD_Z_MINCTAS512
-#define MVD_Z_MINCTAS512 (MVD_Z_ASYNC ? 768 / THREADS : 1024 / THREADS)
+#define MVD_Z_MINCTAS512 (1024 / THREADS)
 #endif
-    // shorter lines: 3 x 256 threads at <= 85 registers (measured faster than 4 x 256 at 64); the persistent ASYNC
-    // grid wants about 1024 threads per SM instead
-    static constexpr int MIN_CTAS_ = BZ >= 512 ? MVD_Z_MINCTAS512
-                                               : (ASYNC ? (1024 / THREADS > 16 ? 16 : 1024 / THREADS) : (THREADS >= 256 ? 3 : 4));
+    // shorter lines: 3 x 256 threads at <= 85 registers (measured faster than 4 x 256 at 64)
+    static constexpr int MIN_CTAS_ = BZ >= 512 ? MVD_Z_MINCTAS512 : (THREADS >= 256 ? 3 : 4);
     static constexpr int MIN_CTAS = MIN_CTAS_ < 1 ? 1 : MIN_CTAS_;
 };
 
-__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gmem_src) {
-    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-
-// ASYNC (off by default, kept for the measurement in DESIGN.md): the grid is persistent (ZCfg::MIN_CTAS CTAs per SM) and every thread copies the EPT elements
-// of the CTA's NEXT work item into thread-private shared-memory slots with cp.async while the current
-// item is transformed -- the HBM latency of an item is hidden behind the arithmetic of the one before
-// it, without holding registers and without extra barriers (a thread only reads slots it filled itself).
-// Work item -> (position block, tile).  Tiles run fastest so that the CTAs in flight read the same part of
-// the kernel spectrum; with MVD_Z_PGROUP = G > 1, G neighbouring position blocks (G * PW * 8 contiguous
-// bytes per z index) run fastest of all, so that CTAs in flight also share DRAM pages.
+// Work item -> (position block, tile): z_items.cuh.  Two round-1 experiments lived here and were removed in round 2 once the
+// TMA kernels superseded them (both measured slower): per-thread cp.async staging of the next item
+// (MVD_Z_ASYNC, 14.0 - 17.4 vs 12.5 ms per iteration) and a register software pipeline (MVD_Z_PIPE, 12.5 vs 11.1 ms).
 template <int BZ, int MODE>
 __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_kernel(float2* __restrict__ scratch, size_t tile_stride,
                                                                                      const float2* __restrict__ kspec,
@@ -383,78 +372,25 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float2* xch = reinterpret_cast<float2*>(smem_raw);
     float2* twz = xch + (size_t)PW * BZ;
-    float2* stage = twz + BZ + threadIdx.x;  // slot m of this thread: stage[m * NTH]
     const int tid = threadIdx.x;
     const int p = tid % PW, t = tid / PW;
     for (int i = tid; i < BZ; i += NTH) twz[i] = __ldg(&tw.t[ilog2<BZ>()][i]);
 
-    // work items = (position block, tile), tile fastest: the CTAs running at the same time read the
-    // same part of the kernel spectrum (L2 hits)
-    auto item_base = [&](int item, bool& valid, int& ti) -> float2* {
-        int pblk;
-        decode_item(item, n_tiles, pblk, ti);
-        const int pos = pblk * PW + p;
-        valid = pos < plane_elems;
-        return scratch + (size_t)ti * tile_stride + (valid ? pos : 0);
-    };
-    auto prefetch_item = [&](int item) {
-        if (item < n_items) {
-            bool nv;
-            int nti;
-            const float2* nb = item_base(item, nv, nti);
-            const unsigned pl = (unsigned)opaque(plane_elems);
-#pragma unroll
-            for (int m = 0; m < EPT; ++m) cp_async8(stage + m * NTH, nb + (unsigned)(t + m * TZ) * pl);
-        }
-    };
-    if constexpr (C::ASYNC) prefetch_item(blockIdx.x);
-    constexpr bool PIPE = C::PIPE && MODE == 1;
-    float2 nxt[PIPE ? EPT : 1];
-    auto load_item = [&](int it, float2 (&dst)[PIPE ? EPT : 1]) {
-        if constexpr (PIPE) {
-            if (it < n_items) {
-                bool nv;
-                int nti;
-                const float2* nb = item_base(it, nv, nti);
-                const unsigned pl = (unsigned)opaque(plane_elems);
-#pragma unroll
-                for (int m = 0; m < EPT; ++m) dst[m] = nb[(unsigned)(t + m * TZ) * pl];
-            }
-        }
-    };
-    load_item(blockIdx.x, nxt);
-
 #pragma unroll 1
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-    bool valid;
-    int ti;
-    float2* __restrict__ base = item_base(item, valid, ti);
-    int pblk_, ti_;
-    decode_item(item, n_tiles, pblk_, ti_);
-    const int pos = pblk_ * PW + p;
+    // work items = (position block, tile), tile fastest: the CTAs running at the same time read the
+    // same part of the kernel spectrum (L2 hits)
+    int pblk, ti;
+    decode_item(item, n_tiles, pblk, ti);
+    const int pos = pblk * PW + p;
+    const bool valid = pos < plane_elems;
+    float2* __restrict__ base = scratch + (size_t)ti * tile_stride + (valid ? pos : 0);
 
     // Element offsets are recomputed in every phase from a laundered copy of the plane size: the
     // loads, the spectrum reads and the stores use the same EPT addresses, and common-subexpression
     // elimination would otherwise keep all of them (2 registers each) alive across both transforms.
     float2 v[EPT];
-    int zlo_p = 0, zhi_p = 0;  // PIPE: planes to write back, requested before the transforms
-    if constexpr (PIPE) {
-        zlo_p = __ldg(&tiles[ti].e[2]) - __ldg(&tiles[ti].o[2]);
-        zhi_p = zlo_p + __ldg(&tiles[ti].n[2]);
-#pragma unroll
-        for (int m = 0; m < EPT; ++m) v[m] = nxt[m];
-        {   // this item's part of the kernel spectrum (L2) -> thread-private staging slots
-            const float2* kbp = kspec + (valid ? pos : 0);
-            const unsigned pl = (unsigned)opaque(plane_elems);
-#pragma unroll
-            for (int m = 0; m < EPT; ++m) cp_async8(stage + m * NTH, kbp + (unsigned)(t + m * TZ) * pl);
-        }
-        load_item(item + gridDim.x, nxt);
-    } else if constexpr (C::ASYNC) {
-        cp_async_wait_all();
-#pragma unroll
-        for (int m = 0; m < EPT; ++m) v[m] = stage[m * NTH];
-    } else {
+    {
         const unsigned pl = (unsigned)plane_elems;
 #pragma unroll
         for (int m = 0; m < EPT; ++m) v[m] = base[(unsigned)(t + m * TZ) * pl];
@@ -467,8 +403,6 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
     auto get = [&](int idx) { return xp[idx * PW]; };
     auto sync = [] { __syncthreads(); };
     line_fft<BZ, EPT, false>(v, t, twz, put, get, sync);
-    // the slots were consumed by the transform above (data dependence): refill them with the next item
-    if constexpr (C::ASYNC) prefetch_item(item + gridDim.x);
 
     if constexpr (MODE == 0) {
         if (valid) {
@@ -487,11 +421,6 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
 #endif
         constexpr int KB_ = BZ >= 512 ? MVD_Z_KB : MVD_Z_KB_SHORT;
         constexpr int KB = EPT >= KB_ ? KB_ : EPT;
-        if constexpr (PIPE) {
-            cp_async_wait_all();
-#pragma unroll
-            for (int m = 0; m < EPT; ++m) v[m] = cmul(v[m], stage[m * NTH]);
-        } else
 #pragma unroll
         for (int h = 0; h < EPT; h += KB) {
             float2 kk[KB];
@@ -504,15 +433,9 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
         }
         if constexpr (TZ > 1) __syncthreads();
         line_fft<BZ, EPT, true>(v, t, twz, put, get, sync);
-        int zlo, zhi;
-        if constexpr (PIPE) {
-            zlo = zlo_p;
-            zhi = zhi_p;
-        } else {
-            const Tile tile = tiles[ti];
-            zlo = tile.e[2] - tile.o[2];
-            zhi = zlo + tile.n[2];
-        }
+        const Tile tile = tiles[ti];
+        const int zlo = tile.e[2] - tile.o[2];
+        const int zhi = zlo + tile.n[2];
         if (valid) {
             const unsigned pl = (unsigned)opaque(plane_elems);
 #pragma unroll
@@ -523,17 +446,13 @@ __global__ void __launch_bounds__(ZCfg<BZ>::THREADS, ZCfg<BZ>::MIN_CTAS) z_pass_
         }
     }
     }  // items
-    if constexpr (C::ASYNC) cp_async_wait_all();
 }
 
-#ifndef MVD_INV_MINCTAS
-#define MVD_INV_MINCTAS 2  // 2 x 256 threads at <= 128 registers beat 3 x 256 at 80 with spills (measured)
-#endif
 template <int BX, int BY, int EPI, bool PUSH>
-__global__ void __launch_bounds__((XYThreads<BX, BY>::NT), (XYCfg<BX, BY>::MIN_CTAS < MVD_INV_MINCTAS ? XYCfg<BX, BY>::MIN_CTAS : MVD_INV_MINCTAS)) inv_xy_kernel(const float2* __restrict__ scratch, size_t tile_stride,
+__global__ void __launch_bounds__((InvThreads<BX, BY>::NT), (InvCfg<BX, BY>::MIN_CTAS < InvThreads<BX, BY>::MIN_CTAS_WANT ? InvCfg<BX, BY>::MIN_CTAS : InvThreads<BX, BY>::MIN_CTAS_WANT)) inv_xy_kernel(const float2* __restrict__ scratch, size_t tile_stride,
                                                                            const Tile* __restrict__ tiles, EpilogueArgs ep, int chunks,
                                                                            int n_items, Twiddles tw) {
-    using C = XYCfg<BX, BY>;
+    using C = InvCfg<BX, BY>;
     using L = PlaneLayout<BX>;
     constexpr int NT = C::NT;
     constexpr int H = C::H, P = L::P, TX = C::TX, RPR = C::RPR, TY = C::TY, CPR = C::CPR;
@@ -901,7 +820,7 @@ cudaError_t launch_z_pass(int bx, int by, int bz, int mode, float2* scratch, con
     {                                                                                                                  \
         const int n_pblk = (pe + ZCfg<BZ>::PW - 1) / ZCfg<BZ>::PW;                                                     \
         const int n_items = n_tiles * ((n_pblk + MVD_Z_PGROUP - 1) / MVD_Z_PGROUP * MVD_Z_PGROUP);                     \
-        const int cap = g_z_grid_cap > 0 ? g_z_grid_cap : ((ZCfg<BZ>::ASYNC || (ZCfg<BZ>::PIPE && mode == 1)) ? g_num_sms * ZCfg<BZ>::MIN_CTAS : 0); \
+        const int cap = g_z_grid_cap;                                                                                  \
         const int grid = cap > 0 ? std::min(n_items, cap) : n_items;                                                   \
         if (mode == 0) z_pass_kernel<BZ, 0><<<grid, ZCfg<BZ>::THREADS, ZCfg<BZ>::SMEM, st>>>(scratch, stride, kspec, d_tiles, pe, scale, n_tiles, n_items, to_dev(tw)); \
         else z_pass_kernel<BZ, 1><<<grid, ZCfg<BZ>::THREADS, ZCfg<BZ>::SMEM, st>>>(scratch, stride, kspec, d_tiles, pe, scale, n_tiles, n_items, to_dev(tw)); \
@@ -923,11 +842,11 @@ cudaError_t launch_inv_xy(int bx, int by, int bz, int epilogue, const float2* sc
     {                                                                                                                    \
         constexpr size_t sm = XYCfg<BX, BY>::SMEM_INV;                                                                       \
         const bool push = ep.peers != nullptr && ep.n_peers > 0;                                                         \
-        if (epilogue == EPI_STORE) inv_xy_kernel<BX, BY, EPI_STORE, false><<<grid, XYCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
-        else if (epilogue == EPI_QUOTIENT && !push) inv_xy_kernel<BX, BY, EPI_QUOTIENT, false><<<grid, XYCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
-        else if (epilogue == EPI_QUOTIENT) inv_xy_kernel<BX, BY, EPI_QUOTIENT, true><<<grid, XYCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
-        else if (!push) inv_xy_kernel<BX, BY, EPI_UPDATE, false><<<grid, XYCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
-        else inv_xy_kernel<BX, BY, EPI_UPDATE, true><<<grid, XYCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        if (epilogue == EPI_STORE) inv_xy_kernel<BX, BY, EPI_STORE, false><<<grid, InvCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else if (epilogue == EPI_QUOTIENT && !push) inv_xy_kernel<BX, BY, EPI_QUOTIENT, false><<<grid, InvCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else if (epilogue == EPI_QUOTIENT) inv_xy_kernel<BX, BY, EPI_QUOTIENT, true><<<grid, InvCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else if (!push) inv_xy_kernel<BX, BY, EPI_UPDATE, false><<<grid, InvCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
+        else inv_xy_kernel<BX, BY, EPI_UPDATE, true><<<grid, InvCfg<BX, BY>::NT, sm, st>>>(scratch, stride, d_tiles, ep, chunks, n_items, to_dev(tw)); \
     }
     MVD_XY_DISPATCH(bx, by, F);
 #undef F

@@ -189,7 +189,7 @@ Device& Device::get(int id) {
 Device::Device(int id) : id_(id) {
     cudaDeviceProp prop;
     MVD_CUDA(cudaGetDeviceProperties(&prop, id));
-    if (prop.major < 10)
+    if (prop.major != 10)  // the binary holds sm_100a code only: sm_12x would fail later with an opaque error
         throw CudaError(std::string("libmvdecon is built for sm_100a (B200); device '") + prop.name + "' is sm_" +
                         std::to_string(prop.major) + std::to_string(prop.minor));
     MVD_CUDA(configure_conv_kernels());

@@ -2,7 +2,12 @@
 
 namespace mvd {
 
-static constexpr int kSMs = 148;
+// grid-stride kernels: 8 CTAs per SM of the current device (148 on B200)
+static int sm_count() {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
+    return n;
+}
 
 __global__ void fill_kernel(float* __restrict__ p, size_t n, float v) {
     const size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -11,7 +16,7 @@ __global__ void fill_kernel(float* __restrict__ p, size_t n, float v) {
 
 cudaError_t launch_fill(float* p, size_t n, float v, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
-    const int blocks = (int)((n + 255) / 256 < (size_t)(kSMs * 8) ? (n + 255) / 256 : (size_t)(kSMs * 8));
+    const int blocks = (int)((n + 255) / 256 < (size_t)(sm_count() * 8) ? (n + 255) / 256 : (size_t)(sm_count() * 8));
     fill_kernel<<<blocks, 256, 0, st>>>(p, n, v);
     return cudaGetLastError();
 }
@@ -50,7 +55,7 @@ __global__ void __launch_bounds__(256) first_iteration_kernel(ViewPtrs views, si
 
 cudaError_t launch_first_iteration_sums(const ViewPtrs& views, size_t n, double* d_sum, unsigned long long* d_count, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
-    const int blocks = (int)((n + 255) / 256 < (size_t)(kSMs * 8) ? (n + 255) / 256 : (size_t)(kSMs * 8));
+    const int blocks = (int)((n + 255) / 256 < (size_t)(sm_count() * 8) ? (n + 255) / 256 : (size_t)(sm_count() * 8));
     first_iteration_kernel<<<blocks, 256, 0, st>>>(views, n, d_sum, d_count);
     return cudaGetLastError();
 }
@@ -98,10 +103,42 @@ cudaError_t launch_mask_never_updated(const ViewPtrs& views, const int brick[3],
                                       cudaStream_t st) {
     const size_t n = (size_t)brick[0] * brick[1] * brick[2];
     if (n == 0) return cudaSuccess;
-    const int blocks = (int)((n + 255) / 256 < (size_t)(kSMs * 8) ? (n + 255) / 256 : (size_t)(kSMs * 8));
+    const int blocks = (int)((n + 255) / 256 < (size_t)(sm_count() * 8) ? (n + 255) / 256 : (size_t)(sm_count() * 8));
     Int3 b, d, o;
     for (int i = 0; i < 3; ++i) { b.v[i] = brick[i]; d.v[i] = psi_dim[i]; o.v[i] = psi_off[i]; }
     mask_kernel<<<blocks, 256, 0, st>>>(views, b, psi, d, o);
+    return cudaGetLastError();
+}
+
+// ---- neighbour-only barrier in peer memory ---------------------------------------------------------------
+// phase 0 = signal, 1 = wait, 2 = both (one launch per exchange when every brick has its own GPU)
+__global__ void peer_barrier_kernel(PeerFlags pf, unsigned int* my_flags, unsigned int value, unsigned int* status, int phase) {
+    const int i = threadIdx.x;
+    if (i >= pf.n) return;
+    if (phase != 1) {
+        // everything this stream wrote before (the step kernels' ghost voxels in the neighbours' arrays) is ordered before the flag
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pf.theirs[i] + pf.their_slot[i]), "r"(value) : "memory");
+    }
+    if (phase != 0) {
+        const unsigned int* mine = my_flags + pf.my_slot[i];
+        const long long t0 = clock64();
+        for (;;) {
+            unsigned int seen;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
+            if ((int)(seen - value) >= 0) break;  // wrap-safe comparison
+            if (clock64() - t0 > 20000000000LL) {  // ~10 s: a neighbour died or the callers' step sequences differ
+                atomicExch(status, 1u);
+                break;
+            }
+            __nanosleep(200);
+        }
+    }
+}
+
+cudaError_t launch_peer_barrier(const PeerFlags& pf, unsigned int* my_flags, unsigned int value, unsigned int* status, int phase, cudaStream_t st) {
+    if (pf.n <= 0) return cudaSuccess;
+    peer_barrier_kernel<<<1, 32, 0, st>>>(pf, my_flags, value, status, phase);
     return cudaGetLastError();
 }
 

@@ -149,6 +149,23 @@ class MVDeconFFT:
             self.kernel2 = inv(e)
 
 
+def prepareKernels(psfs, iterationType, numThreads=8, device=0):
+    """MVDeconInput.init through the library (mvdPrepareKernels): (kernel1[], kernel2[]) for the views' PSFs, for hosts that
+    do not carry their own MVDeconFFT.init.  Same values as MVDeconInput.init below (bit for bit: the same host arithmetic,
+    the same device convolutions)."""
+    lib = _lib.load()
+    psfs = [np.ascontiguousarray(p, dtype=F32) for p in psfs]
+    V = len(psfs)
+    k1 = [np.empty_like(p) for p in psfs]
+    k2 = [np.empty_like(p) for p in psfs]
+    P = _lib.c_float_p * V
+    dims = (C.c_int * (3 * V))(*[int(x) for p in psfs for x in p.shape[::-1]])
+    _lib.check(lib.mvdPrepareKernels(int(device), V, P(*[p.ctypes.data_as(_lib.c_float_p) for p in psfs]), dims, PSFTYPE.ALL.index(iterationType),
+                                     int(numThreads), P(*[k.ctypes.data_as(_lib.c_float_p) for k in k1]),
+                                     P(*[k.ctypes.data_as(_lib.c_float_p) for k in k2])), "mvdPrepareKernels")
+    return k1, k2
+
+
 class MVDeconInput:
     """MVDeconInput.java:10-59."""
 

@@ -798,3 +798,82 @@ def test_blending_image_of_the_reference_main_program_on_the_device(m, o):
     ref = o.blending_weight(np.stack([xx, yy, np.ones_like(xx)], axis=-1), (n, n, 3), (100.0, 0.0, -10.0), (12.0, 150.0, 1.0))
     np.testing.assert_array_equal(w[0], ref)
     assert (w[0][150:350, 112:388] == 1).all() and (w[0][:, :101] == 0).all()
+
+
+def test_direct_path_near_its_threshold_and_small_lambda(m, o):
+    """the rank-1 substitution (sum |K - a x b x c| <= 1e-6 sum |K|) is an approximation the reference does
+    not make; hold it at the edge of its acceptance threshold, with a small lambda (where a cancelling Tikhonov evaluation
+    would lose bits), over 20 iterations: same result as the oracle on the kernel AS GIVEN and as the FFT engine."""
+    from spim_registration_b200 import synthetic
+    shape, V, iters, lam = (40, 48, 72), 2, 20, 0.0006
+    rng = np.random.default_rng(5)
+
+    def g(n, sigma):
+        x = np.arange(n, dtype=np.float64) - n // 2
+        return np.exp(-x * x / (2 * sigma * sigma))
+    psfs = []
+    for v in range(V):
+        sep = g(9, 1.3 + 0.3 * v)[:, None, None] * g(9, 1.1)[None, :, None] * g(9, 1.6 - 0.2 * v)[None, None, :]
+        noise = rng.standard_normal(sep.shape)
+        # a perturbation of 5e-7 of the kernel's L1 norm: still accepted as rank 1 after float rounding and normalisation
+        psfs.append((sep + noise * (5e-7 * np.abs(sep).sum() / np.abs(noise).sum())).astype(np.float32))
+    truth = synthetic.make_truth(shape, "blob", synthetic.SEED0 + 9)
+    imgs = [synthetic.degrade(o.convolve_extended(truth, (p / p.sum()).astype(np.float32), "mirror"), v, V, synthetic.SEED0 + 9)
+            for v, p in enumerate(psfs)]
+    weights = [np.float32(0.5)] * V
+    k1, k2 = o.init_kernels(psfs, "INDEPENDENT", 8)
+    ref, stats, _ = o.run_deconvolution(imgs, weights, k1, k2, iters, lam)
+    res = {}
+    for direct in (True, False):
+        res[direct] = m.MVDeconvolution(_views(m, imgs, [0.5] * V, psfs), "INDEPENDENT", iters, lam, directPath=direct)
+        assert rel_l2(res[direct].getPsi(), ref) <= LOOP_TOL
+    assert all(a > 0 and b > 0 for a, b in res[True].directPath), res[True].directPath
+    assert all(a == 0 and b == 0 for a, b in res[False].directPath)
+    assert rel_l2(res[True].getPsi(), res[False].getPsi()) <= 2e-5
+    rs = np.array([[s for s, _ in row] for row in stats])
+    # the substituted kernel differs by ~1e-6 of its norm: changes of ~1e-3 psi move by up to ~1e-3 of themselves
+    np.testing.assert_allclose(res[True].sumChange, rs, rtol=2e-3)
+
+
+# ---- kernel preparation behind the C ABI (SURVEY 8f row 2) and the declared-but-unused convolutionCPU ----------------------
+@pytest.mark.parametrize("psftype", ["EFFICIENT_BAYESIAN", "OPTIMIZATION_I", "OPTIMIZATION_II", "INDEPENDENT"])
+def test_prepare_kernels_entry_matches_oracle_and_host_mirror(m, o, psftype):
+    """mvdPrepareKernels == MVDeconInput.init: kernel1 bit-exact against the oracle (host arithmetic only, sumImg quirk and
+    Mirror's even-size quirk included), kernel2 within the convolution tolerance, and both bit-identical to the Python host
+    mirror, which does the same arithmetic with the same device convolutions.  Views of different, partly even extents."""
+    from spim_registration_b200 import synthetic
+    from spim_registration_b200.deconvolution import prepareKernels
+    psfs = synthetic.make_psfs(3, (9, 7, 11), extracted=True)
+    psfs[1] = np.ascontiguousarray(psfs[1][:, :6, :8])           # another extent, even in x and y
+    k1, k2 = prepareKernels(psfs, psftype, 8)
+    r1, r2 = o.init_kernels(psfs, psftype, 8)
+    inp = _views(m, [np.ones((4, 4, 4), np.float32)] * 3, [1.0] * 3, psfs)
+    inp.init(psftype, 8)
+    for v, view in enumerate(inp.getViews()):
+        np.testing.assert_array_equal(k1[v], r1[v])
+        assert rel_l2(k2[v], r2[v]) <= 5e-6
+        np.testing.assert_array_equal(k1[v], view.getKernel1())
+        np.testing.assert_array_equal(k2[v], view.getKernel2())
+    single = prepareKernels(psfs[:1], psftype, 8)                 # one view: kernel2 is the mirrored kernel1 for every type
+    np.testing.assert_array_equal(single[1][0], o.compute_inverted_kernel(single[0][0]))
+
+
+def test_convolution_cpu_symbol_runs_on_the_device(m, o, lib):
+    """CUDASeparableConvolution.convolutionCPU (declared at CUDASeparableConvolution.java:19-21, called nowhere): kernels given
+    by RADIUS, different per axis, one axis left alone -- computed by the device kernels behind convolve_N."""
+    import spim_registration_b200._lib as L
+    rng = np.random.default_rng(31)
+    f = rng.random((30, 40, 50), dtype=np.float32) + np.float32(0.1)
+    kx = rng.random(2 * 3 + 1).astype(np.float32)
+    kz = rng.random(2 * 7 + 1).astype(np.float32)
+    kx /= kx.sum()
+    kz /= kz.sum()
+    for oob, mode in ((0, "zero"), (1, "const"), (2, "clamp")):
+        got = f.copy()
+        lib.convolutionCPU(got.ctypes.data_as(L.c_float_p), kx.ctypes.data_as(L.c_float_p), None, kz.ctypes.data_as(L.c_float_p), 3, 0, 7,
+                           50, 40, 30, oob, 0.6)
+        assert rel_l2(got, o.separable_convolve(f, kx, None, kz, mode, 0.6)) <= CONV_TOL
+    big = np.full(2 * 40 + 1, 1.0 / 81, np.float32)               # radius 40: beyond the direct kernels, FFT engine axis by axis
+    got = f.copy()
+    lib.convolutionCPU(got.ctypes.data_as(L.c_float_p), None, big.ctypes.data_as(L.c_float_p), None, 0, 40, 0, 50, 40, 30, 2, 0.0)
+    assert rel_l2(got, o.separable_convolve(f, None, big, None, "clamp")) <= CONV_TOL
