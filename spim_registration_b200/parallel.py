@@ -209,26 +209,42 @@ class ShardedDeconvolution:
                     out.append((r, off, size))
         return out
 
+    def _slot(self, coords):
+        """Slot of the brick at `coords` in THIS brick's flag array: the 3 x 3 x 3 code of its offset."""
+        d = [coords[i] - self.coords[i] for i in range(3)]
+        return (d[0] + 1) + 3 * (d[1] + 1) + 9 * (d[2] + 1)
+
     def attach_peers(self):
         """Switch to the fused exchange (mvdAttachPeer, include/mvdecon.h): the step kernels store
         ghost voxels straight into the neighbours' arrays over NVLink; between the steps only a
-        barrier remains.  One process per GPU: the arrays are shared through CUDA IPC handles."""
+        barrier remains.  One process per GPU: the arrays are shared through CUDA IPC handles.
+        The barrier is neighbour-only, in peer memory (mvdPeerBarrier: every rank stores the step number into its
+        neighbours' flag arrays and waits for theirs); MVD_BARRIER=nccl keeps round 1's 4-byte all-reduce."""
         if self.world == 1:
             return
+        import os
         torch, L = self.torch, self.L
         for d in range(3):
             assert self.grid[d] == 1 or self.size[d] >= self.ghost[d], "bricks thinner than the ghost layer are not supported"
-        hp, hq = (C.c_ubyte * 64)(), (C.c_ubyte * 64)()
+        hp, hq, hf = (C.c_ubyte * 64)(), (C.c_ubyte * 64)(), (C.c_ubyte * 64)()
         L.check(self.lib.mvdExportArrays(self.ctx, hp, hq), "mvdExportArrays")
+        L.check(self.lib.mvdExportFlags(self.ctx, hf, None), "mvdExportFlags")
         dev = self._arrays[0][0].device
-        mine = torch.tensor(list(bytes(hp) + bytes(hq)), dtype=torch.uint8, device=dev)
+        mine = torch.tensor(list(bytes(hp) + bytes(hq) + bytes(hf)), dtype=torch.uint8, device=dev)
         every = [torch.empty_like(mine) for _ in range(self.world)]
         self.dist.all_gather(every, mine)
+        self.flag_barrier = os.environ.get("MVD_BARRIER", "flags") == "flags"
         for r, off, size in self.neighbours():
             hb = bytes(every[r].cpu().numpy().tobytes())
-            a, b = C.create_string_buffer(hb[:64], 64), C.create_string_buffer(hb[64:], 64)
+            a, b = C.create_string_buffer(hb[:64], 64), C.create_string_buffer(hb[64:128], 64)
             L.check(self.lib.mvdAttachPeer(self.ctx, L.int3(off), L.int3(size), a, b, 1, -1), "mvdAttachPeer")
+            if self.flag_barrier:
+                nc = (r % self.grid[0], (r // self.grid[0]) % self.grid[1], r // (self.grid[0] * self.grid[1]))
+                mine_in_theirs = 26 - self._slot(nc)   # the code of the opposite offset
+                L.check(self.lib.mvdAttachPeerFlags(self.ctx, C.create_string_buffer(hb[128:192], 64), 1, mine_in_theirs, self._slot(nc)),
+                        "mvdAttachPeerFlags")
         self._flag = torch.zeros(1, dtype=torch.float32, device=dev)
+        self._barrier_count = 0
         self.fused = True
         self.dist.barrier()
 
@@ -256,15 +272,19 @@ class ShardedDeconvolution:
             t, off = self._arrays[0]
             exchange_ghosts(t, off, self.size[::-1], self.ghost, self.coords, self.grid, self.dist)
             if self.fused:
-                self.dist.all_reduce(self._flag)
+                self.dist.all_reduce(self._flag)   # rare (once per mvdSetPsi): a collective is fine here
 
     def _exchange(self, which):
         if self.world == 1:
             return
         if self.fused:
-            # the ghost layers were written by the neighbours' step kernels; every brick must have
+            # the ghost layers were written by the neighbours' step kernels; every NEIGHBOUR must have
             # finished the step before the next one reads them (stream-ordered, no host sync)
-            self.dist.all_reduce(self._flag)
+            if getattr(self, "flag_barrier", False):
+                self._barrier_count += 1
+                self.L.check(self.lib.mvdPeerBarrier(self.ctx, self._barrier_count), "mvdPeerBarrier")
+            else:
+                self.dist.all_reduce(self._flag)
             return
         t, off = self._arrays[which]
         exchange_ghosts(t, off, self.size[::-1], self.ghost, self.coords, self.grid, self.dist)
@@ -325,9 +345,10 @@ class LocalBrickGroup:
     same library calls and the same exchange schedule as the multi-process path, without
     torch.distributed.  Used by the single-GPU parity test of the brick/ghost code paths."""
 
-    def __init__(self, dim_xyz, grid, imgs, weights, kernel1, kernel2, lam, device=0):
+    def __init__(self, dim_xyz, grid, imgs, weights, kernel1, kernel2, lam, device=0, use_flags=False):
         import torch
         self.torch = torch
+        self.use_flags = use_flags
         self.grid, self.dim = tuple(grid), tuple(dim_xyz)
         self.world = grid[0] * grid[1] * grid[2]
         self.bricks = []
@@ -348,11 +369,29 @@ class LocalBrickGroup:
                 peer = self.bricks[r]
                 pp, pq = peer._arrays[0][0].data_ptr(), peer._arrays[1][0].data_ptr()
                 b.L.check(b.lib.mvdAttachPeer(b.ctx, b.L.int3(off), b.L.int3(size), C.c_void_p(pp), C.c_void_p(pq), 0, -1), "mvdAttachPeer")
+                if self.use_flags:
+                    fp = C.c_void_p()
+                    peer.L.check(peer.lib.mvdExportFlags(peer.ctx, None, C.byref(fp)), "mvdExportFlags")
+                    b.L.check(b.lib.mvdAttachPeerFlags(b.ctx, fp, 0, 26 - b._slot(peer.coords), b._slot(peer.coords)), "mvdAttachPeerFlags")
         self.fused = True
+        self._barrier_count = 0
 
     def _exchange(self, which):
         if self.fused:
-            return  # every brick runs on the same stream: the steps are already ordered
+            # every brick runs on the same stream: the steps are already ordered.  With use_flags the neighbour-only flag
+            # barrier of the multi-process path is exercised as well -- ALL bricks signal before ANY brick waits (kernels of
+            # several bricks on one GPU that wait for one another may never run at the same time)
+            if self.use_flags:
+                self._barrier_count += 1
+                for b in self.bricks:
+                    if b.neighbours():
+                        b.L.check(b.lib.mvdPeerSignal(b.ctx, self._barrier_count), "mvdPeerSignal")
+                for b in self.bricks:
+                    if b.neighbours():
+                        b.L.check(b.lib.mvdPeerWait(b.ctx, self._barrier_count), "mvdPeerWait")
+                for b in self.bricks:
+                    b.L.check(b.lib.mvdSynchronize(b.ctx), "mvdSynchronize")   # raises if a bounded spin expired
+            return
         # axis by axis, full-extent slabs (edges and corners travel through the later axes)
         for axis in (0, 1, 2):
             dimt = 2 - axis

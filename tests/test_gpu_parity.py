@@ -877,3 +877,32 @@ def test_convolution_cpu_symbol_runs_on_the_device(m, o, lib):
     got = f.copy()
     lib.convolutionCPU(got.ctypes.data_as(L.c_float_p), None, big.ctypes.data_as(L.c_float_p), None, 0, 40, 0, 50, 40, 30, 2, 0.0)
     assert rel_l2(got, o.separable_convolve(f, None, big, None, "clamp")) <= CONV_TOL
+
+
+def test_peer_flag_barrier_on_one_gpu(m, o):
+    """The neighbour-only flag barrier of the multi-process path (mvdExportFlags / mvdAttachPeerFlags / mvdPeerSignal /
+    mvdPeerWait) on one GPU: every brick stores the step number into its neighbours' flag arrays, then every brick waits
+    for its neighbours' -- signals before waits, because kernels of several bricks on one GPU that wait for one another may
+    never run at the same time.  Same result as the copy exchange, bit for bit; a wait nobody signals for expires."""
+    from spim_registration_b200 import synthetic
+    from spim_registration_b200.parallel import LocalBrickGroup
+    shape, V, grid = (37, 50, 150), 2, (2, 2, 2)
+    ds = _dataset(o, shape, V, (9, 7, 11), seed=5)
+    weights = synthetic.blending_weights(shape, V)
+    k1, k2 = o.init_kernels(ds["psfs"], "EFFICIENT_BAYESIAN", 8)
+    out = []
+    for flags in (False, True):
+        grp = LocalBrickGroup(shape[::-1], grid, ds["imgs"], weights, k1, k2, 0.006, use_flags=flags)
+        try:
+            grp.init_psi_average()
+            if flags:
+                grp.attach_peers()
+            else:
+                grp._exchange(0)
+            grp.run_iterations(3)
+            if flags:
+                assert grp._barrier_count == 2 * 3 * V          # two exchanges per view and iteration went through the flags
+            out.append(grp.get_psi())
+        finally:
+            grp.close()
+    np.testing.assert_array_equal(out[0], out[1])

@@ -124,3 +124,26 @@ def test_sharded_schedule_equals_single_brick_gloo(grid):
         assert p.exitcode == 0
     for rank, err in res:
         assert err <= 2e-6, (rank, err)
+
+
+def test_brick_grid_by_window_cost():
+    """With the kernel extent given the grid minimises the planner's FFT-window volume of the largest brick
+    (parallel.axis_window_cost mirrors csrc/engine.cu plan_axis); without it the round-1 rule (longest axis first)."""
+    from spim_registration_b200.parallel import XY_WINDOWS, Z_WINDOWS, axis_window_cost, brick_grid, brick_of
+    assert axis_window_cost(1024, 31, 4, XY_WINDOWS) == 11 * (128 + 6)                # eleven 128-point windows of 96 outputs each
+    assert axis_window_cost(512, 31, 1, Z_WINDOWS) == (512 + 6) + (64 + 6)
+    assert brick_grid(8, (1024, 1024, 512)) == (2, 2, 2)
+    assert brick_grid(8, (1024, 1024, 512), (31, 31, 31)) == (2, 4, 1)                # 1.93 x window inflation instead of 2.36 x
+    assert brick_grid(8, (2048, 2048, 1024), (31, 31, 31)) == (1, 4, 2)
+    assert brick_grid(1, (1024, 1024, 512), (31, 31, 31)) == (1, 1, 1)
+    for world in (2, 4, 8):
+        g = brick_grid(world, (192, 160, 96), (15, 15, 15))
+        assert g[0] * g[1] * g[2] == world
+        seen = set()
+        for r in range(world):                                                       # bricks tile the volume exactly
+            off, size, _ = brick_of(r, g, (192, 160, 96))
+            seen.add((off, size))
+            assert all(s >= 7 for s in size)
+        assert sum(s[0] * s[1] * s[2] for _, s in seen) == 192 * 160 * 96
+    # a volume too thin to be cut along z for this kernel: no grid cuts it there
+    assert brick_grid(8, (1024, 1024, 20), (31, 31, 31))[2] == 1
