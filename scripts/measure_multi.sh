@@ -9,10 +9,12 @@ run() {  # N config steps extra...
         || { echo "cfg$c n$n FAILED"; tail -5 gpurun_out/bench_${TAG}_cfg${c}_n$n.err; }
 }
 timeout 200 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "multi_device" 2>&1 | tail -2
+if [ -n "$FULL" ]; then run 4 3 10 --no-parity; run 2 3 10 --no-parity; run 8 5 5 --no-parity; fi
+run 8 3 20 --no-parity && mv gpurun_out/bench_${TAG}_cfg3_n8.json gpurun_out/bench_${TAG}_cfg3_n8_20steps.json
+MVD_BARRIER=nccl timeout 420 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29599 \
+    bench.py --gpus 8 --steps 10 --warmup 3 --no-parity > gpurun_out/bench_${TAG}_cfg3_n8_ncclbarrier.json 2> gpurun_out/bench_${TAG}_cfg3_n8_ncclbarrier.err \
+    || tail -3 gpurun_out/bench_${TAG}_cfg3_n8_ncclbarrier.err
 run 8 3 10
-run 4 3 10 --no-parity
-run 2 3 10 --no-parity
-run 8 5 5 --no-parity
 timeout 420 python bench.py --gpus 8 --single-process --steps 10 --warmup 3 > gpurun_out/bench_${TAG}_cfg3_n8_single.json 2> gpurun_out/bench_${TAG}_cfg3_n8_single.err || tail -5 gpurun_out/bench_${TAG}_cfg3_n8_single.err
 for f in gpurun_out/bench_${TAG}_cfg*_n*.json; do python - "$f" <<'PY'
 import json, sys
