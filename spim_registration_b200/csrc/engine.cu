@@ -317,7 +317,8 @@ std::unique_ptr<KernelSpectra> build_spectra(Device& dev, const ConvPlan& plan, 
         MVD_CUDA(launch_z_pass(bx, by, bz, 0, d_spec, nullptr, d_tile + ci, 1, scale, dev.twiddles(), st));
         g_kernel_launches += 3;
         float2* d_spec_t = nullptr;
-        if (z_warp_supported(bz) && plane_elems(bx, by) % 16 == 0) {
+        // 512-point classes by default; 256-point ones only with z_warp = 2 (measured slower than the register-loading kernel there)
+        if (z_warp_supported(bz) && (bz == 512 || g_use_z_warp.load() >= 2) && plane_elems(bx, by) % 16 == 0) {
             MVD_CUDA(cudaMalloc(&d_spec_t, tile_scratch_elems(bx, by, bz) * sizeof(float2)));
             spec->per_class_t.push_back(d_spec_t);
             MVD_CUDA(launch_transpose_spectrum(d_spec, d_spec_t, (int)plane_elems(bx, by), bz, st));
@@ -459,7 +460,7 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
             if (prof) { prof->end(ls); prof->begin(1, cnt * pe * bz * 8.0 + pe * bz * 8.0 + nz_sum * pe * 8.0, ls); }
             const int zlo = c.tiles[s].e[2] - c.tiles[s].o[2];  // the same for every tile of a plan
             bool z_done = false;
-            if (g_use_z_warp.load() && z_warp_supported(bz) && spec.per_class_t[ci]) {
+            if (g_use_z_warp.load() && z_warp_supported(bz) && (bz == 512 || g_use_z_warp.load() >= 2) && spec.per_class_t[ci]) {
                 const cudaError_t e = launch_z_pass_warp(bx, by, bz, buf, spec.per_class_t[ci], cnt, zlo, c.max_nz, dev.sm_count(), dev.twiddles(), ls);
                 if (e != cudaErrorNotSupported) {
                     MVD_CUDA(e);

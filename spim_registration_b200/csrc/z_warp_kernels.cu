@@ -28,16 +28,36 @@
 
 namespace mvd {
 
-namespace zw {
-constexpr int BZ = 512, PW = 16, THREADS = PW * 32;
-constexpr int XP = BZ + BZ / 16;                           // padded private line: one pad element per 16
-constexpr unsigned SLOT_BYTES = PW * BZ * sizeof(float2);  // 65536
-constexpr size_t OFF_L = 0, OFF_ST = SLOT_BYTES, OFF_X = 2 * (size_t)SLOT_BYTES;
-constexpr size_t OFF_TW3 = OFF_X + (size_t)PW * XP * sizeof(float2);
-constexpr size_t OFF_BAR = OFF_TW3 + 256 * sizeof(float2);
-constexpr size_t SMEM = OFF_BAR + 64;
-constexpr int TC = 11;  // tiles a CTA does per position block before it takes the next unit
-}  // namespace zw
+// BZ = 512: 16 elements per lane, passes 16 x 16 x 2; BZ = 256: 8 elements per lane, passes 8 x 8 x 4
+template <int BZ> struct ZW {
+    static constexpr int EPT = BZ / 32;                // elements per lane
+    static constexpr int R2 = BZ / (EPT * EPT);        // radix of the third pass (2 or 4)
+    static constexpr int NB = EPT / R2;                // butterflies per lane in the third pass
+    static constexpr int PW = 16, THREADS = PW * 32;
+    static constexpr int XP = BZ + BZ / EPT;           // padded private line: one pad element per EPT
+    static constexpr unsigned SLOT_BYTES = PW * BZ * sizeof(float2);  // 65536 / 32768
+    static constexpr int NBOX = BZ / 256;              // a box holds at most 256 rows
+    static constexpr size_t OFF_L = 0, OFF_ST = SLOT_BYTES, OFF_X = 2 * (size_t)SLOT_BYTES;
+    static constexpr size_t OFF_TW3 = OFF_X + (size_t)PW * XP * sizeof(float2);
+    static constexpr size_t OFF_BAR = OFF_TW3 + 256 * sizeof(float2);
+    static constexpr size_t SMEM = OFF_BAR + 64;
+    static constexpr int MIN_CTAS = BZ >= 512 ? 1 : 2;  // 200 KB / 101 KB of shared memory
+    static_assert(BZ == 512 || BZ == 256, "warp-local lines: 512 or 256 points");
+};
+// Tiles a CTA does per position block before it takes the next unit (the line's kernel-spectrum values stay in registers
+// across them): chosen per launch so that the most loaded CTA has the least work.
+static int choose_tiles_per_unit(int n_tiles, int n_pblk, int grid) {
+    int best_tc = 1;
+    double best = 1e300;
+    for (int tc = 1; tc <= 16 && tc <= n_tiles; ++tc) {
+        const int chunks = (n_tiles + tc - 1) / tc;
+        const long long units = (long long)chunks * n_pblk;
+        const long long rounds = (units + grid - 1) / grid;
+        const double cost = (double)rounds * (tc + 0.5);  // + 0.5: a unit reloads its spectrum values (half an item's traffic)
+        if (cost < best) { best = cost; best_tc = tc; }
+    }
+    return best_tc;
+}
 
 // byte offset of element (z, p) inside a landing / staging buffer written or read by the TMA unit with the 128-byte
 // swizzle: rows of 128 B (16 positions), the 16-byte chunk index is XORed with the row index modulo 8
@@ -45,49 +65,61 @@ __device__ __forceinline__ unsigned zw_swz(int z, int p) {
     return (unsigned)z * 128u + ((((unsigned)p >> 1) ^ ((unsigned)z & 7u)) << 4) + ((unsigned)p & 1u) * 8u;
 }
 
-// Passes 2 and 3 of the 512-point line FFT inside a warp, after the leading radix-16 butterfly: lane t holds the
+// Passes 2 and 3 of the line FFT inside a warp, after the leading radix-EPT butterfly: lane t holds the
 // butterfly's outputs in v on entry and X[t + 32 m] on return.  Same passes and arithmetic as
-// line_fft<512, 16, INV> (fft_device.cuh); xw = the warp's padded line buffer.
-template <bool INV>
-__device__ __forceinline__ void warp_fft512_tail(float2 (&v)[16], int t, float2* __restrict__ xw, const float2 (&tw2)[15],
-                                                 const float2* __restrict__ tw3) {
-    {   // pass 1 output r of lane t -> position 16 t + r; pad(16 t + r) = 17 t + r
-        float2* p = xw + 17 * t;
+// line_fft<BZ, EPT, INV> (fft_device.cuh); xw = the warp's padded line buffer (pad(i) = i + i / EPT: every access
+// pattern below is conflict free for 8-byte accesses).
+template <int BZ, bool INV>
+__device__ __forceinline__ void warp_fft_tail(float2 (&v)[ZW<BZ>::EPT], int t, float2* __restrict__ xw, const float2 (&tw2)[ZW<BZ>::EPT - 1],
+                                              const float2* __restrict__ tw3) {
+    constexpr int EPT = ZW<BZ>::EPT, R2 = ZW<BZ>::R2, NB = ZW<BZ>::NB;
+    constexpr int LG = EPT == 16 ? 4 : 3;
+    {   // pass 1 output r of lane t -> position EPT t + r; pad(EPT t + r) = (EPT + 1) t + r
+        float2* p = xw + (EPT + 1) * t;
 #pragma unroll
-        for (int r = 0; r < 16; ++r) p[r] = v[r];
+        for (int r = 0; r < EPT; ++r) p[r] = v[r];
     }
     __syncwarp();
-    const float2* g = xw + t + (t >> 4);  // pad(t + 32 m) = t + (t >> 4) + 34 m
+    const float2* g = xw + t + (t >> LG);  // pad(t + 32 m) = t + (t >> LG) + (32 + 32 / EPT) m
+    constexpr int GS = 32 + 32 / EPT;
 #pragma unroll
-    for (int m = 0; m < 16; ++m) v[m] = g[34 * m];
+    for (int m = 0; m < EPT; ++m) v[m] = g[GS * m];
     __syncwarp();
-    // pass 2: j = t, k = t & 15, twiddles w512^(2 k r), radix 16; output r -> position 256 (t >> 4) + k + 16 r
+    // pass 2: j = t, k = t & (EPT - 1), twiddles w^(k r BZ / EPT^2), radix EPT; output r -> position EPT (t - k) + k + EPT r
 #pragma unroll
-    for (int r = 1; r < 16; ++r) v[r] = ctw<INV>(v[r], tw2[r - 1]);
-    dft16<INV>(v);
+    for (int r = 1; r < EPT; ++r) v[r] = ctw<INV>(v[r], tw2[r - 1]);
+    dftR<EPT, INV>(v);
     {
-        float2* p = xw + 272 * (t >> 4) + (t & 15);  // pad(...) = 272 (t >> 4) + k + 17 r
+        float2* p = xw + (EPT + 1) * EPT * (t >> LG) + (t & (EPT - 1));  // pad(...) = (EPT + 1)(t - k) + k + (EPT + 1) r
 #pragma unroll
-        for (int r = 0; r < 16; ++r) p[17 * r] = v[r];
+        for (int r = 0; r < EPT; ++r) p[(EPT + 1) * r] = v[r];
     }
     __syncwarp();
 #pragma unroll
-    for (int m = 0; m < 16; ++m) v[m] = g[34 * m];
+    for (int m = 0; m < EPT; ++m) v[m] = g[GS * m];
     __syncwarp();  // the buffer may be overwritten by the next transform
-    // pass 3: radix 2 on (v[b], v[b + 8]), j = t + 32 b, twiddle w512^j
+    // pass 3: radix R2 on (v[b], v[b + NB], ...), j = t + 32 b, twiddles w^(j r)
 #pragma unroll
-    for (int b = 0; b < 8; ++b) {
-        const float2 x1 = ctw<INV>(v[b + 8], tw3[t + 32 * b]);
-        const float2 x0 = v[b];
-        v[b] = cadd(x0, x1);
-        v[b + 8] = csub(x0, x1);
+    for (int b = 0; b < NB; ++b) {
+        float2 x[R2];
+#pragma unroll
+        for (int r = 0; r < R2; ++r) x[r] = v[b + r * NB];
+#pragma unroll
+        for (int r = 1; r < R2; ++r) x[r] = ctw<INV>(x[r], tw3[(t + 32 * b) * r]);
+        dftR<R2, INV>(x);
+#pragma unroll
+        for (int r = 0; r < R2; ++r) v[b + r * NB] = x[r];
     }
 }
 
-__global__ void __launch_bounds__(zw::THREADS, 1)
+template <int BZ>
+__global__ void __launch_bounds__(ZW<BZ>::THREADS, ZW<BZ>::MIN_CTAS)
     z_warp_kernel(const __grid_constant__ CUtensorMap map_ld, const __grid_constant__ CUtensorMap map_st, const float2* __restrict__ kspec_t,
-                  int n_tiles, int n_pblk, int n_chunks, Twiddles tw) {
-    using namespace zw;
+                  int n_tiles, int n_pblk, int n_chunks, int TC, Twiddles tw) {
+    using C = ZW<BZ>;
+    constexpr int EPT = C::EPT, PW = C::PW, THREADS = C::THREADS, XP = C::XP;
+    constexpr unsigned SLOT_BYTES = C::SLOT_BYTES;
+    constexpr size_t OFF_L = C::OFF_L, OFF_ST = C::OFF_ST, OFF_X = C::OFF_X, OFF_TW3 = C::OFF_TW3, OFF_BAR = C::OFF_BAR;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* L = smem_raw + OFF_L;
     unsigned char* ST = smem_raw + OFF_ST;
@@ -100,10 +132,10 @@ __global__ void __launch_bounds__(zw::THREADS, 1)
     const int tid = threadIdx.x;
     const int w = tid >> 5, t = tid & 31;  // warp = plane position inside the block, lane = z residue
     float2* xw = reinterpret_cast<float2*>(smem_raw + OFF_X) + (size_t)w * XP;
-    for (int i = tid; i < 256; i += THREADS) tw3[i] = __ldg(&tw.t[9][i]);
-    float2 tw2[15];
+    for (int i = tid; i < 256; i += THREADS) tw3[i] = __ldg(&tw.t[ilog2<BZ>()][i]);
+    float2 tw2[EPT - 1];
 #pragma unroll
-    for (int r = 1; r < 16; ++r) tw2[r - 1] = __ldg(&tw.t[9][2 * (t & 15) * r]);
+    for (int r = 1; r < EPT; ++r) tw2[r - 1] = __ldg(&tw.t[ilog2<BZ>()][(BZ / (EPT * EPT)) * (t & (EPT - 1)) * r]);
     if (tid == 0) {
         tma::mbar_init(full_l, 1);
         tma::mbar_init(st_free, 1);
@@ -129,17 +161,17 @@ __global__ void __launch_bounds__(zw::THREADS, 1)
     auto issue_load = [&](const Item& it) {  // one thread
         const int pblk = it.unit % n_pblk;
         tma::mbar_arrive_expect_tx(full_l, SLOT_BYTES);
-        tma::load_3d(L, &map_ld, full_l, 2 * PW * pblk, 0, it.tile);
-        tma::load_3d(L + SLOT_BYTES / 2, &map_ld, full_l, 2 * PW * pblk, 256, it.tile);
+#pragma unroll
+        for (int b = 0; b < C::NBOX; ++b) tma::load_3d(L + (size_t)b * 256 * 128, &map_ld, full_l, 2 * PW * pblk, 256 * b, it.tile);
     };
     Item it{(int)blockIdx.x, 0};
     it.tile = first_tile(it.unit);
     if (tid == 0 && it.unit < n_units) issue_load(it);
 
-    // this lane's 16 elements sit 32 rows = 4096 bytes apart in a swizzled buffer
+    // this lane's EPT elements sit 32 rows = 4096 bytes apart in a swizzled buffer
     const unsigned lane_off = zw_swz(t, w);
     int cur_unit = -1;
-    float2 kreg[16];
+    float2 kreg[EPT];
     unsigned seq = 0;
 #pragma unroll 1
     for (; it.unit < n_units; advance(it), ++seq) {
@@ -147,14 +179,14 @@ __global__ void __launch_bounds__(zw::THREADS, 1)
             cur_unit = it.unit;
             const float2* __restrict__ kp = kspec_t + ((size_t)(it.unit % n_pblk) * PW + w) * BZ + t;
 #pragma unroll
-            for (int m = 0; m < 16; ++m) kreg[m] = __ldg(kp + 32 * m);
+            for (int m = 0; m < EPT; ++m) kreg[m] = __ldg(kp + 32 * m);
         }
         tma::mbar_wait(full_l, seq & 1u);
-        float2 v[16];
+        float2 v[EPT];
 #pragma unroll
-        for (int m = 0; m < 16; ++m) v[m] = *reinterpret_cast<const float2*>(L + lane_off + 4096u * m);
+        for (int m = 0; m < EPT; ++m) v[m] = *reinterpret_cast<const float2*>(L + lane_off + 4096u * m);
         // forward transform; its first butterflies consume every element, so the landing buffer is released right behind them
-        dft16<false>(v);
+        dftR<EPT, false>(v);
         __syncwarp();
         if (t == 0) {
             __threadfence_block();
@@ -168,15 +200,15 @@ __global__ void __launch_bounds__(zw::THREADS, 1)
                 }
             }
         }
-        warp_fft512_tail<false>(v, t, xw, tw2, tw3);
+        warp_fft_tail<BZ, false>(v, t, xw, tw2, tw3);
 #pragma unroll
-        for (int m = 0; m < 16; ++m) v[m] = cmul(v[m], kreg[m]);
-        dft16<true>(v);
-        warp_fft512_tail<true>(v, t, xw, tw2, tw3);
+        for (int m = 0; m < EPT; ++m) v[m] = cmul(v[m], kreg[m]);
+        dftR<EPT, true>(v);
+        warp_fft_tail<BZ, true>(v, t, xw, tw2, tw3);
         // results -> staging buffer (free once the previous item's store has read it), swizzled box layout
         tma::mbar_wait(st_free, (seq & 1u) ^ 1u);
 #pragma unroll
-        for (int m = 0; m < 16; ++m) *reinterpret_cast<float2*>(ST + lane_off + 4096u * m) = v[m];
+        for (int m = 0; m < EPT; ++m) *reinterpret_cast<float2*>(ST + lane_off + 4096u * m) = v[m];
         tma::fence_proxy_async();
         __syncwarp();
         if (t == 0) {
@@ -185,8 +217,8 @@ __global__ void __launch_bounds__(zw::THREADS, 1)
                 *cnt_st = 0;
                 const int pblk = it.unit % n_pblk;
                 tma::fence_proxy_async();
-                tma::store_3d(&map_st, ST, 2 * PW * pblk, 0, it.tile);
-                tma::store_3d(&map_st, ST + SLOT_BYTES / 2, 2 * PW * pblk, 256, it.tile);
+#pragma unroll
+                for (int b = 0; b < C::NBOX; ++b) tma::store_3d(&map_st, ST + (size_t)b * 256 * 128, 2 * PW * pblk, 256 * b, it.tile);
                 tma::store_commit();
                 tma::store_wait_read();
                 tma::mbar_arrive(st_free);
@@ -211,10 +243,12 @@ __global__ void transpose_spectrum_kernel(const float2* __restrict__ in, float2*
     }
 }
 
-bool z_warp_supported(int bz) { return bz == zw::BZ; }
+bool z_warp_supported(int bz) { return bz == 512 || bz == 256; }
 
 cudaError_t configure_z_warp_kernels() {
-    return cudaFuncSetAttribute(z_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)zw::SMEM);
+    cudaError_t e = cudaFuncSetAttribute(z_warp_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ZW<512>::SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(z_warp_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ZW<256>::SMEM);
+    return e;
 }
 
 cudaError_t launch_transpose_spectrum(const float2* spec, float2* spec_t, int pe, int bz, cudaStream_t st) {
@@ -235,7 +269,7 @@ cudaError_t launch_z_pass_warp(int bx, int by, int bz, float2* scratch, const fl
     if (n_tiles <= 0) return cudaSuccess;
     if (!z_warp_supported(bz) || !kspec_t) return cudaErrorNotSupported;
     const unsigned long long pe = plane_elems(bx, by);
-    if (pe % zw::PW != 0) return cudaErrorNotSupported;
+    if (pe % 16 != 0) return cudaErrorNotSupported;
     const int zext = std::min(bz, zlo + max_nz);
     CUtensorMap ld, stm;
     const unsigned long long strides[2] = {pe * 8ull, pe * 8ull * (unsigned long long)bz};
@@ -245,10 +279,13 @@ cudaError_t launch_z_pass_warp(int bx, int by, int bz, float2* scratch, const fl
     if (!encode_tensor_map_f32_swizzle128(&ld, scratch, 3, dims_ld, strides, box) ||
         !encode_tensor_map_f32_swizzle128(&stm, scratch, 3, dims_st, strides, box))
         return cudaErrorNotSupported;
-    const int n_pblk = (int)(pe / zw::PW);
-    const int n_chunks = (n_tiles + zw::TC - 1) / zw::TC;
-    const int grid = std::max(1, std::min(num_sms, n_pblk * n_chunks));
-    z_warp_kernel<<<grid, zw::THREADS, zw::SMEM, st>>>(ld, stm, kspec_t, n_tiles, n_pblk, n_chunks, to_dev(tw));
+    const int n_pblk = (int)(pe / 16);
+    const int cap = num_sms * (bz == 512 ? ZW<512>::MIN_CTAS : ZW<256>::MIN_CTAS);
+    const int tc = choose_tiles_per_unit(n_tiles, n_pblk, cap);
+    const int n_chunks = (n_tiles + tc - 1) / tc;
+    const int grid = std::max(1, std::min(cap, n_pblk * n_chunks));
+    if (bz == 512) z_warp_kernel<512><<<grid, ZW<512>::THREADS, ZW<512>::SMEM, st>>>(ld, stm, kspec_t, n_tiles, n_pblk, n_chunks, tc, to_dev(tw));
+    else z_warp_kernel<256><<<grid, ZW<256>::THREADS, ZW<256>::SMEM, st>>>(ld, stm, kspec_t, n_tiles, n_pblk, n_chunks, tc, to_dev(tw));
     return cudaGetLastError();
 }
 

@@ -55,6 +55,7 @@ def _kernel(shape, seed):
     ((64, 64, 64), (15, 15, 15)),
     ((70, 130, 150), (15, 11, 9)),   # several windows per axis, mixed window sizes
     ((96, 200, 260), (31, 31, 31)),
+    ((200, 70, 150), (31, 9, 15)),   # z = one 256-point window (the warp-local z pass's second size)
     ((300, 36, 40), (31, 5, 7)),     # z needs the 512-point window
     ((530, 20, 24), (15, 3, 3)),     # z = 512-point window + a short one
     ((80, 150, 170), (63, 63, 63)),  # transformed PSFs grow with the view's affine (ExtractPSF.java:331-345)
@@ -738,13 +739,14 @@ def test_multi_device_handle_on_real_devices(m, o, lib):
 
 
 # ---- the TMA kernel generations (off by default: measured slower) stay correct ---------------------
-@pytest.mark.parametrize("switch,value", [("z_tma", 1), ("inv_ring", 1), ("inv_ring", 0), ("z_warp", 0)])
+@pytest.mark.parametrize("switch,value", [("z_tma", 1), ("inv_ring", 1), ("inv_ring", 0), ("z_warp", 0), ("z_warp", 2)])
 def test_tma_kernels_match_oracle_and_default_kernels(m, o, lib, switch, value):
     """Every kernel generation against the default one and the oracle: the z pass with bulk-tensor loads / stores, the inverse
     xy ring kernel fed by bulk-tensor loads, and (z_warp = 0) the register-loading z pass against the default warp-local z
     pass.  The arithmetic is the same, only the data movement differs."""
     from spim_registration_b200 import synthetic
-    f, k = _rand((300, 150, 260), 31), _kernel((31, 31, 31), 32)       # 512-point z window, two 128-windows in x and y
+    zdim = 200 if (switch, value) == ("z_warp", 2) else 300            # z_warp = 2: the 256-point z window
+    f, k = _rand((zdim, 150, 260), 31), _kernel((31, 31, 31), 32)      # 512-point z window, two 128-windows in x and y
     ref = o.convolve_extended(f, k, "mirror")
     base = m.convolve(f, k, "mirror")
     shape, V = (140, 112, 120), 2
