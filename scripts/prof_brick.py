@@ -28,7 +28,8 @@ def main():
     Z, Y, X = cfg["shape"]
     dim = (X, Y, Z)
     psfs, k1, k2 = bench.prepare_kernels(cfg)
-    grid = brick_grid(world, dim, [cfg["k"]] * 3) if os.environ.get("MVD_GRID", "cost") == "cost" else brick_grid(world, dim)
+    g = os.environ.get("MVD_GRID", "cost")   # "cost" (default rule), "longest" (round 1's rule) or an explicit "gx,gy,gz"
+    grid = brick_grid(world, dim, [cfg["k"]] * 3) if g == "cost" else (brick_grid(world, dim) if g == "longest" else tuple(int(x) for x in g.split(",")))
     off, size, _ = brick_of(rank, grid, dim)
     imgs, weights = bench.gen_dataset_device(cfg, lib, psfs, (off[::-1], size[::-1]))
     dec = ShardedDeconvolution.__new__(ShardedDeconvolution)
