@@ -38,7 +38,7 @@ bool z_warp_supported(int bz);
 cudaError_t configure_z_warp_kernels();
 cudaError_t launch_transpose_spectrum(const float2* spec, float2* spec_t, int pe, int bz, cudaStream_t st);
 cudaError_t launch_z_pass_warp(int bx, int by, int bz, float2* scratch, const float2* kspec_t, int n_tiles, int zlo, int max_nz, int num_sms,
-                               const TwiddleTables& tw, cudaStream_t st);
+                               const TwiddleTables& tw, cudaStream_t st, int generation = 1);
 // inverse xy pass for 128 x 128 windows fed by bulk copies into a shared-memory ring (inv_ring_kernels.cu)
 bool inv_ring_supported(int bx, int by);
 cudaError_t configure_inv_ring_kernels();

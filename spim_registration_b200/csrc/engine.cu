@@ -17,7 +17,13 @@ static int env_flag(const char* name, int dflt) {
 }
 std::atomic<int> g_use_z_tma{env_flag("MVD_Z_TMA", 0)};
 std::atomic<int> g_use_inv_ring{env_flag("MVD_INV_RING", 2)};
+// 0: register-loading z pass; 1: warp-local lines for 512-point windows (z_warp_kernel); 2: also for 256-point windows;
+// 3: lines on part of a warp, two passes (z_part_kernel) for 512-point windows; 4: also for 256-point windows
 std::atomic<int> g_use_z_warp{env_flag("MVD_Z_WARP", 1)};
+static bool z_warp_covers(int bz) {
+    const int g = g_use_z_warp.load();
+    return g != 0 && (bz == 512 || g == 2 || g == 4);
+}
 
 void cuda_check(cudaError_t e, const char* what) {
     if (e != cudaSuccess) throw CudaError(std::string(what) + ": " + cudaGetErrorString(e));
@@ -317,8 +323,8 @@ std::unique_ptr<KernelSpectra> build_spectra(Device& dev, const ConvPlan& plan, 
         MVD_CUDA(launch_z_pass(bx, by, bz, 0, d_spec, nullptr, d_tile + ci, 1, scale, dev.twiddles(), st));
         g_kernel_launches += 3;
         float2* d_spec_t = nullptr;
-        // 512-point classes by default; 256-point ones only with z_warp = 2 (measured slower than the register-loading kernel there)
-        if (z_warp_supported(bz) && (bz == 512 || g_use_z_warp.load() >= 2) && plane_elems(bx, by) % 16 == 0) {
+        // 512-point classes by default; 256-point ones only with z_warp = 2 / 4 (see z_warp_covers)
+        if (z_warp_supported(bz) && z_warp_covers(bz) && plane_elems(bx, by) % 16 == 0) {
             MVD_CUDA(cudaMalloc(&d_spec_t, tile_scratch_elems(bx, by, bz) * sizeof(float2)));
             spec->per_class_t.push_back(d_spec_t);
             MVD_CUDA(launch_transpose_spectrum(d_spec, d_spec_t, (int)plane_elems(bx, by), bz, st));
@@ -460,8 +466,9 @@ void run_convolution(Device& dev, const ConvPlan& plan, const KernelSpectra& spe
             if (prof) { prof->end(ls); prof->begin(1, cnt * pe * bz * 8.0 + pe * bz * 8.0 + nz_sum * pe * 8.0, ls); }
             const int zlo = c.tiles[s].e[2] - c.tiles[s].o[2];  // the same for every tile of a plan
             bool z_done = false;
-            if (g_use_z_warp.load() && z_warp_supported(bz) && (bz == 512 || g_use_z_warp.load() >= 2) && spec.per_class_t[ci]) {
-                const cudaError_t e = launch_z_pass_warp(bx, by, bz, buf, spec.per_class_t[ci], cnt, zlo, c.max_nz, dev.sm_count(), dev.twiddles(), ls);
+            if (g_use_z_warp.load() && z_warp_supported(bz) && z_warp_covers(bz) && spec.per_class_t[ci]) {
+                const cudaError_t e = launch_z_pass_warp(bx, by, bz, buf, spec.per_class_t[ci], cnt, zlo, c.max_nz, dev.sm_count(), dev.twiddles(), ls,
+                                                         g_use_z_warp.load() >= 3 ? 2 : 1);
                 if (e != cudaErrorNotSupported) {
                     MVD_CUDA(e);
                     z_done = true;

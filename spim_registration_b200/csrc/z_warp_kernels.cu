@@ -228,6 +228,175 @@ __global__ void __launch_bounds__(ZW<BZ>::THREADS, ZW<BZ>::MIN_CTAS)
     if (t == 0) tma::store_wait_all();
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Second generation: a line lives in a PART of a warp (BZ / 32 lanes, 32 elements per lane), so that the line FFT has two
+// passes (32 x 16 for 512 points, 32 x 8 for 256) and ONE exchange instead of three passes and two exchanges, and a warp
+// holds 32 / (BZ / 32) neighbouring plane positions: its accesses to the swizzled landing / staging buffers then cover all
+// 32 banks (2 shared-memory wavefronts per 256 bytes, the minimum, instead of 4).  Per line and item that is 192 wavefronts
+// of the compute side instead of 384 -- the first generation is bound by the shared-memory pipe (l1tex 74 % busy, ncu).
+// Half as many threads per item (16 positions = 8 warps for 512 points), so there is room for 255 registers per thread: the
+// 32 spectrum values per lane and all inter-pass twiddles stay in registers.
+template <int BZ> struct ZH {
+    static constexpr int EPT = 32;
+    static constexpr int LPL = BZ / EPT;               // lanes per line (16 / 8)
+    static constexpr int LPW = 32 / LPL;               // lines (plane positions) per warp (2 / 4)
+    static constexpr int R1 = LPL;                     // radix of the second pass
+    static constexpr int NB = EPT / R1;                // butterflies per lane in the second pass (2 / 4)
+    static constexpr int PW = 16, NWARP = PW / LPW, THREADS = NWARP * 32;
+    static constexpr int XP = BZ + BZ / 32;            // padded line: one pad element per 32
+    static constexpr unsigned SLOT_BYTES = PW * BZ * sizeof(float2);
+    static constexpr int NBOX = BZ / 256;
+    static constexpr size_t OFF_L = 0, OFF_ST = SLOT_BYTES, OFF_X = 2 * (size_t)SLOT_BYTES;
+    static constexpr size_t OFF_BAR = OFF_X + (size_t)PW * XP * sizeof(float2);
+    static constexpr size_t SMEM = OFF_BAR + 64;
+    static constexpr int MIN_CTAS = BZ >= 512 ? 1 : 2;  // 194 KB / 97 KB of shared memory
+    static_assert(BZ == 512 || BZ == 256, "part-warp lines: 512 or 256 points");
+};
+
+// One line FFT of BZ points on LPL lanes: lane l of the line holds x[l + LPL m] in v[m] on entry and X[l + LPL m] on return
+// (the passes of line_fft<BZ, 32, INV>, fft_device.cuh: radix 32 with NS = 1, then radix LPL with NS = 32 and twiddles
+// w^(j r), j = l + LPL b).  xs = the warp's exchange buffer, element i of line h at slot LPW * (i + i / 32) + h: for a fixed
+// register index the lanes of a warp then cover all banks with 8-byte accesses, on the way in and on the way out.
+template <int BZ, bool INV>
+__device__ __forceinline__ void part_warp_fft(float2 (&v)[32], int l, int h, float2* __restrict__ xs, const float2 (&tw)[ZH<BZ>::NB][ZH<BZ>::R1 - 1]) {
+    constexpr int LPL = ZH<BZ>::LPL, LPW = ZH<BZ>::LPW, R1 = ZH<BZ>::R1, NB = ZH<BZ>::NB;
+    dftR<32, INV>(v);
+    {   // output r of lane l -> element 32 l + r, slot LPW (33 l + r) + h
+        float2* p = xs + LPW * 33 * l + h;
+#pragma unroll
+        for (int r = 0; r < 32; ++r) p[LPW * r] = v[r];
+    }
+    __syncwarp();
+    {   // element l + LPL m: slot LPW (l + LPL m + (LPL m) / 32) + h   (l < LPL <= 32 / 2)
+        const float2* g = xs + LPW * l + h;
+#pragma unroll
+        for (int m = 0; m < 32; ++m) v[m] = g[LPW * (LPL * m + (LPL * m) / 32)];
+    }
+    __syncwarp();  // the buffer may be overwritten by the next transform
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+        float2 x[R1];
+#pragma unroll
+        for (int r = 0; r < R1; ++r) x[r] = v[b + r * NB];
+#pragma unroll
+        for (int r = 1; r < R1; ++r) x[r] = ctw<INV>(x[r], tw[b][r - 1]);
+        dftR<R1, INV>(x);
+#pragma unroll
+        for (int r = 0; r < R1; ++r) v[b + r * NB] = x[r];
+    }
+}
+
+template <int BZ>
+__global__ void __launch_bounds__(ZH<BZ>::THREADS, ZH<BZ>::MIN_CTAS)
+    z_part_kernel(const __grid_constant__ CUtensorMap map_ld, const __grid_constant__ CUtensorMap map_st, const float2* __restrict__ kspec_t,
+                  int n_tiles, int n_pblk, int n_chunks, int TC, Twiddles tw_tab) {
+    using C = ZH<BZ>;
+    constexpr int LPL = C::LPL, LPW = C::LPW, PW = C::PW, NWARP = C::NWARP, XP = C::XP, R1 = C::R1, NB = C::NB;
+    constexpr unsigned SLOT_BYTES = C::SLOT_BYTES;
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* L = smem_raw + C::OFF_L;
+    unsigned char* ST = smem_raw + C::OFF_ST;
+    uint64_t* full_l = reinterpret_cast<uint64_t*>(smem_raw + C::OFF_BAR);
+    uint64_t* st_free = full_l + 1;
+    int* cnt_l = reinterpret_cast<int*>(full_l + 2);
+    int* cnt_st = cnt_l + 1;
+
+    const int tid = threadIdx.x;
+    const int w = tid >> 5, t = tid & 31;
+    const int h = t / LPL, l = t % LPL;  // line inside the warp, lane inside the line
+    const int p = LPW * w + h;           // plane position inside the block of 16
+    float2* xs = reinterpret_cast<float2*>(smem_raw + C::OFF_X) + (size_t)w * LPW * XP;
+    float2 tw[NB][R1 - 1];
+#pragma unroll
+    for (int b = 0; b < NB; ++b)
+#pragma unroll
+        for (int r = 1; r < R1; ++r) tw[b][r - 1] = __ldg(&tw_tab.t[ilog2<BZ>()][(l + LPL * b) * r]);
+    if (tid == 0) {
+        tma::mbar_init(full_l, 1);
+        tma::mbar_init(st_free, 1);
+        *cnt_l = 0;
+        *cnt_st = 0;
+        tma::fence_barrier_init();
+    }
+    __syncthreads();
+
+    const int n_units = n_pblk * n_chunks;
+    struct Item { int unit, tile; };
+    auto first_tile = [&](int unit) { return (unit / n_pblk) * TC; };
+    auto last_tile = [&](int unit) { return min(n_tiles, (unit / n_pblk + 1) * TC); };
+    auto advance = [&](Item& it) {
+        if (++it.tile >= last_tile(it.unit)) {
+            it.unit += gridDim.x;
+            it.tile = first_tile(it.unit);
+        }
+    };
+    auto issue_load = [&](const Item& it) {  // one thread
+        const int pblk = it.unit % n_pblk;
+        tma::mbar_arrive_expect_tx(full_l, SLOT_BYTES);
+#pragma unroll
+        for (int b = 0; b < C::NBOX; ++b) tma::load_3d(L + (size_t)b * 256 * 128, &map_ld, full_l, 2 * PW * pblk, 256 * b, it.tile);
+    };
+    Item it{(int)blockIdx.x, 0};
+    it.tile = first_tile(it.unit);
+    if (tid == 0 && it.unit < n_units) issue_load(it);
+
+    // this lane's 32 elements (z = l + LPL m) sit LPL rows = LPL * 128 bytes apart in a swizzled buffer; z & 7 = l & 7
+    const unsigned lane_off = zw_swz(l, p);
+    constexpr unsigned MSTEP = LPL * 128u;
+    int cur_unit = -1;
+    float2 kreg[32];
+    unsigned seq = 0;
+#pragma unroll 1
+    for (; it.unit < n_units; advance(it), ++seq) {
+        if (it.unit != cur_unit) {  // the line's kernel-spectrum values (1/n folded in) from the transposed copy: LPL * 8 bytes per line in a row
+            cur_unit = it.unit;
+            const float2* __restrict__ kp = kspec_t + ((size_t)(it.unit % n_pblk) * PW + p) * BZ + l;
+#pragma unroll
+            for (int m = 0; m < 32; ++m) kreg[m] = __ldg(kp + LPL * m);
+        }
+        tma::mbar_wait(full_l, seq & 1u);
+        float2 v[32];
+#pragma unroll
+        for (int m = 0; m < 32; ++m) v[m] = *reinterpret_cast<const float2*>(L + lane_off + MSTEP * m);
+        __syncwarp();
+        if (t == 0) {
+            __threadfence_block();
+            if (atomicAdd(cnt_l, 1) == NWARP - 1) {  // the last warp to take its lines refills the buffer with the next item
+                *cnt_l = 0;
+                Item nx = it;
+                advance(nx);
+                if (nx.unit < n_units) {
+                    tma::fence_proxy_async();
+                    issue_load(nx);
+                }
+            }
+        }
+        part_warp_fft<BZ, false>(v, l, h, xs, tw);
+#pragma unroll
+        for (int m = 0; m < 32; ++m) v[m] = cmul(v[m], kreg[m]);
+        part_warp_fft<BZ, true>(v, l, h, xs, tw);
+        tma::mbar_wait(st_free, (seq & 1u) ^ 1u);
+#pragma unroll
+        for (int m = 0; m < 32; ++m) *reinterpret_cast<float2*>(ST + lane_off + MSTEP * m) = v[m];
+        tma::fence_proxy_async();
+        __syncwarp();
+        if (t == 0) {
+            __threadfence_block();
+            if (atomicAdd(cnt_st, 1) == NWARP - 1) {  // the last warp to deliver its lines sends the item off
+                *cnt_st = 0;
+                const int pblk = it.unit % n_pblk;
+                tma::fence_proxy_async();
+#pragma unroll
+                for (int b = 0; b < C::NBOX; ++b) tma::store_3d(&map_st, ST + (size_t)b * 256 * 128, 2 * PW * pblk, 256 * b, it.tile);
+                tma::store_commit();
+                tma::store_wait_read();
+                tma::mbar_arrive(st_free);
+            }
+        }
+    }
+    if (t == 0) tma::store_wait_all();
+}
+
 // [bz][pe] -> [pe][bz]
 __global__ void transpose_spectrum_kernel(const float2* __restrict__ in, float2* __restrict__ out, int pe, int bz) {
     __shared__ float2 tile[32][33];
@@ -248,6 +417,8 @@ bool z_warp_supported(int bz) { return bz == 512 || bz == 256; }
 cudaError_t configure_z_warp_kernels() {
     cudaError_t e = cudaFuncSetAttribute(z_warp_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ZW<512>::SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(z_warp_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ZW<256>::SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(z_part_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ZH<512>::SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(z_part_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ZH<256>::SMEM);
     return e;
 }
 
@@ -265,7 +436,7 @@ static inline Twiddles to_dev(const TwiddleTables& t) {
 
 // cudaErrorNotSupported: the caller falls back to the register-loading z pass
 cudaError_t launch_z_pass_warp(int bx, int by, int bz, float2* scratch, const float2* kspec_t, int n_tiles, int zlo, int max_nz, int num_sms,
-                               const TwiddleTables& tw, cudaStream_t st) {
+                               const TwiddleTables& tw, cudaStream_t st, int generation) {
     if (n_tiles <= 0) return cudaSuccess;
     if (!z_warp_supported(bz) || !kspec_t) return cudaErrorNotSupported;
     const unsigned long long pe = plane_elems(bx, by);
@@ -280,11 +451,14 @@ cudaError_t launch_z_pass_warp(int bx, int by, int bz, float2* scratch, const fl
         !encode_tensor_map_f32_swizzle128(&stm, scratch, 3, dims_st, strides, box))
         return cudaErrorNotSupported;
     const int n_pblk = (int)(pe / 16);
-    const int cap = num_sms * (bz == 512 ? ZW<512>::MIN_CTAS : ZW<256>::MIN_CTAS);
+    const int cap = num_sms * (bz == 512 ? 1 : 2);  // MIN_CTAS of both generations
     const int tc = choose_tiles_per_unit(n_tiles, n_pblk, cap);
     const int n_chunks = (n_tiles + tc - 1) / tc;
     const int grid = std::max(1, std::min(cap, n_pblk * n_chunks));
-    if (bz == 512) z_warp_kernel<512><<<grid, ZW<512>::THREADS, ZW<512>::SMEM, st>>>(ld, stm, kspec_t, n_tiles, n_pblk, n_chunks, tc, to_dev(tw));
+    if (generation >= 2) {
+        if (bz == 512) z_part_kernel<512><<<grid, ZH<512>::THREADS, ZH<512>::SMEM, st>>>(ld, stm, kspec_t, n_tiles, n_pblk, n_chunks, tc, to_dev(tw));
+        else z_part_kernel<256><<<grid, ZH<256>::THREADS, ZH<256>::SMEM, st>>>(ld, stm, kspec_t, n_tiles, n_pblk, n_chunks, tc, to_dev(tw));
+    } else if (bz == 512) z_warp_kernel<512><<<grid, ZW<512>::THREADS, ZW<512>::SMEM, st>>>(ld, stm, kspec_t, n_tiles, n_pblk, n_chunks, tc, to_dev(tw));
     else z_warp_kernel<256><<<grid, ZW<256>::THREADS, ZW<256>::SMEM, st>>>(ld, stm, kspec_t, n_tiles, n_pblk, n_chunks, tc, to_dev(tw));
     return cudaGetLastError();
 }
