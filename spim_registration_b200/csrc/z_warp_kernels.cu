@@ -231,11 +231,17 @@ __global__ void __launch_bounds__(ZW<BZ>::THREADS, ZW<BZ>::MIN_CTAS)
 // ---------------------------------------------------------------------------------------------------------------------
 // Second generation: a line lives in a PART of a warp (BZ / 32 lanes, 32 elements per lane), so that the line FFT has two
 // passes (32 x 16 for 512 points, 32 x 8 for 256) and ONE exchange instead of three passes and two exchanges, and a warp
-// holds 32 / (BZ / 32) neighbouring plane positions: its accesses to the swizzled landing / staging buffers then cover all
-// 32 banks (2 shared-memory wavefronts per 256 bytes, the minimum, instead of 4).  Per line and item that is 192 wavefronts
-// of the compute side instead of 384 -- the first generation is bound by the shared-memory pipe (l1tex 74 % busy, ncu).
-// Half as many threads per item (16 positions = 8 warps for 512 points), so there is room for 255 registers per thread: the
-// 32 spectrum values per lane and all inter-pass twiddles stay in registers.
+// holds 32 / (BZ / 32) neighbouring plane positions.  The first generation is bound by the shared-memory pipe (l1tex 74 %
+// busy in ncu: 4 wavefronts per 256 bytes at the swizzled buffers, two exchanges per transform); here
+//   * every half-warp (the unit of an 8-byte shared-memory access) holds 8 different z residues of TWO neighbouring
+//     positions, i.e. both halves of 8 different 16-byte chunks: 16 bank pairs, no conflict, at the landing rows, at the
+//     result rows and -- through the row permutation xrow() -- at the exchange;
+//   * an item (16 positions x BZ planes) lands in one of THREE buffers and stays there: a warp takes its lines out of its own
+//     16-byte column of the buffer, exchanges inside that column, leaves the results in it, and the last warp to finish
+//     sends the buffer off (bulk tensor store) and refills it with the item three ahead -- two loads are in flight per
+//     CTA while one item is computed, and warps never wait for each other except through the refill;
+//   * half as many threads per item (8 warps for 512 points), so there is room for 255 registers per thread: the 32 spectrum
+//     values per lane and all inter-pass twiddles stay in registers.
 template <int BZ> struct ZH {
     static constexpr int EPT = 32;
     static constexpr int LPL = BZ / EPT;               // lanes per line (16 / 8)
@@ -243,36 +249,40 @@ template <int BZ> struct ZH {
     static constexpr int R1 = LPL;                     // radix of the second pass
     static constexpr int NB = EPT / R1;                // butterflies per lane in the second pass (2 / 4)
     static constexpr int PW = 16, NWARP = PW / LPW, THREADS = NWARP * 32;
-    static constexpr int XP = BZ + BZ / 32;            // padded line: one pad element per 32
-    static constexpr unsigned SLOT_BYTES = PW * BZ * sizeof(float2);
+    static constexpr int NBUF = 3;
+    static constexpr unsigned SLOT_BYTES = PW * BZ * sizeof(float2);  // 65536 / 32768
     static constexpr int NBOX = BZ / 256;
-    static constexpr size_t OFF_L = 0, OFF_ST = SLOT_BYTES, OFF_X = 2 * (size_t)SLOT_BYTES;
-    static constexpr size_t OFF_BAR = OFF_X + (size_t)PW * XP * sizeof(float2);
+    static constexpr size_t OFF_BAR = (size_t)NBUF * SLOT_BYTES;
     static constexpr size_t SMEM = OFF_BAR + 64;
-    static constexpr int MIN_CTAS = BZ >= 512 ? 1 : 2;  // 194 KB / 97 KB of shared memory
+    static constexpr int MIN_CTAS = BZ >= 512 ? 1 : 2;  // 192 KB / 96 KB of shared memory
     static_assert(BZ == 512 || BZ == 256, "part-warp lines: 512 or 256 points");
 };
 
+// Exchange row of line element i: the low three bits are XORed with bits 5..7, so that the 8 lanes of a half-warp that
+// belong to one line touch 8 different rows modulo 8 (= 8 different swizzled chunks) when they write 32 l + r (fixed r) and
+// when they read l + LPL m (fixed m).
+__host__ __device__ constexpr int xrow(int i) { return i ^ ((i >> 5) & 7); }
+
 // One line FFT of BZ points on LPL lanes: lane l of the line holds x[l + LPL m] in v[m] on entry and X[l + LPL m] on return
 // (the passes of line_fft<BZ, 32, INV>, fft_device.cuh: radix 32 with NS = 1, then radix LPL with NS = 32 and twiddles
-// w^(j r), j = l + LPL b).  xs = the warp's exchange buffer, element i of line h at slot LPW * (i + i / 32) + h: for a fixed
-// register index the lanes of a warp then cover all banks with 8-byte accesses, on the way in and on the way out.
+// w^(j r), j = l + LPL b).  buf + xo[c]: the byte address, in the item's swizzled buffer, of row (c ^ l & 7) of this
+// lane's column; put_base / get_base: the lane's part of the row offset (32 l rows / l & 8 rows).
 template <int BZ, bool INV>
-__device__ __forceinline__ void part_warp_fft(float2 (&v)[32], int l, int h, float2* __restrict__ xs, const float2 (&tw)[ZH<BZ>::NB][ZH<BZ>::R1 - 1]) {
-    constexpr int LPL = ZH<BZ>::LPL, LPW = ZH<BZ>::LPW, R1 = ZH<BZ>::R1, NB = ZH<BZ>::NB;
+__device__ __forceinline__ void part_warp_fft(float2 (&v)[32], unsigned char* __restrict__ buf, const unsigned (&xo)[8], unsigned put_base,
+                                              unsigned get_base, const float2 (&tw)[ZH<BZ>::NB][ZH<BZ>::R1 - 1]) {
+    constexpr int LPL = ZH<BZ>::LPL, R1 = ZH<BZ>::R1, NB = ZH<BZ>::NB;
     dftR<32, INV>(v);
-    {   // output r of lane l -> element 32 l + r, slot LPW (33 l + r) + h
-        float2* p = xs + LPW * 33 * l + h;
+    // output r of lane l -> element 32 l + r -> row 32 l + (r ^ (l & 7)) = 32 l + 8 (r >> 3) + ((r & 7) ^ (l & 7))
 #pragma unroll
-        for (int r = 0; r < 32; ++r) p[LPW * r] = v[r];
-    }
+    for (int r = 0; r < 32; ++r) *reinterpret_cast<float2*>(buf + put_base + xo[r & 7] + 1024u * (r >> 3)) = v[r];
     __syncwarp();
-    {   // element l + LPL m: slot LPW (l + LPL m + (LPL m) / 32) + h   (l < LPL <= 32 / 2)
-        const float2* g = xs + LPW * l + h;
+    // element i = l + LPL m: i >> 5 = (LPL m) >> 5 =: c (l < LPL <= 16 never carries), row = (i & ~7) + ((l & 7) ^ (c & 7))
 #pragma unroll
-        for (int m = 0; m < 32; ++m) v[m] = g[LPW * (LPL * m + (LPL * m) / 32)];
+    for (int m = 0; m < 32; ++m) {
+        const int c = (LPL * m) >> 5;
+        v[m] = *reinterpret_cast<const float2*>(buf + get_base + xo[c & 7] + 128u * ((LPL * m) & ~7));
     }
-    __syncwarp();  // the buffer may be overwritten by the next transform
+    __syncwarp();  // the column may be overwritten by the next exchange or by the results
 #pragma unroll
     for (int b = 0; b < NB; ++b) {
         float2 x[R1];
@@ -291,31 +301,29 @@ __global__ void __launch_bounds__(ZH<BZ>::THREADS, ZH<BZ>::MIN_CTAS)
     z_part_kernel(const __grid_constant__ CUtensorMap map_ld, const __grid_constant__ CUtensorMap map_st, const float2* __restrict__ kspec_t,
                   int n_tiles, int n_pblk, int n_chunks, int TC, Twiddles tw_tab) {
     using C = ZH<BZ>;
-    constexpr int LPL = C::LPL, LPW = C::LPW, PW = C::PW, NWARP = C::NWARP, XP = C::XP, R1 = C::R1, NB = C::NB;
+    constexpr int LPL = C::LPL, LPW = C::LPW, PW = C::PW, NWARP = C::NWARP, R1 = C::R1, NB = C::NB, NBUF = C::NBUF;
     constexpr unsigned SLOT_BYTES = C::SLOT_BYTES;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    unsigned char* L = smem_raw + C::OFF_L;
-    unsigned char* ST = smem_raw + C::OFF_ST;
-    uint64_t* full_l = reinterpret_cast<uint64_t*>(smem_raw + C::OFF_BAR);
-    uint64_t* st_free = full_l + 1;
-    int* cnt_l = reinterpret_cast<int*>(full_l + 2);
-    int* cnt_st = cnt_l + 1;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + C::OFF_BAR);  // [NBUF]
+    int* cnt = reinterpret_cast<int*>(full + NBUF);                       // [NBUF]
 
     const int tid = threadIdx.x;
     const int w = tid >> 5, t = tid & 31;
-    const int h = t / LPL, l = t % LPL;  // line inside the warp, lane inside the line
+    // lane -> (line h inside the warp, lane l inside the line); a half-warp holds l & 7 = 0..7 of two lines
+    const int h = LPL == 16 ? (t >> 3) & 1 : t >> 3;
+    const int l = LPL == 16 ? (t & 7) | ((t >> 4) << 3) : t & 7;
     const int p = LPW * w + h;           // plane position inside the block of 16
-    float2* xs = reinterpret_cast<float2*>(smem_raw + C::OFF_X) + (size_t)w * LPW * XP;
     float2 tw[NB][R1 - 1];
 #pragma unroll
     for (int b = 0; b < NB; ++b)
 #pragma unroll
         for (int r = 1; r < R1; ++r) tw[b][r - 1] = __ldg(&tw_tab.t[ilog2<BZ>()][(l + LPL * b) * r]);
     if (tid == 0) {
-        tma::mbar_init(full_l, 1);
-        tma::mbar_init(st_free, 1);
-        *cnt_l = 0;
-        *cnt_st = 0;
+#pragma unroll
+        for (int b = 0; b < NBUF; ++b) {
+            tma::mbar_init(full + b, 1);
+            cnt[b] = 0;
+        }
         tma::fence_barrier_init();
     }
     __syncthreads();
@@ -330,67 +338,73 @@ __global__ void __launch_bounds__(ZH<BZ>::THREADS, ZH<BZ>::MIN_CTAS)
             it.tile = first_tile(it.unit);
         }
     };
-    auto issue_load = [&](const Item& it) {  // one thread
+    auto issue_load = [&](const Item& it, int b) {  // one thread
         const int pblk = it.unit % n_pblk;
-        tma::mbar_arrive_expect_tx(full_l, SLOT_BYTES);
+        unsigned char* dst = smem_raw + (size_t)b * SLOT_BYTES;
+        tma::mbar_arrive_expect_tx(full + b, SLOT_BYTES);
 #pragma unroll
-        for (int b = 0; b < C::NBOX; ++b) tma::load_3d(L + (size_t)b * 256 * 128, &map_ld, full_l, 2 * PW * pblk, 256 * b, it.tile);
+        for (int x = 0; x < C::NBOX; ++x) tma::load_3d(dst + (size_t)x * 256 * 128, &map_ld, full + b, 2 * PW * pblk, 256 * x, it.tile);
     };
     Item it{(int)blockIdx.x, 0};
     it.tile = first_tile(it.unit);
-    if (tid == 0 && it.unit < n_units) issue_load(it);
+    if (tid == 0) {
+        Item nx = it;
+        for (int b = 0; b < NBUF && nx.unit < n_units; ++b, advance(nx)) issue_load(nx, b);
+    }
 
-    // this lane's 32 elements (z = l + LPL m) sit LPL rows = LPL * 128 bytes apart in a swizzled buffer; z & 7 = l & 7
+    // rows of this lane's column: z = l + LPL m for the item's data, xrow() rows for the exchange; z & 7 = l & 7
+    const unsigned pc = (unsigned)p >> 1, hb = ((unsigned)p & 1u) * 8u, l7 = (unsigned)l & 7u;
     const unsigned lane_off = zw_swz(l, p);
     constexpr unsigned MSTEP = LPL * 128u;
+    unsigned xo[8];
+#pragma unroll
+    for (unsigned c = 0; c < 8; ++c) xo[c] = ((c ^ l7) << 7) + (((pc ^ l7 ^ c) & 7u) << 4) + hb;
+    const unsigned put_base = (unsigned)l * 4096u, get_base = ((unsigned)l & 8u) * 128u;
     int cur_unit = -1;
     float2 kreg[32];
     unsigned seq = 0;
+    int b = 0;
 #pragma unroll 1
-    for (; it.unit < n_units; advance(it), ++seq) {
-        if (it.unit != cur_unit) {  // the line's kernel-spectrum values (1/n folded in) from the transposed copy: LPL * 8 bytes per line in a row
+    for (; it.unit < n_units; advance(it), ++seq, b = b == NBUF - 1 ? 0 : b + 1) {
+        if (it.unit != cur_unit) {  // the line's kernel-spectrum values (1/n folded in) from the transposed copy
             cur_unit = it.unit;
             const float2* __restrict__ kp = kspec_t + ((size_t)(it.unit % n_pblk) * PW + p) * BZ + l;
 #pragma unroll
             for (int m = 0; m < 32; ++m) kreg[m] = __ldg(kp + LPL * m);
         }
-        tma::mbar_wait(full_l, seq & 1u);
+        unsigned char* buf = smem_raw + (size_t)b * SLOT_BYTES;
+        tma::mbar_wait(full + b, (seq / NBUF) & 1u);
         float2 v[32];
 #pragma unroll
-        for (int m = 0; m < 32; ++m) v[m] = *reinterpret_cast<const float2*>(L + lane_off + MSTEP * m);
-        __syncwarp();
-        if (t == 0) {
-            __threadfence_block();
-            if (atomicAdd(cnt_l, 1) == NWARP - 1) {  // the last warp to take its lines refills the buffer with the next item
-                *cnt_l = 0;
-                Item nx = it;
-                advance(nx);
-                if (nx.unit < n_units) {
-                    tma::fence_proxy_async();
-                    issue_load(nx);
-                }
-            }
-        }
-        part_warp_fft<BZ, false>(v, l, h, xs, tw);
+        for (int m = 0; m < 32; ++m) v[m] = *reinterpret_cast<const float2*>(buf + lane_off + MSTEP * m);
+        __syncwarp();  // every lane has its elements before the column becomes exchange space
+        part_warp_fft<BZ, false>(v, buf, xo, put_base, get_base, tw);
 #pragma unroll
         for (int m = 0; m < 32; ++m) v[m] = cmul(v[m], kreg[m]);
-        part_warp_fft<BZ, true>(v, l, h, xs, tw);
-        tma::mbar_wait(st_free, (seq & 1u) ^ 1u);
+        part_warp_fft<BZ, true>(v, buf, xo, put_base, get_base, tw);
 #pragma unroll
-        for (int m = 0; m < 32; ++m) *reinterpret_cast<float2*>(ST + lane_off + MSTEP * m) = v[m];
+        for (int m = 0; m < 32; ++m) *reinterpret_cast<float2*>(buf + lane_off + MSTEP * m) = v[m];
         tma::fence_proxy_async();
         __syncwarp();
         if (t == 0) {
             __threadfence_block();
-            if (atomicAdd(cnt_st, 1) == NWARP - 1) {  // the last warp to deliver its lines sends the item off
-                *cnt_st = 0;
+            int old;
+            asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(tma::smem_u32(cnt + b)) : "memory");
+            if (old == NWARP - 1) {  // the last warp to deliver its lines sends the item off and refills the buffer
+                cnt[b] = 0;
+                __threadfence_block();
                 const int pblk = it.unit % n_pblk;
                 tma::fence_proxy_async();
 #pragma unroll
-                for (int b = 0; b < C::NBOX; ++b) tma::store_3d(&map_st, ST + (size_t)b * 256 * 128, 2 * PW * pblk, 256 * b, it.tile);
+                for (int x = 0; x < C::NBOX; ++x) tma::store_3d(&map_st, buf + (size_t)x * 256 * 128, 2 * PW * pblk, 256 * x, it.tile);
                 tma::store_commit();
-                tma::store_wait_read();
-                tma::mbar_arrive(st_free);
+                Item nx = it;
+#pragma unroll
+                for (int a = 0; a < NBUF; ++a) advance(nx);
+                if (nx.unit < n_units) {
+                    tma::store_wait_read();
+                    issue_load(nx, b);
+                }
             }
         }
     }

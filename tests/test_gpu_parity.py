@@ -739,13 +739,14 @@ def test_multi_device_handle_on_real_devices(m, o, lib):
 
 
 # ---- the TMA kernel generations (off by default: measured slower) stay correct ---------------------
-@pytest.mark.parametrize("switch,value", [("z_tma", 1), ("inv_ring", 1), ("inv_ring", 0), ("z_warp", 0), ("z_warp", 2)])
+@pytest.mark.parametrize("switch,value", [("z_tma", 1), ("inv_ring", 1), ("inv_ring", 0), ("z_warp", 0), ("z_warp", 1), ("z_warp", 2),
+                                          ("z_warp", 3), ("z_warp", 4)])
 def test_tma_kernels_match_oracle_and_default_kernels(m, o, lib, switch, value):
     """Every kernel generation against the default one and the oracle: the z pass with bulk-tensor loads / stores, the inverse
     xy ring kernel fed by bulk-tensor loads, and (z_warp = 0) the register-loading z pass against the default warp-local z
     pass.  The arithmetic is the same, only the data movement differs."""
     from spim_registration_b200 import synthetic
-    zdim = 200 if (switch, value) == ("z_warp", 2) else 300            # z_warp = 2: the 256-point z window
+    zdim = 200 if (switch, value) in (("z_warp", 2), ("z_warp", 4)) else 300   # z_warp = 2 / 4: the 256-point z window
     f, k = _rand((zdim, 150, 260), 31), _kernel((31, 31, 31), 32)      # 512-point z window, two 128-windows in x and y
     ref = o.convolve_extended(f, k, "mirror")
     base = m.convolve(f, k, "mirror")
@@ -756,7 +757,7 @@ def test_tma_kernels_match_oracle_and_default_kernels(m, o, lib, switch, value):
     loop_ref, _, _ = o.run_deconvolution(ds["imgs"], weights, k1, k2, 2, 0.006)
     prev = lib.mvdSetTuning(switch.encode(), value)
     try:
-        assert prev in (0, 1, 2)
+        assert prev in (0, 1, 2, 3, 4)
         got = m.convolve(f, k, "mirror")
         dec = m.MVDeconvolution(_views(m, ds["imgs"], weights, ds["psfs"]), "EFFICIENT_BAYESIAN", 2, 0.006, directPath=False)
     finally:
