@@ -19,7 +19,7 @@ std::atomic<int> g_use_z_tma{env_flag("MVD_Z_TMA", 0)};
 std::atomic<int> g_use_inv_ring{env_flag("MVD_INV_RING", 2)};
 // 0: register-loading z pass; 1: warp-local lines for 512-point windows (z_warp_kernel); 2: also for 256-point windows;
 // 3: lines on part of a warp, two passes (z_part_kernel) for 512-point windows; 4: also for 256-point windows
-std::atomic<int> g_use_z_warp{env_flag("MVD_Z_WARP", 1)};
+std::atomic<int> g_use_z_warp{env_flag("MVD_Z_WARP", 4)};
 static bool z_warp_covers(int bz) {
     const int g = g_use_z_warp.load();
     return g != 0 && (bz == 512 || g == 2 || g == 4);
