@@ -25,8 +25,8 @@ for line in sys.argv[2:]:
 print("# %d launches, %.1f us of GPU time (serialised by the profiler, cold caches)" % (sum(cnt.values()), total))
 group = collections.defaultdict(float)
 for name, us in tot.items():
-    m = re.search(r"(fwd_xy|z_pass|z_warp|z_tma|inv_xy|inv_ring|sep_xy|sep_z)_kernel", name)
-    fam = {"z_warp": "z_pass", "z_tma": "z_pass", "inv_ring": "inv_xy", "sep_xy": "direct_separable", "sep_z": "direct_separable"}
+    m = re.search(r"(fwd_xy|z_pass|z_warp|z_part|z_tma|inv_xy|inv_ring|sep_xy|sep_z)_kernel", name)
+    fam = {"z_warp": "z_pass", "z_part": "z_pass", "z_tma": "z_pass", "inv_ring": "inv_xy", "sep_xy": "direct_separable", "sep_z": "direct_separable"}
     group[fam.get(m.group(1), m.group(1)) if m else "other"] += us
 print("# by kernel family: " + ", ".join("%s %.3f" % (k, v / total) for k, v in sorted(group.items(), key=lambda kv: -kv[1])))
 for name, us in sorted(tot.items(), key=lambda kv: -kv[1])[:40]:

@@ -11,7 +11,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start o
     python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_launches_$TAG.log 2>&1
 # byte model and plain timing of one loop step on two views, then the full counter set of the last view's 12 launches (2 convolutions x 2 tile classes x 3 kernels)
 MVD_PROF_MODEL=1 python scripts/prof_conv.py 1024 1024 512 31 1 > gpurun_out/prof_$TAG.log 2>&1 || { tail -5 gpurun_out/prof_$TAG.log; exit 1; }
-MVD_PROF_MODEL=0 ncu --set full --clock-control none --import-source on -k regex:"fwd_xy|z_pass|z_warp|z_tma|inv_xy|inv_ring" --launch-skip 52 -c 12 -f -o gpurun_out/prof_$TAG \
+MVD_PROF_MODEL=0 ncu --set full --clock-control none --import-source on -k regex:"fwd_xy|z_pass|z_warp|z_part|z_tma|inv_xy|inv_ring" --launch-skip 52 -c 12 -f -o gpurun_out/prof_$TAG \
     python scripts/prof_conv.py 1024 1024 512 31 1 > gpurun_out/ncu_full_$TAG.log 2>&1
 ncu -i gpurun_out/prof_$TAG.ncu-rep --page raw --csv > gpurun_out/prof_${TAG}_raw.csv 2>/dev/null
 python scripts/ncu_summary.py gpurun_out/prof_$TAG.ncu-rep > gpurun_out/ncu_full_${TAG}_summary.txt 2>&1

@@ -29,10 +29,10 @@ fam = collections.defaultdict(lambda: dict(launches=0, dram_read_mb=0.0, dram_wr
 detail = []
 for d in data:
     name = d[ix["Kernel Name"]]
-    m = re.search(r"(fwd_xy|z_pass|z_warp|z_tma|inv_xy|inv_ring)_kernel", name)
+    m = re.search(r"(fwd_xy|z_pass|z_warp|z_part|z_tma|inv_xy|inv_ring)_kernel", name)
     if not m:
         continue
-    family = {"z_warp": "z_pass", "z_tma": "z_pass", "inv_ring": "inv_xy"}.get(m.group(1), m.group(1))  # kernel generations of one pass
+    family = {"z_warp": "z_pass", "z_part": "z_pass", "z_tma": "z_pass", "inv_ring": "inv_xy"}.get(m.group(1), m.group(1))  # kernel generations of one pass
     f = fam[family]
     rd, wr, us = num(d, "dram__bytes_read.sum") / 1e6, num(d, "dram__bytes_write.sum") / 1e6, num(d, "gpu__time_duration.sum")
     f["launches"] += 1
