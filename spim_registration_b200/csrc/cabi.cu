@@ -273,6 +273,11 @@ struct mvdContext {
         std::memset(&ep, 0, sizeof(ep));
         ep.out = out;
         ep.lambda = lambda;
+        {
+            const double a = 2.0 * lambda;  // make_tikhonov (device_common.cuh)
+            ep.tik_hi = (float)a;
+            ep.tik_lo = (float)(a - (double)ep.tik_hi);
+        }
         ep.min_value = min_value;
         for (int d = 0; d < 3; ++d) { ep.out_dim[d] = adim[d]; ep.out_off[d] = glo[d]; ep.aux_dim[d] = bdim[d]; }
         if (out == psi) { ep.peers = d_peers_psi; ep.n_peers = (int)peers_psi.size(); }

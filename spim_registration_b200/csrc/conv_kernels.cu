@@ -480,7 +480,7 @@ __global__ void __launch_bounds__((InvThreads<BX, BY>::NT), (InvCfg<BX, BY>::MIN
     const int cu = tid / CPR;
     const ConstTw256 twc{8 - ilog2<BY>()};
     const bool use_tik = ep.lambda > 0.0;
-    const TikhonovConst tik = make_tikhonov(ep.lambda);
+    const TikhonovConst tik = {ep.tik_hi, ep.tik_lo, ep.lambda};
     double lsum = 0.0;
     float lmax = 0.f;
     __syncthreads();

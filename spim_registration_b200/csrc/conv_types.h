@@ -56,6 +56,8 @@ struct EpilogueArgs {
     float weight_const;    // EPI_UPDATE: used when weight == nullptr
     float add_const;       // added to the convolution result before the epilogue
     double lambda;         // Tikhonov parameter (0 = off)
+    float tik_hi, tik_lo;  // 2 lambda as a float pair (make_tikhonov), filled by the host: left to the kernel, the compiler
+                           // recomputed the pair per voxel (2 DADD, 3 F2F: 5 % of the update kernel's instructions)
     float min_value;       // 1e-4f in the reference (MVDeconvolution.java:49)
     double* sum_change;    // EPI_UPDATE statistics (device scalars) or nullptr
     unsigned int* max_change_bits;

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(ring::THREADS, 1)
 
     auto gsync = [&] { tma::group_sync(1 + g, GT); };
     const bool use_tik = ep.lambda > 0.0;
-    const TikhonovConst tik = make_tikhonov(ep.lambda);
+    const TikhonovConst tik = {ep.tik_hi, ep.tik_lo, ep.lambda};
     double lsum = 0.0;
     float lmax = 0.f;
     PeerTarget* s_peer = peers_all + g * kMaxPeers;

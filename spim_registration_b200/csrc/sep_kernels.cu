@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(SEP_NT) sep_z_kernel(const float* __restrict__
     for (int i = 0; i < KMAX; ++i) { sxy += taps.x[i]; sy += taps.y[i]; }
     const float fill_t = taps.per_pass_fill ? fillv : fillv * sxy * sy;
     const bool use_tik = ep.lambda > 0.0;
-    const TikhonovConst tik = make_tikhonov(ep.lambda);
+    const TikhonovConst tik = {ep.tik_hi, ep.tik_lo, ep.lambda};
     double lsum = 0.0;
     float lmax = 0.f;
     float win[KMAX - 1 + U];  // win[j] = plane (r0 - (KMAX - 1) + j) of tmp at this thread's (x, y)
