@@ -114,15 +114,19 @@ __device__ __forceinline__ void inv_rows128(float2* plane, const float2* twr, co
                     const float av[4] = {a[i4].x, a[i4].y, a[i4].z, a[i4].w};
                     const float bv[4] = {b[i4].x, b[i4].y, b[i4].z, b[i4].w};
                     float r[4];
+                    if constexpr (EPI == EPI_UPDATE) {
+                        next_psi_quad(av, c, bv, use_tik, tik, ep.min_value, r);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        if constexpr (EPI == EPI_STORE) r[i] = c[i];
-                        else if constexpr (EPI == EPI_QUOTIENT) r[i] = quotient_value(av[i], c[i]);
-                        else {
-                            r[i] = next_psi_value(av[i], c[i], bv[i], use_tik, tik, ep.min_value);
+                        for (int i = 0; i < 4; ++i) {
                             const float ch = fabsf(__fsub_rn(r[i], av[i]));
                             rsum += ch;
                             lmax = fmaxf(lmax, ch);  // fmaxf drops NaN
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            if constexpr (EPI == EPI_STORE) r[i] = c[i];
+                            else r[i] = quotient_value(av[i], c[i]);
                         }
                     }
                     *reinterpret_cast<float4*>(outp + 16 * m) = make_float4(r[0], r[1], r[2], r[3]);
