@@ -178,7 +178,7 @@ __global__ void __launch_bounds__((XYThreads<BX, BY>::NT), FwdCfg<BX, BY>::MIN_C
         // ---- phase 1: rows, real -> half spectrum (packed: slot 0 = (X[0], X[H]))
         if constexpr (BX == 128) {
             const int q = tid & 3;
-            if (MVD_PREFETCH && xfast && zi + 1 < XY_ZPC && z + 1 < bz) {
+            if ((MVD_PREFETCH & 1) && xfast && zi + 1 < XY_ZPC && z + 1 < bz) {
                 // pull the next plane's rows towards L2 while this plane is transformed
                 const int zn = map_coord(tile.o[2] + z + 1, src.dim[2], src.off[2], src.gmin[2], src.gdim[2], src.ext);
                 if (zn >= 0) {
@@ -527,8 +527,9 @@ __global__ void __launch_bounds__((InvThreads<BX, BY>::NT), (InvCfg<BX, BY>::MIN
         const int zv = tile.e[2] + zr;              // plane inside the volume
         const float2* __restrict__ in = scratch + (size_t)ti * tile_stride + (size_t)zt * ((H + 1) * BY);
 
-        if constexpr (BX == 128 && MVD_PREFETCH != 0) {
-            // pull this plane's epilogue operands and the next plane's spectrum towards L2
+        if constexpr (BX == 128 && (MVD_PREFETCH & 6) != 0) {
+            // pull this plane's epilogue operands (2) and the next plane's spectrum (4) towards L2
+            if (MVD_PREFETCH & 2)
             for (int yl = tid >> 2; yl < n1; yl += NT / 4) {
                 const int q = tid & 3;
                 const size_t ob = ((size_t)(zv + ep.out_off[2]) * ep.out_dim[1] + (tile.e[1] + yl + ep.out_off[1])) * (size_t)ep.out_dim[0] +
@@ -542,7 +543,7 @@ __global__ void __launch_bounds__((InvThreads<BX, BY>::NT), (InvCfg<BX, BY>::MIN
                     }
                 }
             }
-            if (zi + 1 < XY_ZPC && zr + 1 < tile.n[2]) {
+            if ((MVD_PREFETCH & 4) && zi + 1 < XY_ZPC && zr + 1 < tile.n[2]) {
                 const float2* __restrict__ nx = in + (H + 1) * BY;
                 for (int i = tid; i < (H + 1) * BY / 16; i += NT) prefetch_l2(nx + 16 * i);
             }
