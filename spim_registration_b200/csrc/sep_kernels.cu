@@ -242,28 +242,41 @@ __global__ void __launch_bounds__(SEP_NT) sep_z_kernel(const float* __restrict__
             b[u] = bn[u];
         }
         if (r0 + U < zend + H) request(r0 + U, optr + U * oplane, iptr + U * aplane, wptr + U * aplane);
+        float acc[U];
+        bool ok[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const int z = r0 + u - H;
-            if (!(z >= z0 && z < zend && live)) continue;
-            float acc = 0.f;
+            ok[u] = z >= z0 && z < zend && live;
+            float s = 0.f;
 #pragma unroll
-            for (int i = 0; i < KMAX; ++i) acc = fmaf(taps.z[i], win[u + i], acc);
-            acc += ep.add_const;
-            if constexpr (EPI == EPI_STORE) {
-                optr[u * oplane] = acc;
-                push(z, acc);
-            } else if constexpr (EPI == EPI_QUOTIENT) {
-                const float qv = quotient_value(a[u], acc);
-                optr[u * oplane] = qv;
-                push(z, qv);
-            } else {
-                const float nv = next_psi_value(a[u], acc, b[u], use_tik, tik, ep.min_value);
-                optr[u * oplane] = nv;
-                push(z, nv);
-                const float ch = fabsf(__fsub_rn(nv, a[u]));
-                lsum += (double)ch;
+            for (int i = 0; i < KMAX; ++i) s = fmaf(taps.z[i], win[u + i], s);
+            acc[u] = s + ep.add_const;
+        }
+        if constexpr (EPI == EPI_UPDATE) {
+            // the step's four voxels together (next_psi_quad: no branch per voxel, device_common.cuh); voxels outside the
+            // chunk carry a = 0 and are neither stored nor counted; their change is summed in float first (four terms)
+            static_assert(U == 4, "the update epilogue takes the planes of a step as one quad");
+            float nv[4];
+            next_psi_quad(a, acc, b, use_tik, tik, ep.min_value, nv);
+            float rs = 0.f;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (!ok[u]) continue;
+                optr[u * oplane] = nv[u];
+                push(r0 + u - H, nv[u]);
+                const float ch = fabsf(__fsub_rn(nv[u], a[u]));
+                rs += ch;
                 lmax = fmaxf(lmax, ch);
+            }
+            lsum += (double)rs;
+        } else {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (!ok[u]) continue;
+                const float ov = EPI == EPI_STORE ? acc[u] : quotient_value(a[u], acc[u]);
+                optr[u * oplane] = ov;
+                push(r0 + u - H, ov);
             }
         }
     }
