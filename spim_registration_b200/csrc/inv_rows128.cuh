@@ -122,12 +122,11 @@ __device__ __forceinline__ void inv_rows128(float2* plane, const float2* twr, co
                             rsum += ch;
                             lmax = fmaxf(lmax, ch);  // fmaxf drops NaN
                         }
+                    } else if constexpr (EPI == EPI_QUOTIENT) {
+                        quotient_quad(av, c, r);
                     } else {
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            if constexpr (EPI == EPI_STORE) r[i] = c[i];
-                            else r[i] = quotient_value(av[i], c[i]);
-                        }
+                        for (int i = 0; i < 4; ++i) r[i] = c[i];
                     }
                     *reinterpret_cast<float4*>(outp + 16 * m) = make_float4(r[0], r[1], r[2], r[3]);
                     if (PUSH && npeer) *reinterpret_cast<float4*>(rowf + 4 * q + 16 * m) = make_float4(r[0], r[1], r[2], r[3]);

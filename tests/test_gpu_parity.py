@@ -909,3 +909,46 @@ def test_peer_flag_barrier_on_one_gpu(m, o):
         finally:
             grp.close()
     np.testing.assert_array_equal(out[0], out[1])
+
+
+# ---- the quotient epilogue divides like IEEE float division, special values included ----------------------------------------
+@pytest.mark.parametrize("scale", [1.0, 1e-25, 1e25])
+def test_quotient_epilogue_is_ieee_division_with_special_values(m, lib, scale):
+    """The quotient epilogue of the 128-wide windows evaluates the division for a float4 quad without branches when all
+    four voxels lie inside the fast path's range and falls back to the generic division otherwise (quotient_quad,
+    device_common.cuh).  Both must give img / blurred correctly rounded, 1 where img <= 0 or NaN
+    (MVDeconvolution.java:496-499).  blurred comes from the same transform through the STORE epilogue; scale moves it out
+    of the fast range (every quad takes the fallback)."""
+    import ctypes as C
+    torch = pytest.importorskip("torch")
+    from spim_registration_b200 import _lib as L
+    from spim_registration_b200.parallel import ShardedDeconvolution
+    shape = (40, 150, 260)                                   # two 128-windows in x and y
+    rng = np.random.default_rng(5)
+    psi = ((rng.random(shape, dtype=np.float32) + np.float32(0.5)) * np.float32(scale)).astype(np.float32)
+    k = _kernel((5, 9, 9), 3)
+    img = (rng.random(shape, dtype=np.float32) * np.float32(100.0)).astype(np.float32)
+    flat = img.reshape(-1)
+    special = np.array([0.0, -1.0, 1e-30, 1e30, np.inf, np.nan, 1e-42, -0.0, 3e38, 2.0 ** -60, 2.0 ** 60], np.float32)
+    pos = rng.choice(flat.size, size=special.size * 200, replace=False)
+    flat[pos] = np.tile(special, 200)
+    dec = ShardedDeconvolution(shape[::-1], [img], [1.0], [k], [k], 0.0, None, 0)
+    try:
+        L.check(lib.mvdSetDirectPath(dec.ctx, 0), "mvdSetDirectPath")
+        dec.set_psi(psi)
+        L.check(lib.mvdStepQuotient(dec.ctx, 0), "mvdStepQuotient")
+        torch.cuda.synchronize()
+        q = dec._arrays[1][0].cpu().numpy()
+    finally:
+        dec.close()
+    blurred = m.convolve(psi, k, "mirror")                   # the same kernels up to the epilogue
+    with np.errstate(all="ignore"):
+        want = np.where(img > 0, img / blurred, np.float32(1.0)).astype(np.float32)
+    same = (q == want) | (np.isnan(q) & np.isnan(want))
+    assert same.mean() >= 0.999, "quotient differs from IEEE division in %.4f of the voxels" % (1 - same.mean())
+    bad = ~same
+    if bad.any():                                            # a last-bit difference of the two transforms, not of the division
+        with np.errstate(all="ignore"):
+            assert np.all(np.abs(q[bad] - want[bad]) <= 2e-7 * np.abs(want[bad]))
+    assert (q[~(img > 0)] == 1).all()
+    assert np.isinf(q[np.isinf(img)]).all()
