@@ -271,12 +271,19 @@ __global__ void __launch_bounds__(SEP_NT) sep_z_kernel(const float* __restrict__
             }
             lsum += (double)rs;
         } else {
+            float ov[U];
+            if constexpr (EPI == EPI_QUOTIENT) {
+                static_assert(U == 4, "the quotient epilogue takes the planes of a step as one quad");
+                quotient_quad(a, acc, ov);  // voxels outside the chunk carry a = 0: no division, not stored
+            } else {
+#pragma unroll
+                for (int u = 0; u < U; ++u) ov[u] = acc[u];
+            }
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 if (!ok[u]) continue;
-                const float ov = EPI == EPI_STORE ? acc[u] : quotient_value(a[u], acc[u]);
-                optr[u * oplane] = ov;
-                push(r0 + u - H, ov);
+                optr[u * oplane] = ov[u];
+                push(r0 + u - H, ov[u]);
             }
         }
     }
