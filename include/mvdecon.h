@@ -365,8 +365,10 @@ int mvdSeparableConvolveNoAlloc(int device, const float* dSrc, float* dOut, cons
  *   "z_tma"   1 = z pass with TMA bulk-tensor loads / stores (z_tma_kernels.cu), 0 = register-loading z pass (default)
  *   "inv_ring" inverse xy pass fed by bulk-tensor loads into a shared-memory ring: 2 = for the quotient / store epilogues
  *             (default; the update epilogue keeps the register-loading kernel, which is faster there), 1 = always, 0 = never
- *   "z_warp"  1 = z pass with warp-local 512-point lines behind swizzled bulk-tensor loads / stores (default), 2 = also for
- *             256-point lines (measured slower than the register-loading kernel there), 0 = off; set before views are added
+ *   "z_warp"  z pass with warp-local lines behind swizzled bulk-tensor loads / stores (z_warp_kernels.cu): 4 = lines on part
+ *             of a warp, two FFT passes, three-buffer ring (z_part_kernel) for 512- and 256-point windows (default),
+ *             3 = the same for 512-point windows only, 1 = the first generation (one line per warp, three passes) for
+ *             512-point windows, 2 = also for 256-point ones, 0 = register-loading z pass; set before views are added
  * Returns the previous value, or -1 for an unknown name. */
 int mvdSetTuning(const char* name, int value);
 
