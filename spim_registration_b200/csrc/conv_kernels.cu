@@ -19,6 +19,7 @@
 // for the strided Stockham scatters without per-access swizzle arithmetic, column twiddles come
 // from the constant bank (warp-uniform), and all register arrays are statically indexed.
 #include "conv_kernels.h"
+#include <climits>
 #include "fft_device.cuh"
 #include "row128.cuh"
 #include "z_items.cuh"
@@ -168,6 +169,24 @@ __global__ void __launch_bounds__((XYThreads<BX, BY>::NT), FwdCfg<BX, BY>::MIN_C
     const int cu = tid / CPR;
     const ConstTw256 twc{8 - ilog2<BY>()};
 
+    // the same for every plane of the item (the compiler recomputed them per plane: 134 integer instructions, 6 % of the
+    // kernel): which quads of a row are plain float4 loads, and where the thread's two rows of the window lie in the array
+    unsigned qmask = 0;
+    int ymap0 = 0, ymap1 = 0;
+    if constexpr (BX == 128) {
+        const int q = tid & 3;
+        const bool al4 = ((xo | src.dim[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(src.data) & 15) == 0;
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+            const int xa = xo + 16 * m + 4 * q, xgl = xg + 16 * m + 4 * q;
+            if (al4 && xa >= 0 && xa + 3 < src.dim[0] && xgl >= 0 && xgl + 3 < src.gdim[0]) qmask |= 1u << m;
+        }
+        if constexpr (FwdCfg<BX, BY>::PIPE) {
+            ymap0 = map_coord(tile.o[1] + (tid >> 2), src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
+            ymap1 = map_coord(tile.o[1] + (tid >> 2) + NT / 4, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
+        }
+    }
+
 #pragma unroll 1
     for (int zi = 0; zi < XY_ZPC; ++zi) {
         const int z = z0 + zi;
@@ -190,15 +209,8 @@ __global__ void __launch_bounds__((XYThreads<BX, BY>::NT), FwdCfg<BX, BY>::MIN_C
             }
             // quads (4 consecutive samples) of this thread that lie inside the array and the global
             // domain are loaded as float4 even in tiles that touch the volume border
-            const bool al4 = ((xo | src.dim[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(src.data) & 15) == 0;
-            unsigned qmask = 0;
-#pragma unroll
-            for (int m = 0; m < 8; ++m) {
-                const int xa = xo + 16 * m + 4 * q, xgl = xg + 16 * m + 4 * q;
-                if (al4 && xa >= 0 && xa + 3 < src.dim[0] && xgl >= 0 && xgl + 3 < src.gdim[0]) qmask |= 1u << m;
-            }
-            auto load_row = [&](int row, float2 (&a)[8], float2 (&b)[8]) {
-                const int yl = zl < 0 ? zl : map_coord(tile.o[1] + row, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext);
+            auto load_row = [&](int row, int ymapped, float2 (&a)[8], float2 (&b)[8]) {
+                const int yl = zl < 0 ? zl : (ymapped != INT_MIN ? ymapped : map_coord(tile.o[1] + row, src.dim[1], src.off[1], src.gmin[1], src.gdim[1], src.ext));
                 if (yl < 0) {
                     const float f = yl == -1 ? fillv : 0.f;
 #pragma unroll
@@ -229,15 +241,15 @@ __global__ void __launch_bounds__((XYThreads<BX, BY>::NT), FwdCfg<BX, BY>::MIN_C
                 // both row rounds of the plane requested up front: one exposed load latency per plane instead of two
                 float2 a0[8], b0[8], a1[8], b1[8];
                 const int r0 = tid >> 2, r1 = r0 + NT / 4;
-                load_row(r0, a0, b0);
-                load_row(r1, a1, b1);
+                load_row(r0, ymap0, a0, b0);
+                load_row(r1, ymap1, a1, b1);
                 row128_forward(a0, b0, plane + r0 * P, twr, twu, q, 0xffffffffu);
                 row128_forward(a1, b1, plane + r1 * P, twr, twu, q, 0xffffffffu);
             } else {
 #pragma unroll 1
                 for (int row = tid >> 2; row < BY; row += NT / 4) {
                     float2 a[8], b[8];
-                    load_row(row, a, b);
+                    load_row(row, INT_MIN, a, b);
                     row128_forward(a, b, plane + row * P, twr, twu, q, 0xffffffffu);
                 }
             }
